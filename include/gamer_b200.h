@@ -1,0 +1,181 @@
+/*
+ * gamer_b200.h — C ABI of the B200-native galaxy volume integrator.
+ *
+ * This is the drop-in boundary for ONE path of MichaelMoroz/gamer: the per-pixel
+ * ray march + component evaluation + simplex-noise octaves + dust absorption /
+ * RGB emission (K1) and the exposure/gamma/saturation pass (K2).  Everything a
+ * caller of the reference's `Rasterizer` sets or reads for that path crosses
+ * this header as plain pointers and sizes; no C++/torch/Qt types, no
+ * exceptions, no exit(), no logging.
+ *
+ * Reference seam replaced (paths relative to the reference checkout):
+ *   class Rasterizer            source/galaxy/rasterizer.h:20-127
+ *   Rasterizer::RenderPixels    source/galaxy/rasterizer.cpp:279-313   -> gamer_b200_render*
+ *   Rasterizer::AssembleImage   source/galaxy/rasterizer.cpp:315-327   -> gamer_b200_tonemap*
+ *   Rasterizer::Abort/getPercentDone  rasterizer.h:91-118              -> gamer_b200_abort / _progress
+ *   the parameter model (ComponentParams / GalaxyParams / GalaxyInstance /
+ *   RenderingParams / GamerCamera)                                     -> the three POD structs below
+ *
+ * Precision of the structs follows the reference's own storage: what it keeps
+ * in `double` (componentparams.h:7-23, galaxyparams.h:12-29, renderingparams.h:19-37)
+ * is `double` here, what it keeps in a float Qt value class (QVector3D,
+ * QQuaternion, QMatrix4x4) is `float` here, so "identical parameters" means
+ * identical bits on both sides of a parity test.
+ *
+ * Every function returns 0 on success or a negative GAMER_E_* code; the text of
+ * the last error of a context is available from gamer_b200_last_error().
+ * There is NO CPU fallback: without a CUDA device every compute entry point
+ * fails with GAMER_E_CUDA.
+ */
+#ifndef GAMER_B200_H
+#define GAMER_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GAMER_B200_ABI_VERSION 1
+
+/* error classes */
+#define GAMER_OK          0
+#define GAMER_E_ARG      -1   /* bad argument / scene out of supported range  */
+#define GAMER_E_CUDA     -2   /* CUDA runtime error (text in last_error)      */
+#define GAMER_E_ABORTED  -3   /* gamer_b200_abort() was called during render  */
+#define GAMER_E_STATE    -4   /* call order (e.g. render before upload)       */
+
+/* component classes — the factory strings of source/galaxy/galaxy.cpp:15-42 */
+#define GAMER_CLASS_BULGE          0   /* "bulge"          galaxycomponents.cpp:5-39    */
+#define GAMER_CLASS_DISK           1   /* "disk"           galaxycomponents.cpp:41-59   */
+#define GAMER_CLASS_DUST           2   /* "dust"           galaxycomponents.cpp:64-84   */
+#define GAMER_CLASS_DUST2          3   /* "dust2"          galaxycomponents.cpp:85-114  */
+#define GAMER_CLASS_DUST_POSITIVE  4   /* "dust positive"  galaxycomponents.cpp:116-136 */
+#define GAMER_CLASS_STARS          5   /* "stars"          galaxycomponents.cpp:139-155 */
+#define GAMER_CLASS_STARS_SMALL    6   /* "stars small"    galaxycomponents.cpp:159-170 — libc rand() per sample,
+                                          nondeterministic; evaluated as a no-op exactly as the reference's own
+                                          parity harnesses do (tools/galaxy_repro.py:734-737)                  */
+
+#define GAMER_MAX_GALAXIES    8
+#define GAMER_MAX_COMPONENTS  64      /* over all galaxies of one frame */
+
+/* One GalaxyComponent: ComponentParams (componentparams.h:7-23) + its resolved spectrum (spectrum.h:50-59). */
+typedef struct GamerComponent {
+    int32_t class_id;           /* GAMER_CLASS_*                                              */
+    int32_t _pad0;
+    double  active;             /* evaluated iff == 1.0  (rasterizer.cpp:458)                 */
+    double  strength, arm, z0, r0, inner, delta, winding, scale,
+            noise_offset, noise_tilt, ks;
+    float   spec[3];            /* RGB of the named spectrum; white if the name is unknown    */
+    float   _pad1;
+} GamerComponent;
+
+/* One GalaxyInstance (galaxyinstance.h:8-23) + its GalaxyParams (galaxyparams.h:12-29). */
+typedef struct GamerGalaxy {
+    float   pos[3];             /* GalaxyInstance::position                                   */
+    float   orient[3];          /* GalaxyInstance::orientation (as given; not re-normalised)  */
+    float   rotmat[4];          /* QQuaternion rotationTo((0,1,0), orient) as w,x,y,z         */
+    float   axis[3];            /* GalaxyParams::axis (ellipsoid semi-axes)                   */
+    float   _pad0;
+    double  intensity_scale;
+    double  winding_b, winding_n, no_arms;
+    double  arm[4];             /* arm1..arm4 (radians)                                       */
+    int32_t comp_begin;         /* range into the component array, file order                 */
+    int32_t comp_count;
+} GamerGalaxy;
+
+/* One frame: camera + size + step (RenderingParams, GamerCamera). Galaxies must already be sorted
+ * far -> near as Rasterizer::Prepare does (rasterizer.cpp:190-201). */
+typedef struct GamerFrame {
+    int32_t width, height;      /* tile extent in pixels; the reference has width==height==full_size  */
+    int32_t full_size;          /* the `size` used by coord2ray (gamercamera.cpp:210-212)             */
+    int32_t x0, y0;             /* tile origin inside the full_size x full_size image                 */
+    int32_t band_rows;          /* 0: rows y0..y0+height-1. >0: interleaved bands — local row L is image */
+    int32_t band_stride;        /* row y0 + (L / band_rows) * band_stride + (L % band_rows)            */
+    int32_t _pad0;
+    float   inv_vp[16];         /* inverse(projection*view), element [row*4+col] = QMatrix4x4(row,col)*/
+    float   cam[3];             /* GamerCamera::camera                                                */
+    float   _pad1;
+    double  ray_step;           /* RenderingParams::rayStep                                           */
+    double  min_ray_step;       /* 0.001; 0.01 in preview (rasterizer.cpp:437-441)                    */
+    int32_t n_galaxies;
+    int32_t n_components;
+    int32_t _pad2[2];
+} GamerFrame;
+
+/* counters filled by gamer_b200_counters (same definitions as the oracle's) */
+#define GAMER_CNT_RAYS       0   /* (pixel, galaxy) pairs that reach getIntensity              */
+#define GAMER_CNT_SAMPLES    1   /* iterations of the march loop (rasterizer.cpp:447-475)      */
+#define GAMER_CNT_GATES      2   /* active-component visits (getRadius+getHeightModulation)    */
+#define GAMER_CNT_COMP_EVALS 3   /* componentIntensity calls that do work                      */
+#define GAMER_CNT_OCTAVES    4   /* raw simplex evaluations                                    */
+#define GAMER_CNT_N          8
+
+typedef struct gamer_ctx gamer_ctx;
+
+/* lifecycle ------------------------------------------------------------------------------- */
+int  gamer_b200_abi_version(void);
+int  gamer_b200_device_count(int32_t *count);
+/* One context per Rasterizer. device_ids/n_devices: the CUDA devices this context renders on
+ * (row bands are interleaved across them and gathered into the caller's buffer). */
+int  gamer_b200_create (gamer_ctx **out, const int32_t *device_ids, int32_t n_devices);
+void gamer_b200_destroy(gamer_ctx *ctx);
+const char *gamer_b200_last_error(gamer_ctx *ctx);     /* ctx may be NULL: last create() error */
+
+/* scene ------------------------------------------------------------------------------------ */
+/* Copies the scene; the caller may free its arrays on return. Replaces setRenderingParams/
+ * AddGalaxy/Prepare (rasterizer.cpp:48-51,190-213,229-240). */
+int  gamer_b200_upload (gamer_ctx *ctx, const GamerFrame *frame,
+                        const GamerGalaxy *galaxies, const GamerComponent *components);
+
+/* K1: ray march ---------------------------------------------------------------------------- */
+/* Blocking. Renders the uploaded frame and writes width*height*3 floats, row-major
+ * (x + y*width), RGB interleaved — the layout of Buffer2D (buffer2d.cpp:26-31) — into HOST memory. */
+int  gamer_b200_render (gamer_ctx *ctx, float *rgb_linear_out);
+/* Same, but leaves the result in the context's device framebuffer (no D2H). */
+int  gamer_b200_render_device(gamer_ctx *ctx);
+/* Like render_device but also accumulates the GAMER_CNT_* counters (slower instrumented kernel). */
+int  gamer_b200_render_counted(gamer_ctx *ctx);
+int  gamer_b200_counters(gamer_ctx *ctx, uint64_t out[GAMER_CNT_N]);
+
+/* K2: post-process ------------------------------------------------------------------------- */
+/* Buffer2D::PostProcess + ToColorBuffer (buffer2d.cpp:65-85,106-126) on the last rendered frame.
+ * stars_rgb_or_null: optional host float[width*height*3] added first (Buffer2D::Add, :204-215).
+ * argb_out gets QImage `image` (0xFF, c.red=z, c.green=y, c.blue=x), argb_shadow_out gets the
+ * R/B-swapped `shadowImage` the CLI saves as PNG (consolerenderer.cpp:98). Either may be NULL. */
+int  gamer_b200_tonemap(gamer_ctx *ctx, double exposure, double gamma, double saturation,
+                        const float *stars_rgb_or_null,
+                        uint32_t *argb_out, uint32_t *argb_shadow_out);
+int  gamer_b200_tonemap_device(gamer_ctx *ctx, double exposure, double gamma, double saturation);
+
+/* control (callable from any thread; rasterizer.h:91-118) ----------------------------------- */
+int  gamer_b200_progress(gamer_ctx *ctx, double *fraction);
+int  gamer_b200_abort   (gamer_ctx *ctx);
+
+/* device-side access for callers that keep data on the GPU (multi-GPU gather, benchmarks) ---- */
+/* Device pointers of device `which` (0..n_devices-1): linear float RGB framebuffer and the two
+ * ARGB images; rows_out = number of rows that device holds (its bands, in band order). */
+int  gamer_b200_device_buffers(gamer_ctx *ctx, int32_t which, void **rgb_dev, void **argb_dev,
+                               void **argb_shadow_dev, int32_t *rows_out);
+/* CUDA-event time of the last K1 / K2 launch on device 0 (milliseconds). */
+int  gamer_b200_last_kernel_ms(gamer_ctx *ctx, float *k1_ms, float *k2_ms);
+/* number of kernel launches issued by this context since creation */
+int  gamer_b200_launch_count(gamer_ctx *ctx, uint64_t *launches);
+
+/* function-level probes of the device noise code (parity tests; same device functions as K1) -- */
+/* raw simplex (simplexnoise.cpp:243-333) at n points given as float coordinates widened to
+ * double exactly like the reference's callers do. lattice_out: 10 int32 per point
+ * (i,j,k, i1+2*j1+4*k1, i2+2*j2+4*k2, gi0,gi1,gi2,gi3, 0). value_out: noise value. */
+int  gamer_b200_probe_simplex(gamer_ctx *ctx, const float *xyz, int32_t n, double frequency,
+                              int32_t *lattice_out, float *value_out);
+/* Noise::octave_noise_3d (noise.cpp:162-180) and Noise::getRidgedMf (:81-128) */
+int  gamer_b200_probe_fbm   (gamer_ctx *ctx, const float *xyz, int32_t n, int32_t octaves,
+                             double persistence, double scale, float *value_out);
+int  gamer_b200_probe_ridged(gamer_ctx *ctx, const float *xyz, int32_t n, double frequency,
+                             int32_t octaves, double lacunarity, double offset, double gain,
+                             float *value_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GAMER_B200_H */
