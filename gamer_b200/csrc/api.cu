@@ -1,0 +1,493 @@
+// api.cu — the extern "C" boundary (include/gamer_b200.h): contexts, scene upload, K1/K2 launches,
+// multi-device band split + gather, progress/abort, probes.  No exceptions, exit() or logging cross
+// this file; every CUDA error is turned into GAMER_E_CUDA with its text kept in the context.
+#include <atomic>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <new>
+#include <string>
+#include <vector>
+#include <cuda_runtime.h>
+#include "../../include/gamer_b200.h"
+#include "kernels.h"
+#include "scene_build.h"
+
+#define MD_BAND_ROWS 32      // rows per interleaved band when one context spans several devices
+
+namespace {
+
+struct Dev {
+    int device = 0;
+    int sm_count = 0;
+    cudaStream_t st = nullptr, ctrl = nullptr;
+    cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};   // K1 begin/end, K2 begin/end
+    float *rgb = nullptr, *stars = nullptr;
+    uint32_t *argb = nullptr, *shadow = nullptr;
+    size_t cap_px = 0, cap_stars = 0;
+    unsigned long long *counters = nullptr;
+    int *abort_flag = nullptr;
+    unsigned int *progress = nullptr;
+    unsigned int *progress_host = nullptr;    // pinned
+    unsigned int n_blocks = 0;
+    int rows = 0;                              // local rows this device renders
+    DScene scene;
+};
+
+std::string g_create_error;
+std::mutex g_create_mutex;
+
+}  // namespace
+
+struct gamer_ctx {
+    std::vector<Dev> devs;
+    GamerFrame frame;
+    bool uploaded = false, rendered = false, counted = false;
+    std::string err;
+    std::atomic<int> abort_req{0};
+    std::atomic<int> rendering{0};
+    uint64_t launches = 0;
+    float k1_ms = 0.f, k2_ms = 0.f;
+    uint64_t counters[GAMER_CNT_N] = {0, 0, 0, 0, 0, 0, 0, 0};
+    std::mutex mu;                             // render/tonemap/upload are not re-entrant per context
+};
+
+namespace {
+
+int set_err(gamer_ctx *c, int code, const std::string &m) {
+    if (c) c->err = m;
+    else { std::lock_guard<std::mutex> l(g_create_mutex); g_create_error = m; }
+    return code;
+}
+int cuda_fail(gamer_ctx *c, cudaError_t e, const char *what) {
+    return set_err(c, GAMER_E_CUDA, std::string(what) + ": " + cudaGetErrorString(e));
+}
+#define CK(call)                                                   \
+    do {                                                           \
+        cudaError_t _e = (call);                                   \
+        if (_e != cudaSuccess) return cuda_fail(ctx, _e, #call);   \
+    } while (0)
+
+void free_dev(Dev &d) {
+    cudaSetDevice(d.device);
+    if (d.rgb) cudaFree(d.rgb);
+    if (d.stars) cudaFree(d.stars);
+    if (d.argb) cudaFree(d.argb);
+    if (d.shadow) cudaFree(d.shadow);
+    if (d.counters) cudaFree(d.counters);
+    if (d.abort_flag) cudaFree(d.abort_flag);
+    if (d.progress) cudaFree(d.progress);
+    if (d.progress_host) cudaFreeHost(d.progress_host);
+    for (auto &e : d.ev) if (e) cudaEventDestroy(e);
+    if (d.st) cudaStreamDestroy(d.st);
+    if (d.ctrl) cudaStreamDestroy(d.ctrl);
+    d = Dev();
+}
+
+// rows of a `height`-row frame that device `which` of `n` owns (interleaved MD_BAND_ROWS bands)
+int rows_of_device(int height, int which, int n) {
+    if (n == 1) return height;
+    int rows = 0;
+    for (int b = which; b * MD_BAND_ROWS < height; b += n) {
+        int r0 = b * MD_BAND_ROWS, r1 = r0 + MD_BAND_ROWS;
+        rows += (r1 < height ? r1 : height) - r0;
+    }
+    return rows;
+}
+
+int ensure_capacity(gamer_ctx *ctx, Dev &d, size_t px) {
+    if (px <= d.cap_px) return GAMER_OK;
+    CK(cudaSetDevice(d.device));
+    if (d.rgb) cudaFree(d.rgb);
+    if (d.argb) cudaFree(d.argb);
+    if (d.shadow) cudaFree(d.shadow);
+    d.rgb = nullptr; d.argb = d.shadow = nullptr; d.cap_px = 0;
+    CK(cudaMalloc(&d.rgb, px * 3 * sizeof(float)));
+    CK(cudaMalloc(&d.argb, px * sizeof(uint32_t)));
+    CK(cudaMalloc(&d.shadow, px * sizeof(uint32_t)));
+    d.cap_px = px;
+    return GAMER_OK;
+}
+
+// launch K1 on every device of the context (no host sync)
+int launch_render(gamer_ctx *ctx, bool counted) {
+    for (Dev &d : ctx->devs) {
+        if (d.rows <= 0) continue;
+        CK(cudaSetDevice(d.device));
+        CK(cudaMemsetAsync(d.progress, 0, sizeof(unsigned int), d.st));
+        CK(cudaMemsetAsync(d.abort_flag, 0, sizeof(int), d.st));
+        if (counted) CK(cudaMemsetAsync(d.counters, 0, GAMER_CNT_N * sizeof(unsigned long long), d.st));
+        CK(cudaMemsetAsync(d.rgb, 0, (size_t)d.rows * d.scene.width * 3 * sizeof(float), d.st));
+        CK(cudaEventRecord(d.ev[0], d.st));
+        CK(gk::launch_k1(d.scene, d.rgb, d.counters, d.abort_flag, d.progress, counted, d.st, &d.n_blocks));
+        CK(cudaEventRecord(d.ev[1], d.st));
+        ctx->launches += 1;
+    }
+    return GAMER_OK;
+}
+
+int sync_all(gamer_ctx *ctx) {
+    for (Dev &d : ctx->devs) {
+        CK(cudaSetDevice(d.device));
+        CK(cudaStreamSynchronize(d.st));
+    }
+    return GAMER_OK;
+}
+
+int finish_render(gamer_ctx *ctx, bool counted) {
+    int rc = sync_all(ctx);
+    if (rc) return rc;
+    Dev &d0 = ctx->devs[0];
+    CK(cudaSetDevice(d0.device));
+    if (d0.rows > 0) CK(cudaEventElapsedTime(&ctx->k1_ms, d0.ev[0], d0.ev[1]));
+    if (counted) {
+        for (auto &v : ctx->counters) v = 0;
+        for (Dev &d : ctx->devs) {
+            if (d.rows <= 0) continue;
+            unsigned long long h[GAMER_CNT_N];
+            CK(cudaSetDevice(d.device));
+            CK(cudaMemcpy(h, d.counters, sizeof(h), cudaMemcpyDeviceToHost));
+            for (int q = 0; q < GAMER_CNT_N; q++) ctx->counters[q] += h[q];
+        }
+    }
+    ctx->counted = counted;
+    ctx->rendered = true;
+    if (ctx->abort_req.exchange(0)) return set_err(ctx, GAMER_E_ABORTED, "render aborted");
+    return GAMER_OK;
+}
+
+// copy every device's bands into a full-frame host array with `elem` bytes per pixel
+int gather_to_host(gamer_ctx *ctx, char *host, size_t elem, int which_buf) {
+    const int W = ctx->frame.width, H = ctx->frame.height, n = (int)ctx->devs.size();
+    for (int di = 0; di < n; di++) {
+        Dev &d = ctx->devs[di];
+        if (d.rows <= 0) continue;
+        CK(cudaSetDevice(d.device));
+        const char *src = which_buf == 0 ? (const char *)d.rgb : which_buf == 1 ? (const char *)d.argb : (const char *)d.shadow;
+        if (n == 1) {
+            CK(cudaMemcpyAsync(host, src, (size_t)W * H * elem, cudaMemcpyDeviceToHost, d.st));
+            continue;
+        }
+        int local = 0;
+        for (int b = di; b * MD_BAND_ROWS < H; b += n) {
+            int r0 = b * MD_BAND_ROWS, r1 = r0 + MD_BAND_ROWS;
+            if (r1 > H) r1 = H;
+            CK(cudaMemcpyAsync(host + (size_t)r0 * W * elem, src + (size_t)local * W * elem, (size_t)(r1 - r0) * W * elem,
+                               cudaMemcpyDeviceToHost, d.st));
+            local += r1 - r0;
+        }
+    }
+    return sync_all(ctx);
+}
+
+}  // namespace
+
+extern "C" {
+
+int gamer_b200_abi_version(void) { return GAMER_B200_ABI_VERSION; }
+
+int gamer_b200_device_count(int32_t *count) {
+    if (!count) return GAMER_E_ARG;
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess) { *count = 0; return cuda_fail(nullptr, e, "cudaGetDeviceCount"); }
+    *count = n;
+    return GAMER_OK;
+}
+
+const char *gamer_b200_last_error(gamer_ctx *ctx) {
+    if (ctx) return ctx->err.c_str();
+    return g_create_error.c_str();
+}
+
+void gamer_b200_destroy(gamer_ctx *ctx) {
+    if (!ctx) return;
+    for (Dev &d : ctx->devs) free_dev(d);
+    delete ctx;
+}
+
+int gamer_b200_create(gamer_ctx **out, const int32_t *device_ids, int32_t n_devices) {
+    if (!out) return GAMER_E_ARG;
+    *out = nullptr;
+    gamer_ctx *ctx = nullptr;          // CK() reports into g_create_error while ctx is null
+    int ndev = 0;
+    CK(cudaGetDeviceCount(&ndev));
+    if (ndev <= 0) return set_err(nullptr, GAMER_E_CUDA, "no CUDA device: this library has no CPU fallback");
+    int32_t dflt = 0;
+    if (!device_ids || n_devices <= 0) { device_ids = &dflt; n_devices = 1; }
+    for (int i = 0; i < n_devices; i++)
+        if (device_ids[i] < 0 || device_ids[i] >= ndev) return set_err(nullptr, GAMER_E_ARG, "device id out of range");
+    gamer_ctx *c = new (std::nothrow) gamer_ctx();
+    if (!c) return set_err(nullptr, GAMER_E_ARG, "out of host memory");
+    c->devs.resize(n_devices);
+    for (int i = 0; i < n_devices; i++) {
+        Dev &d = c->devs[i];
+        d.device = device_ids[i];
+        cudaError_t e = cudaSetDevice(d.device);
+        cudaDeviceProp prop;
+        if (e == cudaSuccess) e = cudaGetDeviceProperties(&prop, d.device);
+        if (e == cudaSuccess && prop.major != 10) {
+            gamer_b200_destroy(c);
+            return set_err(nullptr, GAMER_E_CUDA, "device is not sm_100 (B200): kernels are built for sm_100a only");
+        }
+        if (e == cudaSuccess) { d.sm_count = prop.multiProcessorCount; e = cudaStreamCreateWithFlags(&d.st, cudaStreamNonBlocking); }
+        if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&d.ctrl, cudaStreamNonBlocking);
+        for (int k = 0; k < 4 && e == cudaSuccess; k++) e = cudaEventCreate(&d.ev[k]);
+        if (e == cudaSuccess) e = cudaMalloc(&d.counters, GAMER_CNT_N * sizeof(unsigned long long));
+        if (e == cudaSuccess) e = cudaMalloc(&d.abort_flag, sizeof(int));
+        if (e == cudaSuccess) e = cudaMalloc(&d.progress, sizeof(unsigned int));
+        if (e == cudaSuccess) e = cudaHostAlloc(&d.progress_host, sizeof(unsigned int), cudaHostAllocDefault);
+        if (e == cudaSuccess) e = cudaMemset(d.abort_flag, 0, sizeof(int));
+        if (e == cudaSuccess) e = cudaMemset(d.progress, 0, sizeof(unsigned int));
+        if (e != cudaSuccess) {
+            gamer_b200_destroy(c);
+            return cuda_fail(nullptr, e, "context creation");
+        }
+    }
+    *out = c;
+    return GAMER_OK;
+}
+
+int gamer_b200_upload(gamer_ctx *ctx, const GamerFrame *frame, const GamerGalaxy *galaxies, const GamerComponent *components) {
+    if (!ctx || !frame) return GAMER_E_ARG;
+    std::lock_guard<std::mutex> lock(ctx->mu);
+    const int n = (int)ctx->devs.size();
+    if (n > 1 && frame->band_rows != 0) return set_err(ctx, GAMER_E_ARG, "a multi-device context splits bands itself: band_rows must be 0");
+    char msg[256] = {0};
+    for (int di = 0; di < n; di++) {
+        Dev &d = ctx->devs[di];
+        GamerFrame f = *frame;
+        d.rows = rows_of_device(frame->height, di, n);
+        if (n > 1) {
+            f.y0 = frame->y0 + di * MD_BAND_ROWS;
+            f.band_rows = MD_BAND_ROWS;
+            f.band_stride = MD_BAND_ROWS * n;
+            f.height = d.rows > 0 ? d.rows : 1;
+        }
+        int rc = gk_build_scene(&f, galaxies, components, &d.scene, msg, sizeof(msg));
+        if (rc) return set_err(ctx, rc, msg);
+        if (d.rows > 0) {
+            rc = ensure_capacity(ctx, d, (size_t)d.rows * frame->width);
+            if (rc) return rc;
+        }
+    }
+    ctx->frame = *frame;
+    ctx->uploaded = true;
+    ctx->rendered = false;
+    return GAMER_OK;
+}
+
+static int render_common(gamer_ctx *ctx, bool counted, float *host_out) {
+    if (!ctx) return GAMER_E_ARG;
+    std::lock_guard<std::mutex> lock(ctx->mu);
+    if (!ctx->uploaded) return set_err(ctx, GAMER_E_STATE, "render before upload");
+    ctx->rendering.store(1);
+    int rc = launch_render(ctx, counted);
+    if (!rc) rc = finish_render(ctx, counted);
+    ctx->rendering.store(0);
+    if (rc) return rc;
+    if (host_out) return gather_to_host(ctx, (char *)host_out, 3 * sizeof(float), 0);
+    return GAMER_OK;
+}
+
+int gamer_b200_render(gamer_ctx *ctx, float *rgb_linear_out) {
+    if (!rgb_linear_out) return GAMER_E_ARG;
+    return render_common(ctx, false, rgb_linear_out);
+}
+int gamer_b200_render_device(gamer_ctx *ctx) { return render_common(ctx, false, nullptr); }
+int gamer_b200_render_counted(gamer_ctx *ctx) { return render_common(ctx, true, nullptr); }
+
+int gamer_b200_counters(gamer_ctx *ctx, uint64_t out[GAMER_CNT_N]) {
+    if (!ctx || !out) return GAMER_E_ARG;
+    if (!ctx->rendered || !ctx->counted) return set_err(ctx, GAMER_E_STATE, "counters need a preceding render_counted");
+    for (int q = 0; q < GAMER_CNT_N; q++) out[q] = ctx->counters[q];
+    return GAMER_OK;
+}
+
+static int tonemap_common(gamer_ctx *ctx, double exposure, double gamma, double saturation, const float *stars_host,
+                          uint32_t *argb_out, uint32_t *shadow_out) {
+    if (!ctx) return GAMER_E_ARG;
+    std::lock_guard<std::mutex> lock(ctx->mu);
+    if (!ctx->rendered) return set_err(ctx, GAMER_E_STATE, "tonemap before render");
+    if (!(exposure != 0.0)) return set_err(ctx, GAMER_E_ARG, "exposure must be non-zero");
+    const int W = ctx->frame.width, H = ctx->frame.height, n = (int)ctx->devs.size();
+    for (int di = 0; di < n; di++) {
+        Dev &d = ctx->devs[di];
+        if (d.rows <= 0) continue;
+        CK(cudaSetDevice(d.device));
+        size_t px = (size_t)d.rows * W;
+        const float *stars_dev = nullptr;
+        if (stars_host) {
+            if (d.cap_stars < px) {
+                if (d.stars) cudaFree(d.stars);
+                d.stars = nullptr; d.cap_stars = 0;
+                CK(cudaMalloc(&d.stars, px * 3 * sizeof(float)));
+                d.cap_stars = px;
+            }
+            if (n == 1) CK(cudaMemcpyAsync(d.stars, stars_host, px * 3 * sizeof(float), cudaMemcpyHostToDevice, d.st));
+            else {
+                int local = 0;
+                for (int b = di; b * MD_BAND_ROWS < H; b += n) {
+                    int r0 = b * MD_BAND_ROWS, r1 = r0 + MD_BAND_ROWS;
+                    if (r1 > H) r1 = H;
+                    CK(cudaMemcpyAsync(d.stars + (size_t)local * W * 3, stars_host + (size_t)r0 * W * 3,
+                                       (size_t)(r1 - r0) * W * 3 * sizeof(float), cudaMemcpyHostToDevice, d.st));
+                    local += r1 - r0;
+                }
+            }
+            stars_dev = d.stars;
+        }
+        CK(cudaEventRecord(d.ev[2], d.st));
+        CK(gk::launch_k2(d.rgb, stars_dev, d.argb, d.shadow, px, exposure, gamma, saturation, d.sm_count, d.st));
+        CK(cudaEventRecord(d.ev[3], d.st));
+        ctx->launches += 1;
+    }
+    int rc = sync_all(ctx);
+    if (rc) return rc;
+    Dev &d0 = ctx->devs[0];
+    CK(cudaSetDevice(d0.device));
+    if (d0.rows > 0) CK(cudaEventElapsedTime(&ctx->k2_ms, d0.ev[2], d0.ev[3]));
+    if (argb_out) { rc = gather_to_host(ctx, (char *)argb_out, sizeof(uint32_t), 1); if (rc) return rc; }
+    if (shadow_out) { rc = gather_to_host(ctx, (char *)shadow_out, sizeof(uint32_t), 2); if (rc) return rc; }
+    return GAMER_OK;
+}
+
+int gamer_b200_tonemap(gamer_ctx *ctx, double exposure, double gamma, double saturation, const float *stars_rgb_or_null,
+                       uint32_t *argb_out, uint32_t *argb_shadow_out) {
+    return tonemap_common(ctx, exposure, gamma, saturation, stars_rgb_or_null, argb_out, argb_shadow_out);
+}
+int gamer_b200_tonemap_device(gamer_ctx *ctx, double exposure, double gamma, double saturation) {
+    return tonemap_common(ctx, exposure, gamma, saturation, nullptr, nullptr, nullptr);
+}
+
+// Rasterizer::getPercentDone (rasterizer.h:112-118): fraction of pixel blocks finished. Any thread.
+int gamer_b200_progress(gamer_ctx *ctx, double *fraction) {
+    if (!ctx || !fraction) return GAMER_E_ARG;
+    if (!ctx->rendering.load()) { *fraction = ctx->rendered ? 1.0 : 0.0; return GAMER_OK; }
+    double done = 0, total = 0;
+    for (Dev &d : ctx->devs) {
+        if (d.rows <= 0 || d.n_blocks == 0) continue;
+        if (cudaSetDevice(d.device) != cudaSuccess) continue;
+        if (cudaMemcpyAsync(d.progress_host, d.progress, sizeof(unsigned int), cudaMemcpyDeviceToHost, d.ctrl) != cudaSuccess) continue;
+        if (cudaStreamSynchronize(d.ctrl) != cudaSuccess) continue;
+        done += *d.progress_host;
+        total += d.n_blocks;
+    }
+    *fraction = total > 0 ? done / total : 0.0;
+    return GAMER_OK;
+}
+
+// Rasterizer::Abort (rasterizer.h:91-98): blocks that have not started skip their pixels. Any thread.
+int gamer_b200_abort(gamer_ctx *ctx) {
+    if (!ctx) return GAMER_E_ARG;
+    if (!ctx->rendering.load()) return GAMER_OK;
+    ctx->abort_req.store(1);
+    static const int one = 1;
+    for (Dev &d : ctx->devs) {
+        if (cudaSetDevice(d.device) != cudaSuccess) continue;
+        cudaMemcpyAsync(d.abort_flag, &one, sizeof(int), cudaMemcpyHostToDevice, d.ctrl);
+        cudaStreamSynchronize(d.ctrl);
+    }
+    return GAMER_OK;
+}
+
+int gamer_b200_device_buffers(gamer_ctx *ctx, int32_t which, void **rgb_dev, void **argb_dev, void **argb_shadow_dev,
+                              int32_t *rows_out) {
+    if (!ctx || which < 0 || which >= (int)ctx->devs.size()) return GAMER_E_ARG;
+    Dev &d = ctx->devs[which];
+    if (rgb_dev) *rgb_dev = d.rgb;
+    if (argb_dev) *argb_dev = d.argb;
+    if (argb_shadow_dev) *argb_shadow_dev = d.shadow;
+    if (rows_out) *rows_out = d.rows;
+    return GAMER_OK;
+}
+
+int gamer_b200_last_kernel_ms(gamer_ctx *ctx, float *k1_ms, float *k2_ms) {
+    if (!ctx) return GAMER_E_ARG;
+    if (k1_ms) *k1_ms = ctx->k1_ms;
+    if (k2_ms) *k2_ms = ctx->k2_ms;
+    return GAMER_OK;
+}
+
+int gamer_b200_launch_count(gamer_ctx *ctx, uint64_t *launches) {
+    if (!ctx || !launches) return GAMER_E_ARG;
+    *launches = ctx->launches;
+    return GAMER_OK;
+}
+
+int gamer_b200_host_alloc(void **ptr, uint64_t bytes) {
+    if (!ptr) return GAMER_E_ARG;
+    cudaError_t e = cudaHostAlloc(ptr, bytes, cudaHostAllocDefault);
+    if (e != cudaSuccess) { *ptr = nullptr; return cuda_fail(nullptr, e, "cudaHostAlloc"); }
+    return GAMER_OK;
+}
+int gamer_b200_host_free(void *ptr) {
+    if (!ptr) return GAMER_OK;
+    return cudaFreeHost(ptr) == cudaSuccess ? GAMER_OK : GAMER_E_CUDA;
+}
+
+// ---- probes ------------------------------------------------------------------------------------
+static int probe_io(gamer_ctx *ctx, const float *xyz, int32_t n, float **xyz_dev, float **val_dev) {
+    Dev &d = ctx->devs[0];
+    CK(cudaSetDevice(d.device));
+    CK(cudaMalloc(xyz_dev, (size_t)n * 3 * sizeof(float)));
+    CK(cudaMalloc(val_dev, (size_t)n * sizeof(float)));
+    CK(cudaMemcpyAsync(*xyz_dev, xyz, (size_t)n * 3 * sizeof(float), cudaMemcpyHostToDevice, d.st));
+    return GAMER_OK;
+}
+
+int gamer_b200_probe_simplex(gamer_ctx *ctx, const float *xyz, int32_t n, double frequency, int32_t *lattice_out, float *value_out) {
+    if (!ctx || !xyz || n <= 0) return GAMER_E_ARG;
+    std::lock_guard<std::mutex> lock(ctx->mu);
+    Dev &d = ctx->devs[0];
+    float *xd = nullptr, *vd = nullptr;
+    int32_t *ld = nullptr;
+    int rc = probe_io(ctx, xyz, n, &xd, &vd);
+    if (rc) return rc;
+    CK(cudaMalloc(&ld, (size_t)n * 10 * sizeof(int32_t)));
+    CK(gk::launch_probe_simplex(xd, n, frequency, ld, vd, d.st));
+    ctx->launches += 1;
+    if (value_out) CK(cudaMemcpyAsync(value_out, vd, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, d.st));
+    if (lattice_out) CK(cudaMemcpyAsync(lattice_out, ld, (size_t)n * 10 * sizeof(int32_t), cudaMemcpyDeviceToHost, d.st));
+    CK(cudaStreamSynchronize(d.st));
+    cudaFree(xd); cudaFree(vd); cudaFree(ld);
+    return GAMER_OK;
+}
+
+int gamer_b200_probe_fbm(gamer_ctx *ctx, const float *xyz, int32_t n, int32_t octaves, double persistence, double scale, float *value_out) {
+    if (!ctx || !xyz || !value_out || n <= 0 || octaves <= 0 || octaves > 32) return GAMER_E_ARG;
+    std::lock_guard<std::mutex> lock(ctx->mu);
+    Dev &d = ctx->devs[0];
+    float *xd = nullptr, *vd = nullptr;
+    int rc = probe_io(ctx, xyz, n, &xd, &vd);
+    if (rc) return rc;
+    double amp = 1, maxamp = 0;
+    for (int o = 0; o < octaves; o++) { maxamp += amp; amp *= persistence; }
+    CK(gk::launch_probe_fbm(xd, n, octaves, (float)persistence, (float)(1.0 / maxamp), scale, vd, d.st));
+    ctx->launches += 1;
+    CK(cudaMemcpyAsync(value_out, vd, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, d.st));
+    CK(cudaStreamSynchronize(d.st));
+    cudaFree(xd); cudaFree(vd);
+    return GAMER_OK;
+}
+
+int gamer_b200_probe_ridged(gamer_ctx *ctx, const float *xyz, int32_t n, double frequency, int32_t octaves, double lacunarity,
+                            double offset, double gain, float *value_out) {
+    if (!ctx || !xyz || !value_out || n <= 0 || octaves <= 0 || octaves > 16) return GAMER_E_ARG;
+    std::lock_guard<std::mutex> lock(ctx->mu);
+    Dev &d = ctx->devs[0];
+    float *xd = nullptr, *vd = nullptr;
+    int rc = probe_io(ctx, xyz, n, &xd, &vd);
+    if (rc) return rc;
+    float rw[16];
+    const double w = -0.05f;
+    for (int o = 0; o < octaves; o++) { rw[o] = (float)pow(frequency, w); frequency *= lacunarity; }
+    CK(gk::launch_probe_ridged(xd, n, octaves, (float)lacunarity, (float)offset, (float)gain, rw, vd, d.st));
+    ctx->launches += 1;
+    CK(cudaMemcpyAsync(value_out, vd, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, d.st));
+    CK(cudaStreamSynchronize(d.st));
+    cudaFree(xd); cudaFree(vd);
+    return GAMER_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,411 @@
+// kernels.cu — K1 (ray march), K2 (post-process) and the noise probes, plus their launchers.
+// sm_100a only.  See march.cuh / noise.cuh for the design notes and the reference citations.
+#include "march.cuh"
+#include "kernels.h"
+
+using namespace gmarch;
+
+namespace {
+
+#define K1_THREADS 256   // 8 warps: 4 x 2 tiles of 8 x 4 pixels = a 32 x 8 pixel block
+#define K1_BW 32
+#define K1_BH 8
+
+struct NoiseCtx {
+    const char *tbl;
+    uint32_t lane4;
+};
+
+struct Shared1 {          // values of one sample shared by every component of a galaxy
+    f3 p;                 // sample position (exact)
+    f3 P;                 // in-plane part (exact)
+    float dott;           // height above the plane along the axis (exact)
+    float Plen;           // |P| fast float
+    float plen3;          // |p| fast float
+    float weight;         // step * 200
+    bool have_arm;        // lazily computed per sample
+    float W;              // getWinding(radius)
+    float theta0;         // atan2(q.x, q.z), q = rotmat * P
+};
+
+// getWinding (galaxycomponent.h:156-165) and the atan2 of getTheta (:150-153), once per sample
+__device__ __forceinline__ void arm_base(const DGalaxy &g, Shared1 &s) {
+    if (s.have_arm) return;
+    float radius = s.Plen * g.inv_axis_x;
+    float r = radius + 0.05f;
+    s.W = atanf(fexp(-0.5f / r) * g.inv_winding_b) * g.winding_2n;   // -0.25/(0.5*r)
+    f3 q = g.rot_identity ? s.P : q_rotate(g.rot, s.P);
+    s.theta0 = atan2f(q.x, q.z);
+    s.have_arm = true;
+}
+
+// findDifference (galaxycomponent.h:103-118) with M_PI = 3.14159265 (util.h:20)
+__device__ __forceinline__ float find_difference(float d) {
+    const float TP = 6.2831853f, FP = 12.5663706f;
+    float v = fminf(fabsf(d), fabsf(d - TP));
+    v = fminf(v, fabsf(d + TP));
+    v = fminf(v, fabsf(d - FP));
+    v = fminf(v, fabsf(d + FP));
+    return v;
+}
+
+// calculateArmValue (galaxycomponent.h:120-146). max_j pow(1 - v_j/pi, e) = pow(1 - min_j v_j/pi, e) for e > 0.
+__device__ __forceinline__ float arm_value(const DGalaxy &g, const DComp &c, const Shared1 &s) {
+    float base = s.W + s.theta0 + c.delta;    // winding - (-(theta) + disp) = W + theta + delta - disp
+    float v = find_difference(base - g.arm[0]);
+    bool want_min = c.arm15 > 0.0f;
+    for (int j = 1; j < g.no_arms; j++) {
+        float vj = find_difference(base - g.arm[j]);
+        v = want_min ? fminf(v, vj) : fmaxf(v, vj);
+    }
+    float b = fmaxf(1.0f - v * (1.0f / 3.14159265f), 0.0f);   // a negative base is NaN in the reference and contributes nothing
+    return fpow(b, c.arm15);
+}
+
+template <bool COUNT>
+__device__ __forceinline__ void eval_component(const DScene &sc, const DGalaxy &g, const DComp &c, Shared1 &s,
+                                               const NoiseCtx &nz, float &Ir, float &Ig, float &Ib, Counts &cn) {
+    const float rs = sc.ray_step_f;
+    if (c.cls == GAMER_CLASS_BULGE) {   // galaxycomponents.cpp:5-25 — evaluated at every sample, no gates
+        float rad = fmaf(s.plen3 + 0.01f, c.r0, 0.01f);
+        float L = lg2(rad);
+        float i = c.strength * s.weight * (ex2(-0.855f * L) * fexp(-ex2(0.25f * L)) - 0.05f) * c.iscale;
+        i = fmaxf(i, 0.0f) * rs;
+        Ir = fmaf(i, c.spec[0], Ir); Ig = fmaf(i, c.spec[1], Ig); Ib = fmaf(i, c.spec[2], Ib);
+        if (COUNT) cn.evals++;
+        return;
+    }
+    // ---- slab gate: h = |dott/z0| > 2 -> 0 (galaxycomponent.h:61-64), exact --------------------
+    float ad = fabsf(s.dott);
+    if (!(ad <= c.h_gate)) return;
+    float e = fexp(ad * c.inv_z0);
+    float ch = 0.5f * (e + __frcp_rn(e));
+    float z = __frcp_rn(ch * ch);
+    if (!(z > 0.01f)) return;
+    // ---- radial gate: intensity > 0.001 (galaxycomponent.cpp:62-65), exact -----------------------
+    bool pass;
+    if (s.Plen < c.plen_lo) pass = true;
+    else if (s.Plen > c.plen_hi) pass = false;
+    else pass = v_length(s.P) <= c.plen_thr;
+    if (!pass) return;
+    float intensity = fminf(fmaxf(ex2(s.Plen * c.k_radial) - 0.01f, 0.0f), 0.1f);
+    float scale = 1.0f;
+    if (!(c.flags & DC_INNER_ZERO)) {
+        float x = fminf(fmaxf(s.Plen * g.inv_axis_x * c.inv_inner, 0.0f), 1.0f);
+        float sm = x * x * (3.0f - 2.0f * x);
+        sm *= sm;
+        scale = sm * sm;
+    }
+    float armv = 1.0f, winding = 0.0f;
+    if (c.flags & DC_HAS_ARM) {
+        arm_base(g, s);
+        armv = arm_value(g, c, s);
+        if (c.flags & DC_HAS_WINDING) winding = s.W * c.winding;
+    }
+    float val = c.strength * scale * armv * z * intensity;
+    float ival = val * s.weight;
+    if (!(ival > 0.0005f)) return;
+    if (COUNT) cn.evals++;
+
+    switch (c.cls) {
+    case GAMER_CLASS_DISK: {            // galaxycomponents.cpp:41-59
+        f3 r = twirl(g.axis_n, s.p, winding);
+        float n = gnoise::fbm(nz.tbl, nz.lane4, r.x, r.y, r.z, c.nscale, 10, c.pers, c.inv_maxamp);
+        if (COUNT) cn.octaves += 10;
+        float p2 = fpow(fmaxf(fabsf(n), 0.01f), c.noise_tilt) + c.noise_offset;
+        if (p2 < 0.0f) return;
+        float k = ival * p2 * rs;
+        Ir = fmaf(k, c.spec[0], Ir); Ig = fmaf(k, c.spec[1], Ig); Ib = fmaf(k, c.spec[2], Ib);
+        break;
+    }
+    case GAMER_CLASS_DUST: {            // galaxycomponents.cpp:64-84
+        f3 r = twirl(g.axis_n, s.p, winding);
+        float n = gnoise::fbm(nz.tbl, nz.lane4, r.x, r.y, r.z, c.nscale, 9, c.pers, c.inv_maxamp);
+        if (COUNT) cn.octaves += 9;
+        float p2 = fmaxf(n - c.noise_offset, 0.0f);
+        p2 = (p2 > 0.0f) ? fpow(5.0f * p2, c.noise_tilt) : (c.noise_tilt > 0.0f ? 0.0f : (c.noise_tilt == 0.0f ? 1.0f : 10.0f));
+        p2 = fminf(fmaxf(p2, -10.0f), 10.0f);
+        float k = -p2 * ival * 0.01f;
+        Ir *= fexp(k * c.spec[0]); Ig *= fexp(k * c.spec[1]); Ib *= fexp(k * c.spec[2]);
+        break;
+    }
+    case GAMER_CLASS_DUST2:             // galaxycomponents.cpp:85-114
+    case GAMER_CLASS_DUST_POSITIVE: {   // galaxycomponents.cpp:116-136
+        f3 r = twirl(g.axis_n, s.p, winding);
+        float p2 = gnoise::ridged(nz.tbl, nz.lane4, __fmul_rn(r.x, c.rscale), __fmul_rn(r.y, c.rscale),
+                                  __fmul_rn(r.z, c.rscale), DEV_RIDGED_OCTAVES, 2.5f, c.noise_offset, c.noise_tilt, c.rw);
+        if (COUNT) cn.octaves += DEV_RIDGED_OCTAVES;
+        p2 = fmaxf(p2, 0.0f);
+        if (c.cls == GAMER_CLASS_DUST2) {
+            float k = -p2 * ival * 0.01f;
+            Ir *= fexp(k * c.spec[0]); Ig *= fexp(k * c.spec[1]); Ib *= fexp(k * c.spec[2]);
+        } else {
+            float k = ival * p2 * rs;
+            Ir = fmaf(k, c.spec[0], Ir); Ig = fmaf(k, c.spec[1], Ig); Ib = fmaf(k, c.spec[2], Ib);
+        }
+        break;
+    }
+    case GAMER_CLASS_STARS: {           // galaxycomponents.cpp:139-155
+        float n = fabsf(gnoise::fbm(nz.tbl, nz.lane4, s.p.x, s.p.y, s.p.z, c.nscale, 10, c.pers, c.inv_maxamp));
+        if (COUNT) cn.octaves += 10;
+        float add = 0.0f;
+        if (c.flags & DC_HAS_NOFF) {    // two 4-octave helpers, persistence -2: amplitudes 1,-2,4,-8, sum -5
+            f3 r1 = twirl(g.axis_n, s.p, winding);
+            f3 r2 = twirl(g.axis_n, s.p, winding * 0.5f);
+            add = c.noise_offset * gnoise::fbm(nz.tbl, nz.lane4, r1.x, r1.y, r1.z, 2.0 * (double)0.1f, 4, -2.0f, -0.2f);
+            add += 0.5f * (c.noise_offset * gnoise::fbm(nz.tbl, nz.lane4, r2.x, r2.y, r2.z, 4.0 * (double)0.1f, 4, -2.0f, -0.2f));
+            if (COUNT) cn.octaves += 8;
+        }
+        float base = n + 1.0f + add;
+        float val2;
+        if (base >= 0.0f) val2 = fpow(base, c.noise_tilt);
+        else if (c.flags & DC_TILT_INT) val2 = fpow(-base, c.noise_tilt);        // |pow(neg, int)|
+        else { Ir = Ig = Ib = 0.0f; return; }   // pow -> NaN poisons I; Util::floor's fmax(0,NaN) then zeroes it
+        float k = ival * val2 * rs;
+        Ir = fmaf(k, c.spec[0], Ir); Ig = fmaf(k, c.spec[1], Ig); Ib = fmaf(k, c.spec[2], Ib);
+        break;
+    }
+    default: break;                      // "stars small": no-op (see gamer_b200.h)
+    }
+}
+
+// Rasterizer::getIntensity (rasterizer.cpp:422-483) for one galaxy
+template <bool COUNT>
+__device__ __forceinline__ void march(const DScene &sc, const DGalaxy &g, f3 isp1, f3 isp2, f3 camrel,
+                                      const NoiseCtx &nz, float &Ir, float &Ig, float &Ib, Counts &cn) {
+    const f3 origin = isp1;
+    const f3 dseg = v_sub(isp1, isp2);
+    const double length = (double)v_length(dseg);
+    const f3 dir = v_normalized(dseg);
+    const f3 ll = v_normalized(v_sub(isp2, origin));
+    const f3 orient = {g.orient[0], g.orient[1], g.orient[2]};
+    const float step_hi = 0.01f * 1.00001f, step_lo = (float)sc.min_ray_step * 0.99999f;
+    double step = sc.ray_step;
+    f3 p = origin;
+    if (COUNT) cn.rays++;
+    while ((double)v_dot(v_sub(p, origin), ll) < __dadd_rn(length, step)) {
+        // step = clamp(|p - camera| * rayStep, minRayStep, 0.01)   (rasterizer.cpp:449)
+        f3 dc = v_sub(p, camrel);
+        float est = sqrtf(fmaf(dc.z, dc.z, fmaf(dc.y, dc.y, dc.x * dc.x))) * sc.ray_step_f;
+        if (est > step_hi) step = 0.01;
+        else if (est < step_lo) step = sc.min_ray_step;
+        else {
+            double v = __dmul_rn((double)v_length(dc), sc.ray_step);
+            v = (v < 0.01) ? v : 0.01;
+            step = (sc.min_ray_step < v) ? v : sc.min_ray_step;
+        }
+        Shared1 s;
+        s.p = p;
+        s.dott = v_dot(p, orient);                       // getRadius (galaxycomponent.h:72-76)
+        s.P = v_sub(p, v_mul(orient, s.dott));
+        s.Plen = sqrtf(fmaf(s.P.z, s.P.z, fmaf(s.P.y, s.P.y, s.P.x * s.P.x)));
+        s.plen3 = sqrtf(fmaf(p.z, p.z, fmaf(p.y, p.y, p.x * p.x)));
+        s.weight = (float)(step * 200.0);
+        s.have_arm = false;
+#pragma unroll 1
+        for (int k = 0; k < g.comp_count; k++)
+            eval_component<COUNT>(sc, g, sc.comp[g.comp_begin + k], s, nz, Ir, Ig, Ib, cn);
+        if (COUNT) { cn.samples++; cn.gates += g.comp_count; }
+        p = v_sub(p, v_mul(dir, __double2float_rn(step)));
+        Ir = fmaxf(0.0f, Ir); Ig = fmaxf(0.0f, Ig); Ib = fmaxf(0.0f, Ib);   // Util::floor (util.h:62-64)
+    }
+}
+
+__device__ __forceinline__ int image_row(const DScene &sc, int L) {
+    if (sc.band_rows > 0) return sc.y0 + (L / sc.band_rows) * sc.band_stride + (L % sc.band_rows);
+    return sc.y0 + L;
+}
+
+template <bool COUNT>
+__global__ void __launch_bounds__(K1_THREADS)
+k1_march(const __grid_constant__ DScene sc, float *__restrict__ out, unsigned long long *__restrict__ counters,
+         const volatile int *abort_flag, unsigned int *progress) {
+    __shared__ __align__(128) uint32_t s_tbl[GN_TABLE_WORDS];
+    gnoise::table_init(s_tbl);
+    __syncthreads();
+    if (*abort_flag) return;            // rasterizer.cpp:296-297: skipped pixels keep their old value
+
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int lx = blockIdx.x * K1_BW + (warp & 3) * 8 + (lane & 7);
+    const int ly = blockIdx.y * K1_BH + (warp >> 2) * 4 + (lane >> 3);
+    NoiseCtx nz;
+    nz.tbl = reinterpret_cast<const char *>(s_tbl);
+    nz.lane4 = (uint32_t)lane << 2;
+    Counts cn = {0, 0, 0, 0, 0};
+
+    if (lx < sc.width && ly < sc.height) {
+        // ---- GamerCamera::coord2ray (gamercamera.cpp:210-217) --------------------------------
+        const int i = sc.x0 + lx, j = image_row(sc, ly);
+        const double half = __dmul_rn((double)sc.full_size, 0.5);
+        const float v0 = __double2float_rn(__dsub_rn(__ddiv_rn((double)i, half), 1.0));
+        const float v1 = __double2float_rn(-__dsub_rn(__ddiv_rn((double)j, half), 1.0));
+        f3 w;
+        {
+            const float *m = sc.inv_vp;
+            w.x = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(v0, m[0]), __fmul_rn(v1, m[1])), m[2]), m[3]);
+            w.y = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(v0, m[4]), __fmul_rn(v1, m[5])), m[6]), m[7]);
+            w.z = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(v0, m[8]), __fmul_rn(v1, m[9])), m[10]), m[11]);
+        }
+        const f3 d = v_normalized(w);
+        float Ir = 0.f, Ig = 0.f, Ib = 0.f;
+        // ---- Rasterizer::renderPixel (rasterizer.cpp:379-416) --------------------------------
+        for (int gi = 0; gi < sc.n_galaxies; gi++) {
+            const DGalaxy &g = sc.gal[gi];
+            const f3 o = v_sub({sc.cam[0], sc.cam[1], sc.cam[2]}, {g.pos[0], g.pos[1], g.pos[2]});
+            // Util::IntersectSphere (util.h:66-98)
+            const f3 rD = {__fmul_rn(d.x, g.inv_axis2[0]), __fmul_rn(d.y, g.inv_axis2[1]), __fmul_rn(d.z, g.inv_axis2[2])};
+            const f3 rO = {__fmul_rn(o.x, g.inv_axis2[0]), __fmul_rn(o.y, g.inv_axis2[1]), __fmul_rn(o.z, g.inv_axis2[2])};
+            const double A = (double)v_dot(d, rD);
+            const double B = __dmul_rn(2.0, (double)v_dot(d, rO));
+            const double C = __dsub_rn((double)v_dot(o, rO), 1.0);
+            const double S = __dsub_rn(__dmul_rn(B, B), __dmul_rn(__dmul_rn(4.0, A), C));
+            if (S <= 0.0) continue;
+            const double sq = __dsqrt_rn(S), twoA = __dmul_rn(2.0, A);
+            const double t0 = __ddiv_rn(__dsub_rn(-B, sq), twoA);
+            const double t1 = __ddiv_rn(__dadd_rn(-B, sq), twoA);
+            f3 isp1 = v_add(o, v_mul(d, __double2float_rn(t0)));
+            f3 isp2 = v_add(o, v_mul(d, __double2float_rn(t1)));
+            if (t1 > 0.0) isp2 = o;
+            if (t0 > 0.0 && t1 > 0.0) continue;
+            march<COUNT>(sc, g, isp1, isp2, o, nz, Ir, Ig, Ib, cn);
+        }
+        // rp.I * 0.01 / rayStep  (rasterizer.cpp:409): QVector3D*float then QVector3D/float
+        float *dst = out + 3 * ((size_t)ly * sc.width + lx);
+        dst[0] = __fdiv_rn(__fmul_rn(Ir, sc.final_mul), sc.ray_step_f);
+        dst[1] = __fdiv_rn(__fmul_rn(Ig, sc.final_mul), sc.ray_step_f);
+        dst[2] = __fdiv_rn(__fmul_rn(Ib, sc.final_mul), sc.ray_step_f);
+    }
+    if (COUNT) {
+        unsigned long long v[5] = {cn.rays, cn.samples, cn.gates, cn.evals, cn.octaves};
+#pragma unroll
+        for (int q = 0; q < 5; q++) {
+            unsigned long long x = v[q];
+            for (int off = 16; off > 0; off >>= 1) x += __shfl_down_sync(0xffffffffu, x, off);
+            if (lane == 0 && x) atomicAdd(&counters[q], x);
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) atomicAdd(progress, 1u);
+}
+
+// ---- K2: Buffer2D::PostProcess + ToColorBuffer (buffer2d.cpp:65-85,106-126) -------------------------
+// HBM-bound: 12 B (+12 B stars) read, 8 B written per pixel. pow is evaluated in double like the
+// reference (3 per pixel; the kernel stays memory-bound).
+__global__ void __launch_bounds__(256)
+k2_tonemap(const float *__restrict__ rgb, const float *__restrict__ stars, uint32_t *__restrict__ argb,
+           uint32_t *__restrict__ shadow, size_t n, double inv_exposure_d, double gamma, double saturation) {
+    const float inv_exposure = (float)inv_exposure_d;
+    for (size_t k = blockIdx.x * (size_t)blockDim.x + threadIdx.x; k < n; k += (size_t)gridDim.x * blockDim.x) {
+        float x = rgb[3 * k], y = rgb[3 * k + 1], z = rgb[3 * k + 2];
+        if (stars) { x = __fadd_rn(x, stars[3 * k]); y = __fadd_rn(y, stars[3 * k + 1]); z = __fadd_rn(z, stars[3 * k + 2]); }
+        x = __fmul_rn(x, inv_exposure); y = __fmul_rn(y, inv_exposure); z = __fmul_rn(z, inv_exposure);
+        if (gamma != 1.0) { x = (float)pow((double)x, gamma); y = (float)pow((double)y, gamma); z = (float)pow((double)z, gamma); }
+        double center = (double)__fadd_rn(__fadd_rn(x, y), z) / 3.0;
+        float tx = (float)(center - x), ty = (float)(center - y), tz = (float)(center - z);
+        x = (float)__dsub_rn(center, __dmul_rn(saturation, (double)tx));
+        y = (float)__dsub_rn(center, __dmul_rn(saturation, (double)ty));
+        z = (float)__dsub_rn(center, __dmul_rn(saturation, (double)tz));
+        x = __fmul_rn(x, 10.0f); y = __fmul_rn(y, 10.0f); z = __fmul_rn(z, 10.0f);
+        // Util::clamp: std::min(255, v) then std::max(0, v) — NaN becomes 255
+        x = (x < 255.0f) ? x : 255.0f; x = (0.0f < x) ? x : 0.0f;
+        y = (y < 255.0f) ? y : 255.0f; y = (0.0f < y) ? y : 0.0f;
+        z = (z < 255.0f) ? z : 255.0f; z = (0.0f < z) ? z : 0.0f;
+        uint32_t r = (uint32_t)(int)x, g = (uint32_t)(int)y, b = (uint32_t)(int)z;
+        if (argb)   argb[k]   = 0xFF000000u | (b << 16) | (g << 8) | r;
+        if (shadow) shadow[k] = 0xFF000000u | (r << 16) | (g << 8) | b;
+    }
+}
+
+// ---- probes: the same device noise functions, one point per thread ----------------------------------
+__global__ void __launch_bounds__(256)
+kp_simplex(const float *__restrict__ xyz, int n, double frequency, int32_t *__restrict__ lat_out, float *__restrict__ val_out) {
+    __shared__ __align__(128) uint32_t s_tbl[GN_TABLE_WORDS];
+    gnoise::table_init(s_tbl);
+    __syncthreads();
+    int q = blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= n) return;
+    const char *tbl = reinterpret_cast<const char *>(s_tbl);
+    uint32_t lane4 = (threadIdx.x & 31) << 2;
+    gnoise::Skewed su, sv, sw;
+    gnoise::skew(__dmul_rn((double)xyz[3 * q], frequency), __dmul_rn((double)xyz[3 * q + 1], frequency),
+                 __dmul_rn((double)xyz[3 * q + 2], frequency), su, sv, sw);
+    gnoise::Lattice L;
+    float fu, fv, fw;
+    gnoise::cell_of(su, 0, L.i, fu);
+    gnoise::cell_of(sv, 0, L.j, fv);
+    gnoise::cell_of(sw, 0, L.k, fw);
+    float v = gnoise::simplex_cell<true>(tbl, lane4, L.i, L.j, L.k, fu, fv, fw, &L);
+    if (val_out) val_out[q] = v;
+    if (lat_out) {
+        int32_t *o = lat_out + 10 * (size_t)q;
+        o[0] = L.i; o[1] = L.j; o[2] = L.k; o[3] = L.c1; o[4] = L.c2;
+        o[5] = L.g0; o[6] = L.g1; o[7] = L.g2; o[8] = L.g3; o[9] = 0;
+    }
+}
+
+__global__ void __launch_bounds__(256)
+kp_fbm(const float *__restrict__ xyz, int n, int octaves, float pers, float inv_maxamp, double scale, float *__restrict__ out) {
+    __shared__ __align__(128) uint32_t s_tbl[GN_TABLE_WORDS];
+    gnoise::table_init(s_tbl);
+    __syncthreads();
+    int q = blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= n) return;
+    out[q] = gnoise::fbm(reinterpret_cast<const char *>(s_tbl), (threadIdx.x & 31) << 2, xyz[3 * q], xyz[3 * q + 1],
+                         xyz[3 * q + 2], scale, octaves, pers, inv_maxamp);
+}
+
+struct RidgedW { float w[16]; };
+__global__ void __launch_bounds__(256)
+kp_ridged(const float *__restrict__ xyz, int n, int octaves, float lac, float offset, float gain, RidgedW rw,
+          float *__restrict__ out) {
+    __shared__ __align__(128) uint32_t s_tbl[GN_TABLE_WORDS];
+    gnoise::table_init(s_tbl);
+    __syncthreads();
+    int q = blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= n) return;
+    out[q] = gnoise::ridged(reinterpret_cast<const char *>(s_tbl), (threadIdx.x & 31) << 2, xyz[3 * q], xyz[3 * q + 1],
+                            xyz[3 * q + 2], octaves, lac, offset, gain, rw.w);
+}
+
+}  // namespace
+
+// ---- launchers (host) -----------------------------------------------------------------------------
+namespace gk {
+
+cudaError_t launch_k1(const DScene &sc, float *out_dev, unsigned long long *counters_dev, const int *abort_dev,
+                      unsigned int *progress_dev, bool counted, cudaStream_t st, unsigned int *n_blocks) {
+    dim3 grid((sc.width + K1_BW - 1) / K1_BW, (sc.height + K1_BH - 1) / K1_BH);
+    if (n_blocks) *n_blocks = grid.x * grid.y;
+    if (counted) k1_march<true><<<grid, K1_THREADS, 0, st>>>(sc, out_dev, counters_dev, abort_dev, progress_dev);
+    else         k1_march<false><<<grid, K1_THREADS, 0, st>>>(sc, out_dev, counters_dev, abort_dev, progress_dev);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_k2(const float *rgb, const float *stars, uint32_t *argb, uint32_t *shadow, size_t n, double exposure,
+                      double gamma, double saturation, int sm_count, cudaStream_t st) {
+    size_t want = (n + 255) / 256;
+    size_t cap = (size_t)sm_count * 8;          // 8 resident CTAs of 256 threads per SM, grid-stride
+    int blocks = (int)(want < cap ? want : cap);
+    if (blocks < 1) blocks = 1;
+    k2_tonemap<<<blocks, 256, 0, st>>>(rgb, stars, argb, shadow, n, 1.0 / exposure, gamma, saturation);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_probe_simplex(const float *xyz, int n, double frequency, int32_t *lat, float *val, cudaStream_t st) {
+    kp_simplex<<<(n + 255) / 256, 256, 0, st>>>(xyz, n, frequency, lat, val);
+    return cudaGetLastError();
+}
+cudaError_t launch_probe_fbm(const float *xyz, int n, int octaves, float pers, float inv_maxamp, double scale, float *out,
+                             cudaStream_t st) {
+    kp_fbm<<<(n + 255) / 256, 256, 0, st>>>(xyz, n, octaves, pers, inv_maxamp, scale, out);
+    return cudaGetLastError();
+}
+cudaError_t launch_probe_ridged(const float *xyz, int n, int octaves, float lac, float offset, float gain, const float *rw,
+                                float *out, cudaStream_t st) {
+    RidgedW w;
+    for (int i = 0; i < 16; i++) w.w[i] = (i < octaves) ? rw[i] : 0.f;
+    kp_ridged<<<(n + 255) / 256, 256, 0, st>>>(xyz, n, octaves, lac, offset, gain, w, out);
+    return cudaGetLastError();
+}
+
+}  // namespace gk

@@ -1,0 +1,17 @@
+// kernels.h — host-callable launchers of the sm_100a kernels (kernels.cu).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "scene_dev.h"
+
+namespace gk {
+cudaError_t launch_k1(const DScene &sc, float *out_dev, unsigned long long *counters_dev, const int *abort_dev,
+                      unsigned int *progress_dev, bool counted, cudaStream_t st, unsigned int *n_blocks);
+cudaError_t launch_k2(const float *rgb, const float *stars, uint32_t *argb, uint32_t *shadow, size_t n, double exposure,
+                      double gamma, double saturation, int sm_count, cudaStream_t st);
+cudaError_t launch_probe_simplex(const float *xyz, int n, double frequency, int32_t *lat, float *val, cudaStream_t st);
+cudaError_t launch_probe_fbm(const float *xyz, int n, int octaves, float pers, float inv_maxamp, double scale, float *out,
+                             cudaStream_t st);
+cudaError_t launch_probe_ridged(const float *xyz, int n, int octaves, float lac, float offset, float gain, const float *rw,
+                                float *out, cudaStream_t st);
+}  // namespace gk

@@ -1,0 +1,215 @@
+// noise.cuh — 3-D simplex noise, fBm and ridged multifractal for sm_100a.
+//
+// Replaces source/noise/simplexnoise.cpp:243-333 (raw_noise_3d), noise.cpp:162-180
+// (Noise::octave_noise_3d) and noise.cpp:81-128 (Noise::getRidgedMf).
+//
+// Design (not a translation of the reference's double-precision table walk):
+//  * Lattice selection is integer work on a 32.32 fixed-point image of the SKEWED coordinate
+//    u = x + (x+y+z)/3.  u is formed once per fBm call in FP64 with exactly the reference's
+//    operations, so floor() agrees with the CPU renderer bit for bit; because every octave doubles
+//    the frequency and scaling by 2 commutes with IEEE rounding, octave k's skewed coordinate is
+//    exactly 2^k * u — a 64-bit left shift.  Integer cell = high word, in-cell offset = low word.
+//  * In-cell offsets are the fractional parts (fu,fv,fw) in [0,1); the unskewed corner vectors
+//    follow from x0 = fu - (fu+fv+fw)/6, all FP32 on small numbers, so FP32 loses nothing even at
+//    coordinates ~1e5 where a float product would have no fractional bits left.
+//  * The permutation table lives in shared memory replicated once per bank (256 entries x 32
+//    lanes x 4 B = 32 KB): lane l only ever reads bank l, so the data-dependent hash walk is
+//    bank-conflict free.  An entry is (perm[e] << 7) | gradient code of (perm[e] % 12), i.e. the
+//    value is already the byte offset of the next lookup: one IADD + one LOP3 + one LDS per level.
+//  * The reference's fastfloor quirk (simplexnoise.h:130: exact non-positive integers floor one
+//    too low) is reproduced on a rare path.
+#pragma once
+#include <stdint.h>
+
+namespace gnoise {
+
+// Ken Perlin's permutation, as in simplexnoise.h:160-185 (first 256 entries; the second copy is &255).
+__constant__ uint8_t c_perm[256] = {
+    151, 160, 137, 91,  90,  15,  131, 13,  201, 95,  96,  53,  194, 233, 7,   225, 140, 36,  103, 30,
+    69,  142, 8,   99,  37,  240, 21,  10,  23,  190, 6,   148, 247, 120, 234, 75,  0,   26,  197, 62,
+    94,  252, 219, 203, 117, 35,  11,  32,  57,  177, 33,  88,  237, 149, 56,  87,  174, 20,  125, 136,
+    171, 168, 68,  175, 74,  165, 71,  134, 139, 48,  27,  166, 77,  146, 158, 231, 83,  111, 229, 122,
+    60,  211, 133, 230, 220, 105, 92,  41,  55,  46,  245, 40,  244, 102, 143, 54,  65,  25,  63,  161,
+    1,   216, 80,  73,  209, 76,  132, 187, 208, 89,  18,  169, 200, 196, 135, 130, 116, 188, 159, 86,
+    164, 100, 109, 198, 173, 186, 3,   64,  52,  217, 226, 250, 124, 123, 5,   202, 38,  147, 118, 126,
+    255, 82,  85,  212, 207, 206, 59,  227, 47,  16,  58,  17,  182, 189, 28,  42,  223, 183, 170, 213,
+    119, 248, 152, 2,   44,  154, 163, 70,  221, 153, 101, 155, 167, 43,  172, 9,   129, 22,  39,  253,
+    19,  98,  108, 110, 79,  113, 224, 232, 178, 185, 112, 104, 218, 246, 97,  228, 251, 34,  242, 193,
+    238, 210, 144, 12,  191, 179, 162, 241, 81,  51,  145, 235, 249, 14,  239, 107, 49,  192, 214, 31,
+    181, 199, 106, 157, 184, 84,  204, 176, 115, 121, 50,  45,  127, 4,   150, 254, 138, 236, 205, 93,
+    222, 114, 67,  29,  24,  72,  243, 141, 128, 195, 78,  66,  215, 61,  156, 180};
+
+// Gradient code of g = perm % 12 for grad3 (simplexnoise.h:142-146): dot(grad3[g], (x,y,z)) = ±a ± b with
+//   g<4: (a,b)=(x,y)   4<=g<8: (x,z)   g>=8: (y,z);  sign(a) = g&1, sign(b) = (g>>1)&1.
+// Bit 31 = sign of a, bit 30 = sign of b, bit 0 = "a is y", bit 1 = "b is y"; bits 2..5 = g itself.
+__host__ __device__ inline uint32_t grad_code(uint32_t g) {
+    uint32_t code = (g << 2);
+    if (g & 1) code |= 0x80000000u;
+    if (g & 2) code |= 0x40000000u;
+    if (g >= 8) code |= 1u;
+    if (g < 4) code |= 2u;
+    return code;
+}
+
+#define GN_TABLE_WORDS (256 * 32)
+#define GN_ADDR_MASK 0x7F80u
+
+// Fill the replicated table; call from all threads of the block, then __syncthreads().
+__device__ __forceinline__ void table_init(uint32_t *tbl) {
+    for (uint32_t w = threadIdx.x + threadIdx.y * blockDim.x; w < GN_TABLE_WORDS; w += blockDim.x * blockDim.y) {
+        uint32_t e = w >> 5;
+        uint32_t p = c_perm[e];
+        tbl[w] = (p << 7) | grad_code(p % 12u);
+    }
+}
+
+// one level of the hash walk: entry ((off7 >> 7) & 255) of this lane's bank
+__device__ __forceinline__ uint32_t look(const char *tbl_bytes, uint32_t lane4, uint32_t off7) {
+    return *reinterpret_cast<const uint32_t *>(tbl_bytes + ((off7 & GN_ADDR_MASK) | lane4));
+}
+
+// ±a ± b from a table entry
+__device__ __forceinline__ float grad_dot(uint32_t e, float x, float y, float z) {
+    float a = (e & 1u) ? y : x;
+    float b = (e & 2u) ? y : z;
+    a = __uint_as_float(__float_as_uint(a) ^ (e & 0x80000000u));
+    b = __uint_as_float(__float_as_uint(b) ^ ((e << 1) & 0x80000000u));
+    return a + b;
+}
+
+struct Lattice {   // filled only by the probe path
+    int i, j, k, c1, c2, g0, g1, g2, g3;
+};
+
+// Skewed coordinate in 32.32 fixed point; d keeps the double for the rare exact-integer test.
+struct Skewed {
+    uint32_t lo;
+    int32_t hi;
+    double d;
+};
+__device__ __forceinline__ Skewed to_fixed(double u) {
+    Skewed s;
+    long long f = __double2ll_rd(u * 4294967296.0);
+    s.lo = (uint32_t)f;
+    s.hi = (int32_t)(f >> 32);
+    s.d = u;
+    return s;
+}
+
+// integer cell and in-cell fraction of octave k (skewed coordinate 2^k * u)
+__device__ __forceinline__ void cell_of(const Skewed &s, int k, int &cell, float &frac) {
+    uint32_t lo = s.lo << k;
+    cell = (int)__funnelshift_l(s.lo, (uint32_t)s.hi, k);
+    frac = __uint2float_rn(lo) * 2.3283064365386963e-10f;
+    if (lo == 0u) {   // rare: looks like an exact integer in fixed point
+        double uk = s.d * (double)(1u << k);
+        if (uk <= 0.0 && uk == rint(uk)) {   // simplexnoise.h:130 fastfloor: (int)x - 1 for exact x <= 0
+            cell -= 1;
+            frac = 1.0f;
+        }
+    }
+}
+
+// One raw simplex value from cells (ci,cj,ck) and fractions (fu,fv,fw).  Returns 32*(n0+n1+n2+n3).
+template <bool PROBE>
+__device__ __forceinline__ float simplex_cell(const char *tbl, uint32_t lane4, int ci, int cj, int ck,
+                                              float fu, float fv, float fw, Lattice *lat) {
+    const float G3 = 1.0f / 6.0f;
+    float t = (fu + fv + fw) * G3;
+    float x0 = fu - t, y0 = fv - t, z0 = fw - t;
+
+    // the six orderings of simplexnoise.cpp:267-276 as three comparisons
+    bool a = x0 >= y0, b = y0 >= z0, c = x0 >= z0;
+    bool i1 = a && c, j1 = !a && b, k1 = !b && !c;
+    bool i2 = a || c, j2 = !a || b, k2 = !(b && c);
+
+    float x1 = x0 - (i1 ? 1.0f : 0.0f) + G3, y1 = y0 - (j1 ? 1.0f : 0.0f) + G3, z1 = z0 - (k1 ? 1.0f : 0.0f) + G3;
+    float x2 = x0 - (i2 ? 1.0f : 0.0f) + 2.0f * G3, y2 = y0 - (j2 ? 1.0f : 0.0f) + 2.0f * G3,
+          z2 = z0 - (k2 ? 1.0f : 0.0f) + 2.0f * G3;
+    float x3 = x0 - 0.5f, y3 = y0 - 0.5f, z3 = z0 - 0.5f;
+
+    // hash walk: perm[ii+oi+perm[jj+oj+perm[kk+ok]]], offsets pre-scaled by 128
+    uint32_t K7 = (uint32_t)ck << 7, J7 = (uint32_t)cj << 7, I7 = (uint32_t)ci << 7;
+    uint32_t A0 = look(tbl, lane4, K7), A1 = look(tbl, lane4, K7 + 128u);
+    uint32_t B0 = look(tbl, lane4, A0 + J7);
+    uint32_t B1 = look(tbl, lane4, (k1 ? A1 : A0) + J7 + (j1 ? 128u : 0u));
+    uint32_t B2 = look(tbl, lane4, (k2 ? A1 : A0) + J7 + (j2 ? 128u : 0u));
+    uint32_t B3 = look(tbl, lane4, A1 + J7 + 128u);
+    uint32_t C0 = look(tbl, lane4, B0 + I7);
+    uint32_t C1 = look(tbl, lane4, B1 + I7 + (i1 ? 128u : 0u));
+    uint32_t C2 = look(tbl, lane4, B2 + I7 + (i2 ? 128u : 0u));
+    uint32_t C3 = look(tbl, lane4, B3 + I7 + 128u);
+
+    float t0 = fmaxf(0.6f - x0 * x0 - y0 * y0 - z0 * z0, 0.0f);
+    float t1 = fmaxf(0.6f - x1 * x1 - y1 * y1 - z1 * z1, 0.0f);
+    float t2 = fmaxf(0.6f - x2 * x2 - y2 * y2 - z2 * z2, 0.0f);
+    float t3 = fmaxf(0.6f - x3 * x3 - y3 * y3 - z3 * z3, 0.0f);
+    t0 *= t0; t1 *= t1; t2 *= t2; t3 *= t3;
+    float n = t0 * t0 * grad_dot(C0, x0, y0, z0);
+    n = fmaf(t1 * t1, grad_dot(C1, x1, y1, z1), n);
+    n = fmaf(t2 * t2, grad_dot(C2, x2, y2, z2), n);
+    n = fmaf(t3 * t3, grad_dot(C3, x3, y3, z3), n);
+
+    if (PROBE) {
+        lat->c1 = (int)i1 + 2 * (int)j1 + 4 * (int)k1;
+        lat->c2 = (int)i2 + 2 * (int)j2 + 4 * (int)k2;
+        lat->g0 = (C0 >> 2) & 15; lat->g1 = (C1 >> 2) & 15; lat->g2 = (C2 >> 2) & 15; lat->g3 = (C3 >> 2) & 15;
+    }
+    return 32.0f * n;
+}
+
+// skewed coordinates of the point (x,y,z) (doubles), reference operation order (simplexnoise.cpp:247-251)
+__device__ __forceinline__ void skew(double x, double y, double z, Skewed &su, Skewed &sv, Skewed &sw) {
+    const double F3 = 1.0 / 3.0;
+    double s = __dmul_rn(__dadd_rn(__dadd_rn(x, y), z), F3);
+    su = to_fixed(__dadd_rn(x, s));
+    sv = to_fixed(__dadd_rn(y, s));
+    sw = to_fixed(__dadd_rn(z, s));
+}
+
+// Noise::octave_noise_3d (noise.cpp:162-180): sum_k raw(x f_k) a_k / sum a_k, f_k = scale 2^k, a_k = pers^k.
+// (px,py,pz) are the float coordinates the reference widens to double; scale is the double frequency.
+__device__ __forceinline__ float fbm(const char *tbl, uint32_t lane4, float px, float py, float pz, double scale,
+                                     int octaves, float pers, float inv_maxamp) {
+    Skewed su, sv, sw;
+    skew(__dmul_rn((double)px, scale), __dmul_rn((double)py, scale), __dmul_rn((double)pz, scale), su, sv, sw);
+    float total = 0.0f, amp = 1.0f;
+#pragma unroll 1
+    for (int k = 0; k < octaves; k++) {
+        int ci, cj, ck;
+        float fu, fv, fw;
+        cell_of(su, k, ci, fu);
+        cell_of(sv, k, cj, fv);
+        cell_of(sw, k, ck, fw);
+        total = fmaf(simplex_cell<false>(tbl, lane4, ci, cj, ck, fu, fv, fw, nullptr), amp, total);
+        amp *= pers;
+    }
+    return total * inv_maxamp;
+}
+
+// Noise::getRidgedMf (noise.cpp:81-128). v is the float QVector3D (already r*scale); it is scaled by
+// float(lacunarity) per octave exactly like `vt = vt * lacunarity`. rw[o] = pow(frequency_o, -0.05f).
+__device__ __forceinline__ float ridged(const char *tbl, uint32_t lane4, float vx, float vy, float vz, int octaves,
+                                        float lac, float offset, float gain, const float *rw) {
+    float value = 0.0f, weight = 1.0f;
+#pragma unroll 1
+    for (int o = 0; o < octaves; o++) {
+        Skewed su, sv, sw;
+        skew((double)vx, (double)vy, (double)vz, su, sv, sw);
+        int ci, cj, ck;
+        float fu, fv, fw;
+        cell_of(su, 0, ci, fu);
+        cell_of(sv, 0, cj, fv);
+        cell_of(sw, 0, ck, fw);
+        float signal = fabsf(simplex_cell<false>(tbl, lane4, ci, cj, ck, fu, fv, fw, nullptr));
+        signal = offset - signal;
+        signal *= signal;
+        signal *= weight;
+        weight = fminf(fmaxf(signal * gain, 0.0f), 1.0f);
+        value = fmaf(signal, rw[o], value);
+        vx = __fmul_rn(vx, lac); vy = __fmul_rn(vy, lac); vz = __fmul_rn(vz, lac);
+    }
+    return fmaf(value, 1.25f, -1.0f);
+}
+
+}  // namespace gnoise

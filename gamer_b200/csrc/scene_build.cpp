@@ -1,0 +1,156 @@
+// scene_build.cpp — host: ABI scene (GamerFrame/GamerGalaxy/GamerComponent) -> DScene kernel parameter.
+// The exact gate thresholds are found here by bisection over float bit patterns, evaluating the
+// reference's double-precision expressions (galaxycomponent.h:61-81, galaxycomponent.cpp:58-65).
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <limits>
+#include "scene_build.h"
+
+namespace {
+
+inline float bits_f(uint32_t b) { float f; std::memcpy(&f, &b, 4); return f; }
+
+// largest non-negative float for which pred holds, pred monotone (true ... true false ... false).
+// returns -1 if pred(0) is false, +inf if pred holds for every finite float.
+template <class P> float largest_passing(P pred) {
+    if (!pred(0.0f)) return -1.0f;
+    uint32_t lo = 0, hi = 0x7f800000u;              // lo passes; hi = +inf
+    if (pred(bits_f(hi - 1))) return std::numeric_limits<float>::infinity();
+    hi = hi - 1;                                    // hi fails
+    while (hi - lo > 1) {
+        uint32_t mid = lo + (hi - lo) / 2;
+        if (pred(bits_f(mid))) lo = mid; else hi = mid;
+    }
+    return bits_f(lo);
+}
+
+inline double ref_clamp(double v, double mi, double ma) { v = (v < ma) ? v : ma; v = (mi < v) ? v : mi; return v; }
+
+// Qt 5.15 QVector3D::normalized in double, result float
+void normalize3(const float in[3], float out[3]) {
+    double len = double(in[0]) * in[0] + double(in[1]) * in[1] + double(in[2]) * in[2];
+    if (std::fabs(len - 1.0) <= 1e-12) { out[0] = in[0]; out[1] = in[1]; out[2] = in[2]; return; }
+    if (std::fabs(len) > 1e-12) {
+        double s = std::sqrt(len);
+        out[0] = float(in[0] / s); out[1] = float(in[1] / s); out[2] = float(in[2] / s);
+        return;
+    }
+    out[0] = out[1] = out[2] = 0.f;
+}
+
+}  // namespace
+
+int gk_build_scene(const GamerFrame *f, const GamerGalaxy *gal, const GamerComponent *comp, DScene *out, char *err,
+                   size_t errlen) {
+    auto fail = [&](const char *m) { if (err && errlen) std::snprintf(err, errlen, "%s", m); return GAMER_E_ARG; };
+    if (!f || !out) return fail("null frame");
+    if (f->width <= 0 || f->height <= 0 || f->full_size <= 0) return fail("frame size must be positive");
+    if (f->n_galaxies < 0 || f->n_galaxies > DEV_MAX_GALAXIES) return fail("n_galaxies out of range (max 8 per frame)");
+    if (f->n_components < 0) return fail("n_components negative");
+    if ((f->n_galaxies && !gal) || (f->n_components && !comp)) return fail("null galaxy/component array");
+    if (f->band_rows < 0 || (f->band_rows > 0 && f->band_stride < f->band_rows)) return fail("bad band_rows/band_stride");
+    if (!(f->ray_step > 0.0) || !(f->min_ray_step > 0.0) || f->min_ray_step > 0.01) return fail("ray_step/min_ray_step out of range");
+
+    std::memset(out, 0, sizeof(*out));
+    DScene &s = *out;
+    s.width = f->width; s.height = f->height; s.full_size = f->full_size;
+    s.x0 = f->x0; s.y0 = f->y0; s.band_rows = f->band_rows; s.band_stride = f->band_stride;
+    s.n_galaxies = f->n_galaxies;
+    for (int i = 0; i < 16; i++) s.inv_vp[i] = f->inv_vp[i];
+    for (int i = 0; i < 3; i++) s.cam[i] = f->cam[i];
+    s.ray_step = f->ray_step;
+    s.ray_step_f = float(f->ray_step);
+    s.min_ray_step = f->min_ray_step;
+    s.final_mul = float(0.01);
+
+    int nc = 0;
+    for (int gi = 0; gi < f->n_galaxies; gi++) {
+        const GamerGalaxy &g = gal[gi];
+        DGalaxy &d = s.gal[gi];
+        if (g.comp_begin < 0 || g.comp_count < 0 || g.comp_begin + g.comp_count > f->n_components)
+            return fail("galaxy component range outside the component array");
+        for (int i = 0; i < 3; i++) {
+            d.pos[i] = g.pos[i];
+            d.orient[i] = g.orient[i];
+            d.inv_axis2[i] = float(1.0 / (g.axis[i] * g.axis[i]));   // util.h:68-70: float product, double divide
+        }
+        normalize3(g.orient, d.axis_n);
+        for (int i = 0; i < 4; i++) { d.rot[i] = g.rotmat[i]; d.arm[i] = float(g.arm[i]); }
+        d.rot_identity = (g.rotmat[0] == 1.f && g.rotmat[1] == 0.f && g.rotmat[2] == 0.f && g.rotmat[3] == 0.f);
+        d.axis_x = g.axis[0];
+        d.inv_axis_x = 1.0f / g.axis[0];
+        d.inv_winding_b = float(1.0 / g.winding_b);
+        d.winding_2n = float(2.0 * g.winding_n);
+        d.no_arms = (g.no_arms == 1) ? 1 : (g.no_arms == 2) ? 2 : (g.no_arms == 3) ? 3 : 4;
+        d.comp_begin = nc;
+        for (int k = 0; k < g.comp_count; k++) {
+            const GamerComponent &c = comp[g.comp_begin + k];
+            if (!(c.active == 1)) continue;                                   // rasterizer.cpp:458
+            if (c.class_id < GAMER_CLASS_BULGE || c.class_id > GAMER_CLASS_STARS_SMALL) return fail("unknown class_id");
+            if (c.class_id == GAMER_CLASS_STARS_SMALL) continue;              // no-op, see gamer_b200.h
+            if (nc >= DEV_MAX_COMPONENTS) return fail("too many active components (max 64 per frame)");
+            DComp &q = s.comp[nc++];
+            q.cls = c.class_id;
+            q.flags = 0;
+            if (c.arm != 0) q.flags |= DC_HAS_ARM;
+            if (c.winding != 0) q.flags |= DC_HAS_WINDING;
+            if (c.noise_offset != 0) q.flags |= DC_HAS_NOFF;
+            const double inner = 1.0f * c.inner;
+            if (inner == 0.0) q.flags |= DC_INNER_ZERO;
+            if (c.noise_tilt == std::floor(c.noise_tilt) && std::fabs(c.noise_tilt) < 1e9) {
+                q.flags |= DC_TILT_INT;
+                if (std::fmod(std::fabs(c.noise_tilt), 2.0) == 1.0) q.flags |= DC_TILT_ODD;
+            }
+            q.iscale = float(g.intensity_scale);
+            q.strength = (c.class_id == GAMER_CLASS_BULGE) ? float(c.strength) : float(c.strength * g.intensity_scale);
+            q.arm15 = float(c.arm * 15);
+            q.inv_z0 = float(1.0 / std::fabs(c.z0));
+            q.inv_inner = float(1.0 / inner);
+            q.delta = float(c.delta);
+            q.winding = float(c.winding);
+            q.noise_offset = float(c.noise_offset);
+            q.noise_tilt = float(c.noise_tilt);
+            q.rscale = float(c.scale);
+            q.r0 = float(c.r0);
+            for (int i = 0; i < 3; i++) q.spec[i] = c.spec[i];
+
+            // slab gate (galaxycomponent.h:61-64): h = |height/z0|; h > 2 -> 0
+            const double z0 = c.z0;
+            q.h_gate = largest_passing([&](float a) { double h = std::fabs(double(a) / z0); return !(h > 2.0) && h == h; });
+            // radial gate (galaxycomponent.h:72-81, galaxycomponent.cpp:58-65)
+            const float ax = g.axis[0];
+            const double r0h = c.r0 * 0.5f;
+            auto radial = [&](float plen) {
+                float radius = plen / ax;
+                double r = std::exp(-double(radius) / r0h);
+                double in = ref_clamp(r - 0.01f, 0, 1);
+                if (in > 0.1) in = 0.1;
+                return in > 0.001;
+            };
+            if (c.r0 > 0 && ax > 0) q.plen_thr = largest_passing(radial);
+            else q.plen_thr = radial(1.0f) ? std::numeric_limits<float>::infinity() : -1.0f;
+            if (std::isinf(q.plen_thr)) { q.plen_lo = q.plen_hi = q.plen_thr; }
+            else if (q.plen_thr < 0) { q.plen_lo = q.plen_hi = -1.0f; }
+            else { q.plen_lo = q.plen_thr * (1.0f - 2e-6f); q.plen_hi = q.plen_thr * (1.0f + 2e-6f); }
+            q.k_radial = float(-1.4426950408889634 / (r0h * double(ax)));
+
+            // noise set-up
+            int oct = 0;
+            q.nscale = 0.0;
+            if (c.class_id == GAMER_CLASS_DISK) { oct = 10; q.nscale = c.scale * 0.1f; }      // galaxycomponent.h:96
+            if (c.class_id == GAMER_CLASS_DUST) { oct = 9;  q.nscale = c.scale * 0.1f; }
+            if (c.class_id == GAMER_CLASS_STARS) { oct = 10; q.nscale = 0.01f * c.scale * 100; } // galaxycomponents.cpp:141
+            q.pers = float(c.ks);
+            double amp = 1, maxamp = 0;
+            for (int o = 0; o < oct; o++) { maxamp += amp; amp *= c.ks; }
+            q.inv_maxamp = oct ? float(1.0 / maxamp) : 0.f;
+            if (std::fabs(q.nscale) >= 65536.0) return fail("noise scale too large (|scale| must stay below 65536)");
+            double freq = c.ks;                                                        // noise.cpp:119-124
+            const double w = -0.05f;
+            for (int o = 0; o < DEV_RIDGED_OCTAVES; o++) { q.rw[o] = float(std::pow(freq, w)); freq *= 2.5; }
+        }
+        d.comp_count = nc - d.comp_begin;
+    }
+    return GAMER_OK;
+}

@@ -1,0 +1,80 @@
+// scene_dev.h — the scene as the kernels see it: one POD passed as a __grid_constant__ kernel
+// parameter (constant bank, warp-uniform reads), built on the host from the ABI structs.
+//
+// What is precomputed here, in double exactly as the reference would evaluate it, so that the
+// kernel's discontinuous decisions agree with the CPU renderer bit for bit:
+//   * h_gate     — getHeightModulation's `h > 2` cut (galaxycomponent.h:61-64) as a threshold on the
+//                  float |dott| the kernel computes with the same unfused float ops as QVector3D;
+//   * plen_thr   — calculateIntensity's `intensity > 0.001` cut (galaxycomponent.cpp:62-65) as a
+//                  threshold on the float |P| (getRadius, galaxycomponent.h:72-76);
+// everything else is the component's parameters narrowed to float once.
+#pragma once
+#include <stdint.h>
+
+#define DEV_MAX_GALAXIES   8
+#define DEV_MAX_COMPONENTS 64
+#define DEV_RIDGED_OCTAVES 9
+
+// flags
+#define DC_HAS_ARM      1    // cp.arm != 0                (galaxycomponent.cpp:69)
+#define DC_HAS_WINDING  2    // cp.winding != 0            (galaxycomponent.cpp:72)
+#define DC_HAS_NOFF     4    // cp.noiseOffset != 0        (galaxycomponents.cpp:144)
+#define DC_INNER_ZERO   8    // smoothstep(0, 0, r) -> 1   (util.cpp:114-120)
+#define DC_TILT_INT     16   // noiseTilt is an integer (pow of a negative base is defined)
+#define DC_TILT_ODD     32
+
+struct DComp {
+    int32_t cls;
+    int32_t flags;
+    float   strength;        // cp.strength (bulge) or cp.strength * gi.intensityScale (others)
+    float   iscale;          // gi.intensityScale
+    float   arm15;           // cp.arm * 15
+    float   h_gate;          // pass the slab gate iff |dott| <= h_gate  (exact)
+    float   inv_z0;
+    float   plen_thr;        // pass the radial gate iff |P| <= plen_thr (exact)
+    float   plen_lo, plen_hi;// outside [lo,hi] the fast float |P| decides; inside, the exact one
+    float   k_radial;        // exp(-radius/(r0*0.5)) = exp2(|P| * k_radial)
+    float   inv_inner;       // 1 / cp.inner
+    float   delta;
+    float   winding;
+    float   pers;            // cp.ks used as persistence
+    float   inv_maxamp;      // 1 / sum_k pers^k
+    float   noise_offset;
+    float   noise_tilt;
+    float   rscale;          // float(cp.scale): getRidgedMf input scale (QVector3D * double)
+    float   r0;
+    float   spec[3];
+    float   rw[DEV_RIDGED_OCTAVES];   // pow(ks * 2.5^o, -0.05f)  (noise.cpp:119)
+    float   _pad;
+    double  nscale;          // fBm start frequency, as a double the way the reference forms it
+};
+
+struct DGalaxy {
+    float   pos[3];
+    float   orient[3];       // as given (getRadius uses it un-normalised)
+    float   axis_n[3];       // normalised orientation (twirl axis, QQuaternion::fromAxisAndAngle)
+    float   rot[4];          // rotmat w,x,y,z
+    float   inv_axis2[3];    // float(1.0/(a*a)) per axis  (util.h:68-70)
+    float   inv_axis_x;      // 1 / axis.x
+    float   axis_x;
+    float   inv_winding_b;
+    float   winding_2n;      // 2 * windingN
+    float   arm[4];
+    int32_t no_arms;         // 1,2,3 or 4 (anything else means 4: galaxycomponent.h:120-137)
+    int32_t rot_identity;
+    int32_t comp_begin, comp_count;   // ACTIVE components only, file order
+};
+
+struct DScene {
+    int32_t width, height, full_size, x0, y0, band_rows, band_stride;
+    int32_t n_galaxies;
+    float   inv_vp[16];
+    float   cam[3];
+    float   ray_step_f;      // float(rayStep)
+    double  ray_step;
+    double  min_ray_step;
+    float   final_mul;       // float(0.01)
+    float   _pad;
+    DGalaxy gal[DEV_MAX_GALAXIES];
+    DComp   comp[DEV_MAX_COMPONENTS];
+};

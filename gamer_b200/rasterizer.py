@@ -1,0 +1,239 @@
+"""Rasterizer — the reference's seam (source/galaxy/rasterizer.h:20-127) over the C ABI.
+
+Method names, argument meaning and call order follow the reference class so a caller written for
+`Rasterizer` (ConsoleRenderer::RenderSingleGalaxy, consolerenderer.cpp:29-101) ports line by line:
+setRenderingParams / AddGalaxy / Render (or RenderDirect) / getState / getPercentDone / Abort /
+AssembleImage / getRenderBuffer / getBuffer / getImageShadowBuffer.  RenderPixels() is one blocking
+FFI call into the CUDA kernels; there is no CPU fallback.
+"""
+import ctypes as C
+import threading
+from typing import List, Optional
+
+import numpy as np
+
+from . import _lib
+from .gax import Galaxy
+from .model import GalaxyInstance, RenderingParams, Scene, build_scene
+
+
+class Context:
+    """Owns one gamer_ctx (device memory + streams). One per Rasterizer."""
+
+    def __init__(self, device_ids: Optional[List[int]] = None):
+        self.lib = _lib.load()
+        self.h = C.c_void_p()
+        ids = device_ids or [0]
+        arr = (C.c_int32 * len(ids))(*ids)
+        _lib.check(None, self.lib.gamer_b200_create(C.byref(self.h), arr, len(ids)))
+        self.shape = None
+
+    def close(self):
+        if self.h:
+            self.lib.gamer_b200_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def upload(self, scene: Scene):
+        _lib.check(self.h, self.lib.gamer_b200_upload(self.h, C.byref(scene.frame), scene.galaxies, scene.components))
+        self.shape = (scene.frame.height, scene.frame.width)
+
+    def render(self, out: Optional[np.ndarray] = None) -> np.ndarray:
+        h, w = self.shape
+        if out is None:
+            out = np.empty((h, w, 3), dtype=np.float32)
+        assert out.dtype == np.float32 and out.size == h * w * 3 and out.flags.c_contiguous
+        _lib.check(self.h, self.lib.gamer_b200_render(self.h, out.ctypes.data))
+        return out
+
+    def render_ptr(self, host_ptr: int):
+        _lib.check(self.h, self.lib.gamer_b200_render(self.h, host_ptr))
+
+    def render_device(self):
+        _lib.check(self.h, self.lib.gamer_b200_render_device(self.h))
+
+    def render_counted(self) -> dict:
+        _lib.check(self.h, self.lib.gamer_b200_render_counted(self.h))
+        c = (C.c_uint64 * _lib.CNT_N)()
+        _lib.check(self.h, self.lib.gamer_b200_counters(self.h, c))
+        return {"rays": c[0], "samples": c[1], "gates": c[2], "comp_evals": c[3], "octaves": c[4]}
+
+    def tonemap(self, exposure=1.0, gamma=1.0, saturation=1.0, stars: Optional[np.ndarray] = None):
+        h, w = self.shape
+        argb = np.empty((h, w), dtype=np.uint32)
+        shadow = np.empty((h, w), dtype=np.uint32)
+        sp = None
+        if stars is not None:
+            stars = np.ascontiguousarray(stars, dtype=np.float32)
+            assert stars.size == h * w * 3
+            sp = stars.ctypes.data
+        _lib.check(self.h, self.lib.gamer_b200_tonemap(self.h, exposure, gamma, saturation, sp,
+                                                       argb.ctypes.data, shadow.ctypes.data))
+        return argb, shadow
+
+    def tonemap_ptr(self, exposure, gamma, saturation, argb_ptr, shadow_ptr):
+        _lib.check(self.h, self.lib.gamer_b200_tonemap(self.h, exposure, gamma, saturation, None, argb_ptr, shadow_ptr))
+
+    def tonemap_device(self, exposure=1.0, gamma=1.0, saturation=1.0):
+        _lib.check(self.h, self.lib.gamer_b200_tonemap_device(self.h, exposure, gamma, saturation))
+
+    def kernel_ms(self):
+        a, b = C.c_float(), C.c_float()
+        _lib.check(self.h, self.lib.gamer_b200_last_kernel_ms(self.h, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
+    def launches(self) -> int:
+        n = C.c_uint64()
+        _lib.check(self.h, self.lib.gamer_b200_launch_count(self.h, C.byref(n)))
+        return n.value
+
+    def device_buffers(self, which=0):
+        p = [C.c_void_p(), C.c_void_p(), C.c_void_p()]
+        rows = C.c_int32()
+        _lib.check(self.h, self.lib.gamer_b200_device_buffers(self.h, which, C.byref(p[0]), C.byref(p[1]), C.byref(p[2]),
+                                                              C.byref(rows)))
+        return p[0].value, p[1].value, p[2].value, rows.value
+
+    def progress(self) -> float:
+        f = C.c_double()
+        _lib.check(self.h, self.lib.gamer_b200_progress(self.h, C.byref(f)))
+        return f.value
+
+    def abort(self):
+        _lib.check(self.h, self.lib.gamer_b200_abort(self.h))
+
+    # probes of the device noise code (parity tests)
+    def probe_simplex(self, xyz: np.ndarray, frequency=1.0):
+        xyz = np.ascontiguousarray(xyz, dtype=np.float32)
+        n = xyz.shape[0]
+        lat = np.empty((n, 10), dtype=np.int32)
+        val = np.empty(n, dtype=np.float32)
+        _lib.check(self.h, self.lib.gamer_b200_probe_simplex(self.h, xyz.ctypes.data, n, frequency, lat.ctypes.data, val.ctypes.data))
+        return lat, val
+
+    def probe_fbm(self, xyz, octaves, persistence, scale):
+        xyz = np.ascontiguousarray(xyz, dtype=np.float32)
+        val = np.empty(xyz.shape[0], dtype=np.float32)
+        _lib.check(self.h, self.lib.gamer_b200_probe_fbm(self.h, xyz.ctypes.data, xyz.shape[0], octaves, persistence, scale, val.ctypes.data))
+        return val
+
+    def probe_ridged(self, xyz, frequency, octaves, lacunarity, offset, gain):
+        xyz = np.ascontiguousarray(xyz, dtype=np.float32)
+        val = np.empty(xyz.shape[0], dtype=np.float32)
+        _lib.check(self.h, self.lib.gamer_b200_probe_ridged(self.h, xyz.ctypes.data, xyz.shape[0], frequency, octaves, lacunarity,
+                                                            offset, gain, val.ctypes.data))
+        return val
+
+
+class Rasterizer:
+    """rasterizer.h:20-127."""
+
+    class State:
+        idle, rendering, done = 0, 1, 2
+
+    def __init__(self, device_ids: Optional[List[int]] = None):
+        self.m_galaxies: List[GalaxyInstance] = []
+        self.m_renderingParams: Optional[RenderingParams] = None
+        self.m_state = Rasterizer.State.idle
+        self.m_isPreview = False
+        self.m_renderBuffer: Optional[np.ndarray] = None      # Buffer2D: float RGB [y][x][3]
+        self.m_starsBuffer: Optional[np.ndarray] = None
+        self.m_imageBuffer: Optional[np.ndarray] = None       # QImage ARGB32
+        self.m_imageShadowBuffer: Optional[np.ndarray] = None
+        self._ctx = Context(device_ids)
+        self._thread: Optional[threading.Thread] = None
+        self._error: Optional[BaseException] = None
+
+    # -- inputs --------------------------------------------------------------------------------
+    def setRenderingParams(self, rp: RenderingParams):
+        self.m_renderingParams = rp
+
+    def AddGalaxy(self, gi_or_file, position=(0, 0, 0), orientation=(0, 1, 0), iscale=1.0, redshift=0.0, name=""):
+        if isinstance(gi_or_file, GalaxyInstance):
+            self.m_galaxies.append(gi_or_file)
+        else:                                              # rasterizer.cpp:229-236
+            g = Galaxy.Load(gi_or_file)
+            self.m_galaxies.append(GalaxyInstance(g, name, position, orientation, iscale, redshift))
+
+    def Clear(self):
+        self.m_galaxies = []
+
+    def CopyFrom(self, other: "Rasterizer"):
+        self.m_galaxies = list(other.m_galaxies)
+
+    def setNewSize(self, s: int):
+        self.m_renderingParams.m_size = int(s)
+
+    # -- render ---------------------------------------------------------------------------------
+    def Prepare(self) -> Scene:
+        return build_scene(self.m_renderingParams, self.m_galaxies, preview=self.m_isPreview)
+
+    def RenderPixels(self):
+        scene = self.Prepare()
+        self._ctx.upload(scene)
+        try:
+            self.m_renderBuffer = self._ctx.render()
+        except _lib.GamerError as e:
+            if e.code != _lib.E_ABORTED:
+                raise
+            self.m_renderBuffer = np.zeros(self._ctx.shape + (3,), dtype=np.float32)
+
+    def run(self):
+        self.m_state = Rasterizer.State.rendering
+        try:
+            self.RenderPixels()
+        except BaseException as e:          # surfaced by getState()
+            self._error = e
+        self.m_state = Rasterizer.State.done
+
+    def Render(self):
+        """Asynchronous, like QThread::start (rasterizer.cpp:350-362)."""
+        self.m_isPreview = False
+        self._error = None
+        self.m_state = Rasterizer.State.rendering
+        self._thread = threading.Thread(target=self.run, daemon=True)
+        self._thread.start()
+
+    def RenderDirect(self):
+        """Synchronous preview (rasterizer.cpp:365-370)."""
+        self.m_isPreview = True
+        self.run()
+        if self._error:
+            raise self._error
+
+    def getState(self):
+        if self.m_state == Rasterizer.State.done and self._error:
+            err, self._error = self._error, None
+            raise err
+        return self.m_state
+
+    def getPercentDone(self) -> float:
+        return self._ctx.progress()
+
+    def Abort(self):
+        self._ctx.abort()
+
+    def RenderStars(self, stars: np.ndarray):
+        """The star layer is rand()-driven host code in the reference (buffer2d.cpp:140-173); a caller
+        supplies the buffer and AssembleImage adds it (rasterizer.cpp:320-321)."""
+        self.m_starsBuffer = stars
+
+    def AssembleImage(self):
+        rp = self.m_renderingParams
+        stars = None if self.m_isPreview else self.m_starsBuffer
+        self.m_imageBuffer, self.m_imageShadowBuffer = self._ctx.tonemap(rp.m_exposure, rp.m_gamma, rp.m_saturation, stars)
+
+    # -- outputs --------------------------------------------------------------------------------
+    def getRenderBuffer(self):
+        return self.m_renderBuffer
+
+    def getBuffer(self):
+        return self.m_imageBuffer
+
+    def getImageShadowBuffer(self):
+        return self.m_imageShadowBuffer

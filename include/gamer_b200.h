@@ -162,6 +162,18 @@ int  gamer_b200_last_kernel_ms(gamer_ctx *ctx, float *k1_ms, float *k2_ms);
 /* number of kernel launches issued by this context since creation */
 int  gamer_b200_launch_count(gamer_ctx *ctx, uint64_t *launches);
 
+/* host-side helpers of the parameter model (pure host code, no device needed) ---------------- */
+/* GamerCamera::setupViewmatrix (gamercamera.cpp:185-208) with m_rotMatrix = identity:
+ * inverse(perspective(fov,1,1,100) * lookAt(target, camera, up)) — eye/centre swapped as in the
+ * reference — as 16 floats [row*4+col], ready for GamerFrame.inv_vp. */
+int  gamer_b200_camera_inv_vp(const float cam[3], const float target[3], const float up[3],
+                              double fov_deg, float inv_vp_out[16]);
+/* GalaxyInstance::setupQuaternions (galaxyinstance.cpp:69-71): rotationTo((0,1,0), orient) as w,x,y,z */
+int  gamer_b200_rotation_to_orientation(const float orient[3], float wxyz_out[4]);
+/* Pinned host memory for fast host<->device copies of framebuffers (optional; any host pointer works). */
+int  gamer_b200_host_alloc(void **ptr, uint64_t bytes);
+int  gamer_b200_host_free (void *ptr);
+
 /* function-level probes of the device noise code (parity tests; same device functions as K1) -- */
 /* raw simplex (simplexnoise.cpp:243-333) at n points given as float coordinates widened to
  * double exactly like the reference's callers do. lattice_out: 10 int32 per point
