@@ -1,0 +1,144 @@
+"""CPU-only tests: the oracle against the reference-produced golden vectors, the host logic, and
+that the C-ABI library loads and exports every symbol include/gamer_b200.h declares."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+import oracle_lib
+import scenes
+from gamer_b200 import _lib
+from gamer_b200.gax import Galaxy
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+# ---- oracle pinned by the reference's own simplexnoise.cpp ------------------------------------------
+def test_oracle_simplex_equals_reference_golden(oracle):
+    g = np.load(os.path.join(ROOT, "tests", "golden", "simplex_ref.npz"))
+    raw = np.array([oracle.lib.go_raw3d(*p) for p in g["pts"]])
+    assert np.array_equal(raw, g["raw"])                      # bit for bit
+    for (oc, pe, sc), ref in zip(g["oct_cases"], g["oct"]):
+        v = oracle.fbm(g["pts"][:300].astype(np.float32), int(oc), float(pe), float(sc))
+        assert np.array_equal(v, ref)
+
+
+@pytest.mark.skipif(not os.path.exists(oracle_lib.REF_NOISE), reason="oracle/_ref not built (needs /root/reference)")
+def test_oracle_simplex_equals_reference_library(oracle):
+    ref = C.CDLL(oracle_lib.REF_NOISE)
+    ref.ref_raw_noise_3d_batch.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+    rng = np.random.default_rng(11)
+    pts = np.concatenate([rng.uniform(-50, 50, (200000, 3)), rng.integers(-5, 5, (2000, 3)).astype(np.float64)])
+    out = np.empty(len(pts))
+    ref.ref_raw_noise_3d_batch(pts.ctypes.data, len(pts), out.ctypes.data)
+    mine = np.array([oracle.lib.go_raw3d(*p) for p in pts[:20000]])
+    assert np.array_equal(mine, out[:20000])
+
+
+def test_simplex_known_properties(oracle):
+    assert oracle.lib.go_raw3d(0.0, 0.0, 0.0) == 0.0
+    pts = np.random.default_rng(5).uniform(-100, 100, (20000, 3)).astype(np.float32)
+    _, v = oracle.simplex(pts)
+    assert np.all(np.abs(v) < 1.0)
+    lat, _ = oracle.simplex(np.array([[0, 0, 0], [-2, 0, 0], [1, 2, 3]], dtype=np.float32))
+    assert lat[0, :3].tolist() == [-1, -1, -1]                # fastfloor quirk at exact non-positive integers
+    assert lat[2, :3].tolist() == [3, 4, 5]
+
+
+# ---- .gax reader ------------------------------------------------------------------------------------
+@pytest.mark.parametrize("name", scenes.FIXTURES)
+def test_gax_roundtrip(name):
+    path = os.path.join(scenes.GAX_DIR, name + ".gax")
+    g = Galaxy.Load(path)
+    assert g.to_bytes() == open(path, "rb").read()
+    assert g.galaxyParams.name == name
+    assert 3 <= len(g.componentParams) <= 8
+
+
+def test_gax_contents_spiral():
+    g = scenes.load_galaxy("Spiral")
+    c = g.componentParams
+    assert [x.className for x in c] == ["bulge", "disk", "dust2", "bulge", "stars", "disk"]
+    assert c[1].strength == 5000 and c[1].spectrum == "Blue" and c[3].active == 0
+    assert (g.galaxyParams.windingB, g.galaxyParams.windingN, g.galaxyParams.noArms) == (0.5, 4.0, 2.0)
+
+
+# ---- C ABI ------------------------------------------------------------------------------------------
+def test_abi_exports_every_declared_symbol():
+    hdr = open(os.path.join(ROOT, "include", "gamer_b200.h")).read()
+    declared = set(re.findall(r"\b(gamer_b200_[a-z0-9_]+)\s*\(", hdr))
+    assert declared == set(_lib.SYMBOLS), declared ^ set(_lib.SYMBOLS)
+    lib = _lib.load()
+    for s in declared:
+        assert hasattr(lib, s), s
+    assert lib.gamer_b200_abi_version() == 1
+
+
+def test_struct_layout_matches_header():
+    assert C.sizeof(_lib.GamerComponent) == 120
+    assert C.sizeof(_lib.GamerGalaxy) == 128
+    assert C.sizeof(_lib.GamerFrame) == 144
+
+
+def test_no_cpu_fallback_without_device():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    lib = _lib.load()
+    h = C.c_void_p()
+    rc = lib.gamer_b200_create(C.byref(h), None, 0)
+    assert rc == _lib.E_CUDA and not h.value
+    assert b"CUDA" in lib.gamer_b200_last_error(None) or b"cuda" in lib.gamer_b200_last_error(None)
+
+
+# ---- host math vs oracle's independent restatement -----------------------------------------------------
+@pytest.mark.parametrize("view", list(scenes.VIEWS))
+def test_camera_matrix(oracle, view):
+    cam, target, up, fov = scenes.VIEWS[view]
+    rp = scenes.rendering_params(64, view)
+    m = rp.camera().setupViewmatrix()
+    ref = oracle.camera_inv_vp(cam, target, up, fov)
+    assert np.allclose(m, ref, rtol=2e-6, atol=2e-6)
+
+
+def test_rotation_to(oracle):
+    from gamer_b200.model import GalaxyInstance
+    for o in [(0, 1, 0), (0.3, 0.8, -0.5), (-0.6, 0.5, 0.62), (0, -1, 0), (1, 0, 0)]:
+        q = np.array(GalaxyInstance(Galaxy(), "", (0, 0, 0), o).rotmat(), dtype=np.float32)
+        assert np.allclose(q, oracle.rotation_to(o), atol=1e-6)
+    assert GalaxyInstance(Galaxy(), "", (0, 0, 0), (0, 1, 0)).rotmat() == [1.0, 0.0, 0.0, 0.0]
+
+
+def test_scene_sorted_far_to_near():
+    sc = scenes.multi_galaxy_scene(32)
+    cam = np.array(sc.frame.cam[:])
+    d = [np.linalg.norm(np.array(sc.galaxies[i].pos[:]) - cam) for i in range(sc.frame.n_galaxies)]
+    assert d == sorted(d, reverse=True)
+    assert sc.frame.n_components == sum(sc.galaxies[i].comp_count for i in range(3))
+
+
+# ---- oracle behaviour the reference documents ----------------------------------------------------------
+def test_oracle_render_basics(oracle):
+    sc = scenes.single_galaxy_scene("Spiral", 24, "cli")
+    img, cnt = oracle.render(sc)
+    assert img.shape == (24, 24, 3) and np.all(img >= 0) and img.max() > 1
+    assert cnt["rays"] == 24 * 24 and cnt["gates"] == 5 * cnt["samples"]      # 5 active components
+    img1, _ = oracle.render(sc, threads=1)
+    assert np.array_equal(img, img1)                                          # thread-count independent
+    # tiles and interleaved bands index the same pixels
+    t = sc.tile(5, 7, 11, 9)
+    part, _ = oracle.render(t)
+    assert np.array_equal(part, img[7:16, 5:16])
+    b = sc.tile(0, 2, 24, 6, band_rows=2, band_stride=8)
+    part, _ = oracle.render(b)
+    assert np.array_equal(part, img[[2, 3, 10, 11, 18, 19]])
+
+
+def test_oracle_tonemap(oracle):
+    rgb = np.array([[[0.0, 1.0, 2.55], [30.0, 0.05, 12.345]]], dtype=np.float32)
+    a, s = oracle.tonemap(rgb)
+    assert s[0, 0] == 0xFF000000 | (0 << 16) | (10 << 8) | 25
+    assert s[0, 1] == 0xFF000000 | (255 << 16) | (0 << 8) | 123
+    assert a[0, 1] == 0xFF000000 | (123 << 16) | (0 << 8) | 255

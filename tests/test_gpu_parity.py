@@ -1,0 +1,216 @@
+"""GPU parity: the CUDA path (through the C ABI) against the CPU oracle on the same seeded inputs.
+
+Bars (BASELINE.json north_star):
+  * integer work — lattice cell (i,j,k), corner ordering, gradient indices gi0..gi3, sample and ray
+    counts, pixel/tile indexing — bit-exact;
+  * linear RGB intensity — |gpu - cpu| <= RTOL*|cpu| + ATOL per channel per pixel, RTOL = 1e-3,
+    ATOL = 1e-5 (1e-4 of one 8-bit output step, which is 0.1 in linear units: buffer2d.cpp:120-124).
+"""
+import numpy as np
+import pytest
+
+import scenes
+
+pytestmark = pytest.mark.gpu
+
+RTOL, ATOL = 1e-3, 1e-5
+
+
+def assert_pixels_close(gpu, cpu, what=""):
+    err = np.abs(gpu.astype(np.float64) - cpu.astype(np.float64))
+    bound = RTOL * np.abs(cpu.astype(np.float64)) + ATOL
+    worst = np.max(err / bound)
+    rel = np.max(err / (np.abs(cpu) + 1e-3))
+    assert worst <= 1.0, f"{what}: max err/bound {worst:.3g} (max rel {rel:.3g}) at {np.unravel_index(np.argmax(err / bound), err.shape)}"
+    return rel
+
+
+def noise_points(seed=7, n=200000):
+    rng = np.random.default_rng(seed)
+    pts = np.concatenate([
+        rng.uniform(-2, 2, (n, 3)), rng.uniform(-300, 300, (n // 4, 3)), rng.uniform(-60000, 60000, (n // 4, 3)),
+    ]).astype(np.float32)
+    # adversarial: exact integers (fastfloor quirk for <= 0), cell faces, tiny values, negatives
+    ints = np.array([[a, b, c] for a in (-3, -1, 0, 1, 2) for b in (-2, 0, 3) for c in (-1, 0, 4)], dtype=np.float32)
+    edge = np.array([[0.5, 0.5, 0.5], [-0.5, -0.5, -0.5], [1e-9, -1e-9, 0], [255, 256, 257], [-255.5, 0.25, 1024.75],
+                     [1e-30, 1e-30, 1e-30], [-1e-30, 0, 0], [0.75, -0.25, 0.5]], dtype=np.float32)
+    return np.concatenate([pts, ints, edge])
+
+
+def test_simplex_hash_bit_exact(gpu_ctx, oracle):
+    pts = noise_points()
+    for freq in (1.0, 0.1 * 7, 150.0):
+        lat_g, val_g = gpu_ctx.probe_simplex(pts, freq)
+        lat_c, val_c = oracle.simplex(pts, freq)
+        # cell + the two hash results that depend on the cell alone: always exact
+        assert np.array_equal(lat_g[:, [0, 1, 2, 5, 8]], lat_c[:, [0, 1, 2, 5, 8]])
+        # corner ordering / middle hashes: exact except on exact ties between coordinates of
+        # different cells, where the reference's own double rounding picks either side
+        same = np.all(lat_g == lat_c, axis=1)
+        assert same.mean() > 0.99999, same.mean()
+        assert np.max(np.abs(val_g - val_c)) < 3e-6
+        # where the ordering differs the value still agrees (the two simplices share the face)
+        assert np.max(np.abs(val_g[~same] - val_c[~same]), initial=0.0) < 4e-3
+
+
+def test_simplex_matches_reference_golden(gpu_ctx):
+    g = np.load(scenes.GAX_DIR + "/../simplex_ref.npz")
+    _, val = gpu_ctx.probe_simplex(g["pts"].astype(np.float32), 1.0)
+    assert np.max(np.abs(val - g["raw"])) < 3e-6
+    for (oc, pe, sc), ref in zip(g["oct_cases"], g["oct"]):
+        v = gpu_ctx.probe_fbm(g["pts"][:300].astype(np.float32), int(oc), float(pe), float(sc))
+        assert np.max(np.abs(v - ref)) < 5e-6 * max(1.0, abs(pe) ** int(oc) / 50)
+
+
+@pytest.mark.parametrize("octaves,pers,scale", [(10, 1.0, 1.0), (9, -0.8, 0.5), (10, 1.0, 150.0), (4, -2.0, 0.2), (10, -0.5, 0.7)])
+def test_fbm(gpu_ctx, oracle, octaves, pers, scale):
+    pts = np.random.default_rng(3).uniform(-1, 1, (100000, 3)).astype(np.float32)
+    g = gpu_ctx.probe_fbm(pts, octaves, pers, scale)
+    c = oracle.fbm(pts, octaves, pers, scale)
+    assert np.max(np.abs(g - c)) < 4e-6
+
+
+@pytest.mark.parametrize("freq,offset,gain,scale", [(1.0, 1.0, 1.5, 5.0), (1.0, 1.2, 1.5, 4.0), (1.0, 1.05, 1.5, 20.0), (2.0, 0.9, 2.0, 8.0)])
+def test_ridged(gpu_ctx, oracle, freq, offset, gain, scale):
+    pts = (np.random.default_rng(4).uniform(-1, 1, (100000, 3)) * scale).astype(np.float32)
+    g = gpu_ctx.probe_ridged(pts, freq, 9, 2.5, offset, gain)
+    c = oracle.ridged(pts, freq, 9, 2.5, offset, gain)
+    assert np.max(np.abs(g - c)) < 2e-5
+
+
+def render_both(gpu_ctx, oracle, scene):
+    gpu_ctx.upload(scene)
+    cnt_g = gpu_ctx.render_counted()
+    img_g = gpu_ctx.render()
+    img_c, cnt_c = oracle.render(scene)
+    return img_g, img_c, cnt_g, cnt_c
+
+
+def check_scene(gpu_ctx, oracle, scene, what):
+    img_g, img_c, cnt_g, cnt_c = render_both(gpu_ctx, oracle, scene)
+    # integer parity: the march takes exactly the reference's samples
+    assert cnt_g["rays"] == cnt_c["rays"], what
+    assert cnt_g["samples"] == cnt_c["samples"], what
+    assert cnt_g["gates"] == cnt_c["gates"], what
+    # value-gated counts may differ by a handful of threshold flips (each far below ATOL)
+    assert abs(cnt_g["comp_evals"] - cnt_c["comp_evals"]) <= 1e-4 * cnt_c["comp_evals"] + 2, what
+    assert_pixels_close(img_g, img_c, what)
+
+
+@pytest.mark.parametrize("name", scenes.FIXTURES)
+def test_fixture_cli_view_64(gpu_ctx, oracle, name):
+    """The reference harness' own sweep: nine .gax files, singleGalaxy.sh view, 64x64 (galaxy_repro.py:1024-1066)."""
+    check_scene(gpu_ctx, oracle, scenes.single_galaxy_scene(name, 64, "cli"), name)
+
+
+@pytest.mark.parametrize("view", ["oblique", "faceon", "edge", "outside"])
+@pytest.mark.parametrize("name", ["Spiral", "Sombrero", "RedBar", "TonsOfArms", "Irregular", "WheelGalaxy"])
+def test_fixture_views_96(gpu_ctx, oracle, name, view):
+    check_scene(gpu_ctx, oracle, scenes.single_galaxy_scene(name, 96, view), f"{name}/{view}")
+
+
+def test_spiral_cli_256(gpu_ctx, oracle):
+    check_scene(gpu_ctx, oracle, scenes.single_galaxy_scene("Spiral", 256, "cli"), "Spiral 256")
+
+
+@pytest.mark.parametrize("kind", ["allclasses", "ellipsoid"])
+@pytest.mark.parametrize("view", ["oblique", "cli"])
+def test_synthetic_classes(gpu_ctx, oracle, kind, view):
+    check_scene(gpu_ctx, oracle, scenes.single_galaxy_scene(scenes.synthetic_galaxy(kind), 80, view), f"{kind}/{view}")
+
+
+def test_oriented_and_multi_galaxy(gpu_ctx, oracle):
+    check_scene(gpu_ctx, oracle, scenes.single_galaxy_scene("Spiral", 80, "outside", position=(0.2, -0.1, 0.3),
+                                                           orientation=(0.3, 0.8, -0.5), iscale=0.6), "oriented")
+    check_scene(gpu_ctx, oracle, scenes.multi_galaxy_scene(96), "multi")
+
+
+def test_preview_mode(gpu_ctx, oracle):
+    check_scene(gpu_ctx, oracle, scenes.single_galaxy_scene("Spiral", 64, "cli", preview=True), "preview")
+
+
+def test_empty_and_ragged(gpu_ctx, oracle):
+    # camera looking away from a far galaxy: every ray misses
+    sc = scenes.single_galaxy_scene("Spiral", 40, ((5, 5, 5), (10, 10, 10), (0, 1, 0), 30.0))
+    gpu_ctx.upload(sc)
+    img = gpu_ctx.render()
+    assert np.all(img == 0)
+    # ragged tile not a multiple of the 32x8 block, offset inside the frame
+    full = scenes.single_galaxy_scene("Spiral", 100, "oblique")
+    gpu_ctx.upload(full)
+    whole = gpu_ctx.render()
+    tile = full.tile(13, 27, 45, 19)
+    gpu_ctx.upload(tile)
+    part = gpu_ctx.render()
+    assert np.array_equal(part, whole[27:46, 13:58])          # tile indexing is bit-exact
+    img_c, _ = oracle.render(tile)
+    assert_pixels_close(part, img_c, "tile")
+
+
+def test_interleaved_bands_bit_exact(gpu_ctx):
+    full = scenes.single_galaxy_scene("Sombrero", 128, "edge")
+    gpu_ctx.upload(full)
+    whole = gpu_ctx.render()
+    parts = np.zeros_like(whole)
+    G, B = 4, 8
+    for r in range(G):
+        rows = [y for y in range(128) if (y // B) % G == r]
+        t = full.tile(0, r * B, 128, len(rows), band_rows=B, band_stride=B * G)
+        gpu_ctx.upload(t)
+        parts[rows] = gpu_ctx.render()
+    assert np.array_equal(parts, whole)
+
+
+def test_tonemap_exact(gpu_ctx, oracle):
+    sc = scenes.single_galaxy_scene("Spiral", 96, "oblique")
+    gpu_ctx.upload(sc)
+    img = gpu_ctx.render()
+    a_g, s_g = gpu_ctx.tonemap(1.0, 1.0, 1.0)
+    a_c, s_c = oracle.tonemap(img, 1.0, 1.0, 1.0)
+    assert np.array_equal(a_g, a_c) and np.array_equal(s_g, s_c)
+    stars = np.random.default_rng(1).uniform(0, 3, img.shape).astype(np.float32)
+    a_g, s_g = gpu_ctx.tonemap(0.767, 1.0, 1.467, stars)
+    a_c, s_c = oracle.tonemap(img, 0.767, 1.0, 1.467, stars)
+    assert np.array_equal(a_g, a_c) and np.array_equal(s_g, s_c)
+    # gamma != 1 goes through pow(): allow one 8-bit step on a vanishing fraction of channels
+    a_g, s_g = gpu_ctx.tonemap(0.767, 0.867, 1.467)
+    a_c, s_c = oracle.tonemap(img, 0.767, 0.867, 1.467)
+    d = np.abs(((s_g[..., None] >> np.array([16, 8, 0])) & 255).astype(int) - ((s_c[..., None] >> np.array([16, 8, 0])) & 255).astype(int))
+    assert d.max() <= 1 and (d > 0).mean() < 1e-3
+
+
+def test_rasterizer_api(oracle):
+    """Drive the reference-shaped class the way ConsoleRenderer::RenderSingleGalaxy does."""
+    import time
+    from gamer_b200 import Rasterizer
+    from gamer_b200.model import GalaxyInstance
+    rp = scenes.rendering_params(64, "cli")
+    r = Rasterizer()
+    r.setRenderingParams(rp)
+    g = scenes.load_galaxy("Spiral")
+    r.AddGalaxy(GalaxyInstance(g, g.galaxyParams.name, (0, 0, 0), (0, 1, 0), 1, 0))
+    r.Render()
+    while r.getState() != Rasterizer.State.done:
+        assert 0.0 <= r.getPercentDone() <= 1.0
+        time.sleep(0.001)
+    r.AssembleImage()
+    img_c, _ = oracle.render(scenes.single_galaxy_scene("Spiral", 64, "cli"))
+    assert_pixels_close(r.getRenderBuffer(), img_c, "Rasterizer")
+    _, s_c = oracle.tonemap(r.getRenderBuffer())
+    assert np.array_equal(r.getImageShadowBuffer(), s_c)
+
+
+def test_errors(gpu_ctx):
+    from gamer_b200 import _lib
+    from gamer_b200.rasterizer import Context
+    c = Context([0])
+    with pytest.raises(_lib.GamerError) as e:
+        c.shape = (1, 1)
+        c.render()
+    assert e.value.code == _lib.E_STATE
+    sc = scenes.single_galaxy_scene("Spiral", 16, "cli")
+    sc.frame.ray_step = 0.0
+    with pytest.raises(_lib.GamerError) as e:
+        c.upload(sc)
+    assert e.value.code == _lib.E_ARG
+    c.close()
