@@ -24,16 +24,21 @@ struct Shared1 {          // values of one sample shared by every component of a
     float plen3;          // |p| fast float
     float weight;         // step * 200
     bool have_arm;        // lazily computed per sample
-    float W;              // getWinding(radius)
+    float W;              // getWinding(radius), narrowed
+    double Wd;            // getWinding(radius) in double: it feeds the twirl angle
     float theta0;         // atan2(q.x, q.z), q = rotmat * P
 };
 
 // getWinding (galaxycomponent.h:156-165) and the atan2 of getTheta (:150-153), once per sample
 __device__ __forceinline__ void arm_base(const DGalaxy &g, Shared1 &s) {
     if (s.have_arm) return;
-    float radius = s.Plen * g.inv_axis_x;
-    float r = radius + 0.05f;
-    s.W = atanf(fexp(-0.5f / r) * g.inv_winding_b) * g.winding_2n;   // -0.25/(0.5*r)
+    // radius exactly as getRadius returns it: float |P| (double sqrt) / float axis.x, then the
+    // reference's double expression atan(exp(-0.25/(0.5*r))/windingB)*2*windingN
+    const float radius = __fdiv_rn(v_length(s.P), g.axis_x);
+    const double r = __dadd_rn((double)radius, 0.05);
+    const double e = exp(__ddiv_rn(-0.25, __dmul_rn(0.5, r)));
+    s.Wd = __dmul_rn(__dmul_rn(atan(__ddiv_rn(e, g.winding_b)), 2.0), g.winding_n);
+    s.W = (float)s.Wd;
     f3 q = g.rot_identity ? s.P : q_rotate(g.rot, s.P);
     s.theta0 = atan2f(q.x, q.z);
     s.have_arm = true;
@@ -96,11 +101,12 @@ __device__ __forceinline__ void eval_component(const DScene &sc, const DGalaxy &
         sm *= sm;
         scale = sm * sm;
     }
-    float armv = 1.0f, winding = 0.0f;
+    float armv = 1.0f;
+    double winding = 0.0;
     if (c.flags & DC_HAS_ARM) {
         arm_base(g, s);
         armv = arm_value(g, c, s);
-        if (c.flags & DC_HAS_WINDING) winding = s.W * c.winding;
+        if (c.flags & DC_HAS_WINDING) winding = __dmul_rn(s.Wd, c.winding_d);
     }
     float val = c.strength * scale * armv * z * intensity;
     float ival = val * s.weight;
@@ -109,7 +115,7 @@ __device__ __forceinline__ void eval_component(const DScene &sc, const DGalaxy &
 
     switch (c.cls) {
     case GAMER_CLASS_DISK: {            // galaxycomponents.cpp:41-59
-        f3 r = twirl(g.axis_n, s.p, winding);
+        f3 r = twirl_qt(g.axis_n, s.p, winding);
         float n = gnoise::fbm(nz.tbl, nz.lane4, r.x, r.y, r.z, c.nscale, 10, c.pers, c.inv_maxamp);
         if (COUNT) cn.octaves += 10;
         float p2 = fpow(fmaxf(fabsf(n), 0.01f), c.noise_tilt) + c.noise_offset;
@@ -119,7 +125,7 @@ __device__ __forceinline__ void eval_component(const DScene &sc, const DGalaxy &
         break;
     }
     case GAMER_CLASS_DUST: {            // galaxycomponents.cpp:64-84
-        f3 r = twirl(g.axis_n, s.p, winding);
+        f3 r = twirl_qt(g.axis_n, s.p, winding);
         float n = gnoise::fbm(nz.tbl, nz.lane4, r.x, r.y, r.z, c.nscale, 9, c.pers, c.inv_maxamp);
         if (COUNT) cn.octaves += 9;
         float p2 = fmaxf(n - c.noise_offset, 0.0f);
@@ -131,7 +137,7 @@ __device__ __forceinline__ void eval_component(const DScene &sc, const DGalaxy &
     }
     case GAMER_CLASS_DUST2:             // galaxycomponents.cpp:85-114
     case GAMER_CLASS_DUST_POSITIVE: {   // galaxycomponents.cpp:116-136
-        f3 r = twirl(g.axis_n, s.p, winding);
+        f3 r = twirl_qt(g.axis_n, s.p, winding);
         float p2 = gnoise::ridged(nz.tbl, nz.lane4, __fmul_rn(r.x, c.rscale), __fmul_rn(r.y, c.rscale),
                                   __fmul_rn(r.z, c.rscale), DEV_RIDGED_OCTAVES, 2.5f, c.noise_offset, c.noise_tilt, c.rw);
         if (COUNT) cn.octaves += DEV_RIDGED_OCTAVES;
@@ -150,8 +156,8 @@ __device__ __forceinline__ void eval_component(const DScene &sc, const DGalaxy &
         if (COUNT) cn.octaves += 10;
         float add = 0.0f;
         if (c.flags & DC_HAS_NOFF) {    // two 4-octave helpers, persistence -2: amplitudes 1,-2,4,-8, sum -5
-            f3 r1 = twirl(g.axis_n, s.p, winding);
-            f3 r2 = twirl(g.axis_n, s.p, winding * 0.5f);
+            f3 r1 = twirl_qt(g.axis_n, s.p, winding);
+            f3 r2 = twirl_qt(g.axis_n, s.p, __dmul_rn(winding, 0.5));
             add = c.noise_offset * gnoise::fbm(nz.tbl, nz.lane4, r1.x, r1.y, r1.z, 2.0 * (double)0.1f, 4, -2.0f, -0.2f);
             add += 0.5f * (c.noise_offset * gnoise::fbm(nz.tbl, nz.lane4, r2.x, r2.y, r2.z, 4.0 * (double)0.1f, 4, -2.0f, -0.2f));
             if (COUNT) cn.octaves += 8;
@@ -205,7 +211,7 @@ __device__ __forceinline__ void march(const DScene &sc, const DGalaxy &g, f3 isp
 #pragma unroll 1
         for (int k = 0; k < g.comp_count; k++)
             eval_component<COUNT>(sc, g, sc.comp[g.comp_begin + k], s, nz, Ir, Ig, Ib, cn);
-        if (COUNT) { cn.samples++; cn.gates += g.comp_count; }
+        if (COUNT) { cn.samples++; cn.gates += g.comp_count + g.noop_count; }
         p = v_sub(p, v_mul(dir, __double2float_rn(step)));
         Ir = fmaxf(0.0f, Ir); Ig = fmaxf(0.0f, Ig); Ib = fmaxf(0.0f, Ib);   // Util::floor (util.h:62-64)
     }

@@ -82,13 +82,15 @@ int gk_build_scene(const GamerFrame *f, const GamerGalaxy *gal, const GamerCompo
         d.inv_axis_x = 1.0f / g.axis[0];
         d.inv_winding_b = float(1.0 / g.winding_b);
         d.winding_2n = float(2.0 * g.winding_n);
+        d.winding_b = g.winding_b;
+        d.winding_n = g.winding_n;
         d.no_arms = (g.no_arms == 1) ? 1 : (g.no_arms == 2) ? 2 : (g.no_arms == 3) ? 3 : 4;
         d.comp_begin = nc;
         for (int k = 0; k < g.comp_count; k++) {
             const GamerComponent &c = comp[g.comp_begin + k];
             if (!(c.active == 1)) continue;                                   // rasterizer.cpp:458
             if (c.class_id < GAMER_CLASS_BULGE || c.class_id > GAMER_CLASS_STARS_SMALL) return fail("unknown class_id");
-            if (c.class_id == GAMER_CLASS_STARS_SMALL) continue;              // no-op, see gamer_b200.h
+            if (c.class_id == GAMER_CLASS_STARS_SMALL) { d.noop_count++; continue; }   // no-op, see gamer_b200.h
             if (nc >= DEV_MAX_COMPONENTS) return fail("too many active components (max 64 per frame)");
             DComp &q = s.comp[nc++];
             q.cls = c.class_id;
@@ -109,6 +111,7 @@ int gk_build_scene(const GamerFrame *f, const GamerGalaxy *gal, const GamerCompo
             q.inv_inner = float(1.0 / inner);
             q.delta = float(c.delta);
             q.winding = float(c.winding);
+            q.winding_d = c.winding;
             q.noise_offset = float(c.noise_offset);
             q.noise_tilt = float(c.noise_tilt);
             q.rscale = float(c.scale);

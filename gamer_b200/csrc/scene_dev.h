@@ -47,6 +47,7 @@ struct DComp {
     float   rw[DEV_RIDGED_OCTAVES];   // pow(ks * 2.5^o, -0.05f)  (noise.cpp:119)
     float   _pad;
     double  nscale;          // fBm start frequency, as a double the way the reference forms it
+    double  winding_d;       // cp.winding as the double the reference multiplies getWinding() with
 };
 
 struct DGalaxy {
@@ -63,6 +64,9 @@ struct DGalaxy {
     int32_t no_arms;         // 1,2,3 or 4 (anything else means 4: galaxycomponent.h:120-137)
     int32_t rot_identity;
     int32_t comp_begin, comp_count;   // ACTIVE components only, file order
+    int32_t noop_count;               // active "stars small" components: visited by the reference, no-op here
+    int32_t _pad;
+    double  winding_b, winding_n;     // getWinding is evaluated in double (its result feeds the twirl angle)
 };
 
 struct DScene {

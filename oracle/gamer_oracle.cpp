@@ -224,7 +224,9 @@ inline double radial_intensity(const Ctx &c, double rad) {   // :78-81
     double r = std::exp(-rad / (c.cp->r0 * 0.5f));
     return u_clamp(r - 0.01f, 0, 1);
 }
+double g_dbg_twirl_rel = 0.0;   // debug: relative perturbation of the twirl angle (sensitivity studies only)
 inline V3 twirl(const Ctx &c, const V3 &p, double tw) {      // :86-90
+    if (g_dbg_twirl_rel != 0.0) tw *= (1.0 + g_dbg_twirl_rel);
     Quat q = q5::from_axis_angle(c.orient, float(tw * 180.0));
     return q5::rotate(q, p);
 }
@@ -476,6 +478,7 @@ inline void post_process(const float in[3], double exposure, double gamma, doubl
 extern "C" {
 
 int go_abi_version(void) { return GAMER_B200_ABI_VERSION; }
+void go_debug_twirl_perturb(double rel) { g_dbg_twirl_rel = rel; }
 
 int go_max_threads(void) {
 #ifdef _OPENMP
