@@ -1,0 +1,356 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the galaxy volume integrator (BASELINE.json metric).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload NAME]
+
+A "step" is one frame: K1 (ray march) + K2 (post-process) of a 2048x2048 render of Spiral.gax
+(arms + dust + stars; 10/9/10 noise octaves hard-coded per class) at the reference step count
+(rayStep 0.025f) from the oblique exterior orbit of SURVEY.md §8(d) C2b.  Frame f of the orbit has
+azimuth 45deg + f * 1deg (frame 0 is exactly C2b); with N GPUs step s renders frames s*N .. s*N+N-1,
+one per rank (weak scaling, no data-path collective).  `value` = ray samples/s (loop iterations of
+Rasterizer::getIntensity, counted exactly by the instrumented kernel; same integer as the CPU
+oracle) with the scene resident on the device; `e2e` = the same through the host-buffer C-ABI
+calls (scene upload, D2H of the float framebuffer and the 8-bit image inside the timed region).
+"""
+import argparse
+import json
+import math
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+import numpy as np  # noqa: E402
+
+METRIC = "ray samples/s (and ms/frame) at 2048x2048"
+UNIT = "ray samples/s"
+SIZE = 2048
+FP32_LANES_PER_SM = 128
+
+
+def orbit_view(frame_index: int, radius=0.9, elevation=math.asin(1 / math.sqrt(3)), fov=60.0):
+    """Camera of orbit frame f: |cam| = 0.9, elevation 35.26deg, azimuth 45deg + f deg. Frame 0 = C2b."""
+    if frame_index == 0:
+        return ((0.5196, 0.5196, 0.5196), (0, 0, 0), (0, 1, 0), fov)
+    az = math.radians(45.0 + frame_index)
+    c = radius * math.cos(elevation)
+    return ((c * math.cos(az), radius * math.sin(elevation), c * math.sin(az)), (0, 0, 0), (0, 1, 0), fov)
+
+
+WORKLOADS = {
+    # name: (galaxy, size, view or None for the orbit)
+    "spiral_2048_oblique_orbit": ("Spiral", 2048, None),
+    "spiral_2048_cli_view": ("Spiral", 2048, "cli"),
+    "spiral_512_cli_view": ("Spiral", 512, "cli"),
+    "sombrero_4096_edge": ("Sombrero", 4096, "edge"),
+}
+
+
+def make_scene(workload: str, frame_index: int, size=None):
+    import scenes
+    gal, sz, view = WORKLOADS[workload]
+    return scenes.single_galaxy_scene(gal, size or sz, orbit_view(frame_index) if view is None else view)
+
+
+def algorithmic_flop(cnt: dict) -> float:
+    """100 per simplex octave + 64 per component evaluation + 32 per sample + 18 per gate."""
+    return 100.0 * cnt["octaves"] + 64.0 * cnt["comp_evals"] + 32.0 * cnt["samples"] + 18.0 * cnt["gates"]
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.idx, self.rows, self.proc = gpu_index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                                          "-i", str(self.idx)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self) -> dict:
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        self.t.join(timeout=2)
+        sm = [float(r[1]) for r in self.rows if len(r) >= 9 and r[1].replace(".", "").isdigit()]
+        mx = [float(r[2]) for r in self.rows if len(r) >= 9 and r[2].replace(".", "").isdigit()]
+        reasons = set()
+        for r in self.rows:
+            if len(r) < 9:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        busy = sorted(s for s in sm if s > 0.5 * max(sm)) if sm else []
+        return {"sm_mhz": busy[len(busy) // 2] if busy else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return json.load(open(p)), "measured"
+    return {"hbm_gbs": 6650.0, "sm_max_mhz": 1965.0}, "fallback"
+
+
+def cpu_sample_scene(workload: str, row_stride: int):
+    """Bounded sample of frame 0 of the workload for the CPU legs: every row_stride-th image row."""
+    sc = make_scene(workload, 0)
+    n = sc.frame.full_size
+    return sc.tile(0, 0, n, n // row_stride, band_rows=1, band_stride=row_stride)
+
+
+def time_cpu(workload: str, row_stride: int, repeats: int = 1):
+    """Times the CPU oracle built with the reference's own flags (-Ofast -march=native -fopenmp,
+    gamer.pro:13,20,23) on all host threads. Returns (samples/s, cores, sample description, seconds)."""
+    import oracle_lib
+    o = oracle_lib.load(fast=True)
+    sc = cpu_sample_scene(workload, row_stride)
+    best, samples = None, 0
+    for _ in range(repeats):
+        t0 = time.perf_counter()
+        _, cnt = o.render(sc)
+        dt = time.perf_counter() - t0
+        samples = cnt["samples"]
+        best = dt if best is None else min(best, dt)
+    desc = (f"frame 0 of {workload}, every {row_stride}th row ({sc.frame.height} of {sc.frame.full_size} rows, "
+            f"{samples} ray samples), pixel loop only, best of {repeats}")
+    return samples / best, o.max_threads(), desc, best
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from gamer_b200.rasterizer import Context
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    ctx = Context([local])
+    K, Wm = args.steps, args.warmup
+    wl = args.workload
+    size = WORKLOADS[wl][1]
+    frames = [s * world + rank for s in range(Wm + K)]
+    scenes_ = [make_scene(wl, f) for f in frames]
+
+    # exact work of every timed frame (instrumented kernel, outside the timed region)
+    counts = []
+    for sc in scenes_[Wm:]:
+        ctx.upload(sc)
+        counts.append(ctx.render_counted())
+    my_samples = sum(c["samples"] for c in counts)
+    my_flop = sum(algorithmic_flop(c) for c in counts)
+
+    stream = torch.cuda.ExternalStream(ctx.stream(0), device=torch.device("cuda", local))
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")       # > 126 MB L2
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+
+    def step_device(i, timed_idx=None):
+        ctx.upload(scenes_[i])                      # host-side: scene -> kernel parameter block
+        with torch.cuda.stream(stream):
+            flush.zero_()
+            if timed_idx is not None:
+                ev[timed_idx][0].record(stream)
+            ctx.render_device()                     # K1
+            ctx.tonemap_device(1.0, 1.0, 1.0)       # K2
+            if timed_idx is not None:
+                ev[timed_idx][1].record(stream)
+
+    for i in range(Wm):
+        step_device(i)
+    clocks = ClockSampler(local)
+    barrier()
+    if rank == 0:
+        clocks.start()
+    l0 = ctx.launches()
+    k1_ms, k2_ms = [], []
+    t_wall0 = time.perf_counter()
+    for k in range(K):
+        step_device(Wm + k, k)
+        a, b = ctx.kernel_ms()
+        k1_ms.append(a)
+        k2_ms.append(b)
+    barrier()
+    t_wall = time.perf_counter() - t_wall0
+    launches = ctx.launches() - l0
+    clk = clocks.stop() if rank == 0 else None
+    dev_ms = sum(e0.elapsed_time(e1) for e0, e1 in ev)
+
+    # ---- e2e: host buffers through the C ABI (upload + K1 + D2H float frame + K2 + D2H 8-bit image) ----
+    host_rgb = torch.empty((size, size, 3), dtype=torch.float32, pin_memory=True)
+    host_img = torch.empty((size, size), dtype=torch.int32, pin_memory=True)
+
+    def step_e2e(i):
+        ctx.upload(scenes_[i])
+        ctx.render_ptr(host_rgb.data_ptr())
+        ctx.tonemap_ptr(1.0, 1.0, 1.0, None, host_img.data_ptr())
+
+    for i in range(min(Wm, 3)):
+        step_e2e(i)
+    barrier()
+    t0 = time.perf_counter()
+    for k in range(K):
+        step_e2e(Wm + k)
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    checksum = float(host_rgb[::64, ::64].double().sum())
+
+    # ---- K2 alone, cold L2, for its HBM roofline ----
+    k2_cold = []
+    for _ in range(5):
+        with torch.cuda.stream(stream):
+            flush.zero_()
+        ctx.tonemap_device(1.0, 1.0, 1.0)
+        k2_cold.append(ctx.kernel_ms()[1])
+
+    # ---- reduce over ranks: time = max, work = sum ----
+    t = torch.tensor([dev_ms, e2e_s * 1e3, t_wall * 1e3], dtype=torch.float64, device="cuda")
+    w = torch.tensor([float(my_samples), my_flop, float(launches)], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(w, op=dist.ReduceOp.SUM)
+    dev_ms_max, e2e_ms_max, wall_ms_max = t.tolist()
+    tot_samples, tot_flop, tot_launches = w.tolist()
+
+    if rank == 0:
+        peaks, peak_src = measured_peaks()
+        sm_count = torch.cuda.get_device_properties(local).multi_processor_count
+        sm_max = float(peaks.get("sm_max_mhz", 1965.0))
+        fp32_peak = sm_count * FP32_LANES_PER_SM * 2 * sm_max * 1e6 / 1e12
+        k1_avg_ms = sum(k1_ms) / len(k1_ms)
+        k1_tflops = (my_flop / K) / (k1_avg_ms * 1e-3) / 1e12
+        px = size * size
+        k2_best = min(k2_cold)
+        k2_bytes = px * (12 + 4 + 4)
+        out = {
+            "metric": METRIC, "value": tot_samples / (dev_ms_max * 1e-3), "unit": UNIT, "n_gpus": world,
+            "steps": K, "warmup": Wm, "ms_per_step": dev_ms_max / K, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": wl, "galaxy": WORKLOADS[wl][0] + ".gax (tests/golden/gax)", "size": size,
+                       "ray_step": "0.025f", "frames_per_step": world, "parallelism": f"frames x{world}",
+                       "l2": "256 MB device buffer zeroed between timed iterations (outside the event bracket); "
+                             "inputs are a few KB of scene parameters",
+                       "ray_samples_per_frame": my_samples / K, "octaves_per_frame": sum(c["octaves"] for c in counts) / K},
+            "gpu_launches": int(tot_launches),
+            "e2e": {"value": tot_samples / (e2e_ms_max * 1e-3), "unit": UNIT,
+                    "h2d_bytes_per_step": world * ctx_scene_bytes(scenes_[0]), "d2h_bytes_per_step": world * px * 16,
+                    "ms_per_step": e2e_ms_max / K, "checksum": checksum},
+            "roofline": {"kernel": "k1_march", "bound": "fp32", "achieved": k1_tflops, "peak": fp32_peak, "unit": "TFLOP/s",
+                         "frac": k1_tflops / fp32_peak, "traffic": None,
+                         "peak_source": f"{sm_count} SMs x 128 FP32 lanes x 2 flop x {sm_max:.0f} MHz (sm_max_mhz of "
+                                        f"MEASURED_PEAKS.json, {peak_src}); the path is FP32/SFU-pipe bound, not HBM or tensor",
+                         "algorithmic_flop_per_launch": my_flop / K, "launch_ms": k1_avg_ms},
+            "roofline_k2": {"kernel": "k2_tonemap", "bound": "hbm", "achieved": k2_bytes / (k2_best * 1e-3) / 1e9,
+                            "peak": float(peaks.get("hbm_gbs", 6650.0)), "unit": "GB/s",
+                            "frac": k2_bytes / (k2_best * 1e-3) / 1e9 / float(peaks.get("hbm_gbs", 6650.0)),
+                            "traffic": None, "algorithmic_bytes_per_launch": k2_bytes, "launch_ms": k2_best,
+                            "peak_source": f"hbm_gbs of MEASURED_PEAKS.json ({peak_src})"},
+            "kernel_ms": {"k1_avg": k1_avg_ms, "k2_avg_in_step": sum(k2_ms) / len(k2_ms), "k2_cold_l2": k2_best,
+                          "wall_ms_per_step_incl_flush": wall_ms_max / K},
+            "clocks": clk,
+        }
+        if world == 1 and not args.no_cpu:
+            v, cores, desc, secs = time_cpu(wl, args.cpu_row_stride)
+            out["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": desc, "seconds": secs}
+        print(json.dumps(out), flush=True)
+    ctx.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def ctx_scene_bytes(scene) -> int:
+    import ctypes as C
+    return C.sizeof(scene.frame) + C.sizeof(scene.galaxies) + C.sizeof(scene.components)
+
+
+def run_reference(args):
+    """Reference arm: the reference's CPU implementation of the path on the host cores. The reference
+    itself cannot be built here (Qt headers absent), so this times the oracle port
+    compiled with the reference's own flags, all host threads, on a bounded sample of the same workload."""
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if rank != 0:
+        return
+    import oracle_lib
+    o = oracle_lib.load(fast=True)
+    wl = args.workload
+    sc = cpu_sample_scene(wl, args.ref_row_stride)
+    times, samples = [], 0
+    for i in range(args.warmup + args.steps):
+        t0 = time.perf_counter()
+        _, cnt = o.render(sc)
+        dt = time.perf_counter() - t0
+        samples = cnt["samples"]
+        if i >= args.warmup:
+            times.append(dt)
+    total = sum(times)
+    value = samples * len(times) / total
+    size = WORKLOADS[wl][1]
+    frac = sc.frame.height / sc.frame.full_size
+    desc = (f"each step = every {args.ref_row_stride}th row of frame 0 of {wl} ({sc.frame.height} of {size} rows, {samples} "
+            f"ray samples); a whole frame is ~{1 / frac:.0f}x that")
+    out = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+           "warmup": args.warmup, "ms_per_step": 1e3 * total / len(times), "higher_is_better": True, "scaling": "weak",
+           "vs_baseline": None, "dtype": "f64/f32 (reference mix)", "data": "synthetic",
+           "config": {"workload": wl, "galaxy": WORKLOADS[wl][0] + ".gax (tests/golden/gax)", "size": size, "ray_step": "0.025f",
+                      "sample": desc, "est_ms_per_full_frame": 1e3 * total / len(times) / frac},
+           "cpu_baseline": {"value": value, "unit": UNIT, "cores": o.max_threads(), "kind": "port", "sample": desc},
+           "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+           "gpu_launches": 0}
+    print(json.dumps(out), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="spiral_2048_oblique_orbit", choices=list(WORKLOADS))
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--cpu-row-stride", type=int, default=16, help="cpu_baseline sample: every n-th row")
+    ap.add_argument("--ref-row-stride", type=int, default=64, help="--impl reference step: every n-th row")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+        return
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if world != args.gpus:
+        if world == 1 and args.gpus > 1:           # convenience: relaunch under torchrun
+            cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
+                   "--master-addr", "127.0.0.1", "--master-port", "29517", os.path.abspath(__file__)] + sys.argv[1:]
+            sys.exit(subprocess.call(cmd))
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
+    if args.warmup < 3:
+        args.warmup = 3
+    run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -48,7 +48,7 @@ SYMBOLS = [
     "gamer_b200_last_error", "gamer_b200_upload", "gamer_b200_render", "gamer_b200_render_device",
     "gamer_b200_render_counted", "gamer_b200_counters", "gamer_b200_tonemap", "gamer_b200_tonemap_device",
     "gamer_b200_progress", "gamer_b200_abort", "gamer_b200_device_buffers", "gamer_b200_last_kernel_ms",
-    "gamer_b200_launch_count", "gamer_b200_camera_inv_vp", "gamer_b200_rotation_to_orientation",
+    "gamer_b200_launch_count", "gamer_b200_stream", "gamer_b200_camera_inv_vp", "gamer_b200_rotation_to_orientation",
     "gamer_b200_host_alloc", "gamer_b200_host_free",
     "gamer_b200_probe_simplex", "gamer_b200_probe_fbm", "gamer_b200_probe_ridged",
 ]
@@ -90,6 +90,7 @@ def load():
     lib.gamer_b200_abort.argtypes = [p]
     lib.gamer_b200_device_buffers.argtypes = [p, C.c_int32, C.POINTER(p), C.POINTER(p), C.POINTER(p), C.POINTER(C.c_int32)]
     lib.gamer_b200_last_kernel_ms.argtypes = [p, C.POINTER(C.c_float), C.POINTER(C.c_float)]
+    lib.gamer_b200_stream.argtypes = [p, C.c_int32, C.POINTER(p)]
     lib.gamer_b200_launch_count.argtypes = [p, C.POINTER(C.c_uint64)]
     lib.gamer_b200_camera_inv_vp.argtypes = [C.POINTER(C.c_float), C.POINTER(C.c_float), C.POINTER(C.c_float), C.c_double,
                                              C.POINTER(C.c_float)]

@@ -402,6 +402,12 @@ int gamer_b200_device_buffers(gamer_ctx *ctx, int32_t which, void **rgb_dev, voi
     return GAMER_OK;
 }
 
+int gamer_b200_stream(gamer_ctx *ctx, int32_t which, void **stream_out) {
+    if (!ctx || !stream_out || which < 0 || which >= (int)ctx->devs.size()) return GAMER_E_ARG;
+    *stream_out = (void *)ctx->devs[which].st;
+    return GAMER_OK;
+}
+
 int gamer_b200_last_kernel_ms(gamer_ctx *ctx, float *k1_ms, float *k2_ms) {
     if (!ctx) return GAMER_E_ARG;
     if (k1_ms) *k1_ms = ctx->k1_ms;

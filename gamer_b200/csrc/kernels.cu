@@ -12,7 +12,6 @@ namespace {
 #define K1_BH 8
 
 struct NoiseCtx {
-    const char *tbl;
     uint32_t lane4;
 };
 
@@ -67,16 +66,22 @@ __device__ __forceinline__ float arm_value(const DGalaxy &g, const DComp &c, con
     return fpow(b, c.arm15);
 }
 
+// Bulge emission (galaxycomponents.cpp:5-18): rad = (|p|+0.01) r0 + 0.01; i = k (rad^-0.855 exp(-rad^0.25) - 0.05), i >= 0
+__device__ __forceinline__ void bulge_add(float k, float r0, float sr, float sg, float sb, float plen3,
+                                          float &Ir, float &Ig, float &Ib) {
+    float rad = fmaf(plen3 + 0.01f, r0, 0.01f);
+    float L = lg2a(rad);
+    float v = fmaf(ex2a(-0.855f * L), ex2a(-1.4426950408889634f * ex2a(0.25f * L)), -0.05f);
+    float i = fmaxf(k * v, 0.0f);
+    Ir = fmaf(i, sr, Ir); Ig = fmaf(i, sg, Ig); Ib = fmaf(i, sb, Ib);
+}
+
 template <bool COUNT>
 __device__ __forceinline__ void eval_component(const DScene &sc, const DGalaxy &g, const DComp &c, Shared1 &s,
                                                const NoiseCtx &nz, float &Ir, float &Ig, float &Ib, Counts &cn) {
     const float rs = sc.ray_step_f;
     if (c.cls == GAMER_CLASS_BULGE) {   // galaxycomponents.cpp:5-25 — evaluated at every sample, no gates
-        float rad = fmaf(s.plen3 + 0.01f, c.r0, 0.01f);
-        float L = lg2(rad);
-        float i = c.strength * s.weight * (ex2(-0.855f * L) * fexp(-ex2(0.25f * L)) - 0.05f) * c.iscale;
-        i = fmaxf(i, 0.0f) * rs;
-        Ir = fmaf(i, c.spec[0], Ir); Ig = fmaf(i, c.spec[1], Ig); Ib = fmaf(i, c.spec[2], Ib);
+        bulge_add(c.strength * c.iscale * rs * s.weight, c.r0, c.spec[0], c.spec[1], c.spec[2], s.plen3, Ir, Ig, Ib);
         if (COUNT) cn.evals++;
         return;
     }
@@ -116,7 +121,7 @@ __device__ __forceinline__ void eval_component(const DScene &sc, const DGalaxy &
     switch (c.cls) {
     case GAMER_CLASS_DISK: {            // galaxycomponents.cpp:41-59
         f3 r = twirl_qt(g.axis_n, s.p, winding);
-        float n = gnoise::fbm(nz.tbl, nz.lane4, r.x, r.y, r.z, c.nscale, 10, c.pers, c.inv_maxamp);
+        float n = gnoise::fbm(nz.lane4, r.x, r.y, r.z, c.nscale, 10, c.pers, c.inv_maxamp);
         if (COUNT) cn.octaves += 10;
         float p2 = fpow(fmaxf(fabsf(n), 0.01f), c.noise_tilt) + c.noise_offset;
         if (p2 < 0.0f) return;
@@ -126,7 +131,7 @@ __device__ __forceinline__ void eval_component(const DScene &sc, const DGalaxy &
     }
     case GAMER_CLASS_DUST: {            // galaxycomponents.cpp:64-84
         f3 r = twirl_qt(g.axis_n, s.p, winding);
-        float n = gnoise::fbm(nz.tbl, nz.lane4, r.x, r.y, r.z, c.nscale, 9, c.pers, c.inv_maxamp);
+        float n = gnoise::fbm(nz.lane4, r.x, r.y, r.z, c.nscale, 9, c.pers, c.inv_maxamp);
         if (COUNT) cn.octaves += 9;
         float p2 = fmaxf(n - c.noise_offset, 0.0f);
         p2 = (p2 > 0.0f) ? fpow(5.0f * p2, c.noise_tilt) : (c.noise_tilt > 0.0f ? 0.0f : (c.noise_tilt == 0.0f ? 1.0f : 10.0f));
@@ -138,7 +143,7 @@ __device__ __forceinline__ void eval_component(const DScene &sc, const DGalaxy &
     case GAMER_CLASS_DUST2:             // galaxycomponents.cpp:85-114
     case GAMER_CLASS_DUST_POSITIVE: {   // galaxycomponents.cpp:116-136
         f3 r = twirl_qt(g.axis_n, s.p, winding);
-        float p2 = gnoise::ridged(nz.tbl, nz.lane4, __fmul_rn(r.x, c.rscale), __fmul_rn(r.y, c.rscale),
+        float p2 = gnoise::ridged(nz.lane4, __fmul_rn(r.x, c.rscale), __fmul_rn(r.y, c.rscale),
                                   __fmul_rn(r.z, c.rscale), DEV_RIDGED_OCTAVES, 2.5f, c.noise_offset, c.noise_tilt, c.rw);
         if (COUNT) cn.octaves += DEV_RIDGED_OCTAVES;
         p2 = fmaxf(p2, 0.0f);
@@ -152,14 +157,14 @@ __device__ __forceinline__ void eval_component(const DScene &sc, const DGalaxy &
         break;
     }
     case GAMER_CLASS_STARS: {           // galaxycomponents.cpp:139-155
-        float n = fabsf(gnoise::fbm(nz.tbl, nz.lane4, s.p.x, s.p.y, s.p.z, c.nscale, 10, c.pers, c.inv_maxamp));
+        float n = fabsf(gnoise::fbm(nz.lane4, s.p.x, s.p.y, s.p.z, c.nscale, 10, c.pers, c.inv_maxamp));
         if (COUNT) cn.octaves += 10;
         float add = 0.0f;
         if (c.flags & DC_HAS_NOFF) {    // two 4-octave helpers, persistence -2: amplitudes 1,-2,4,-8, sum -5
             f3 r1 = twirl_qt(g.axis_n, s.p, winding);
             f3 r2 = twirl_qt(g.axis_n, s.p, __dmul_rn(winding, 0.5));
-            add = c.noise_offset * gnoise::fbm(nz.tbl, nz.lane4, r1.x, r1.y, r1.z, 2.0 * (double)0.1f, 4, -2.0f, -0.2f);
-            add += 0.5f * (c.noise_offset * gnoise::fbm(nz.tbl, nz.lane4, r2.x, r2.y, r2.z, 4.0 * (double)0.1f, 4, -2.0f, -0.2f));
+            add = c.noise_offset * gnoise::fbm(nz.lane4, r1.x, r1.y, r1.z, 2.0 * (double)0.1f, 4, -2.0f, -0.2f);
+            add += 0.5f * (c.noise_offset * gnoise::fbm(nz.lane4, r2.x, r2.y, r2.z, 4.0 * (double)0.1f, 4, -2.0f, -0.2f));
             if (COUNT) cn.octaves += 8;
         }
         float base = n + 1.0f + add;
@@ -175,7 +180,12 @@ __device__ __forceinline__ void eval_component(const DScene &sc, const DGalaxy &
     }
 }
 
-// Rasterizer::getIntensity (rasterizer.cpp:422-483) for one galaxy
+// Rasterizer::getIntensity (rasterizer.cpp:422-483) for one galaxy.
+// Control arithmetic is exact (see march.cuh). The loop test `dot(p-origin,ll) < length + step`
+// compares a float with a double; for a float d and double L, d < L  <=>  d < round_up_to_float(L),
+// so the bound is kept as a float that is refreshed only when the step length changes. Samples
+// outside every component's slab (|dott| > max h_gate: ~90 % of an exterior view) take a short path
+// that evaluates only the bulges, whose parameters sit in registers.
 template <bool COUNT>
 __device__ __forceinline__ void march(const DScene &sc, const DGalaxy &g, f3 isp1, f3 isp2, f3 camrel,
                                       const NoiseCtx &nz, float &Ir, float &Ig, float &Ib, Counts &cn) {
@@ -185,34 +195,63 @@ __device__ __forceinline__ void march(const DScene &sc, const DGalaxy &g, f3 isp
     const f3 dir = v_normalized(dseg);
     const f3 ll = v_normalized(v_sub(isp2, origin));
     const f3 orient = {g.orient[0], g.orient[1], g.orient[2]};
-    const float step_hi = 0.01f * 1.00001f, step_lo = (float)sc.min_ray_step * 0.99999f;
-    double step = sc.ray_step;
+    // the two clamped step states (rasterizer.cpp:449): step = 0.01 and step = minRayStep
+    const float thr_hi = __double2float_ru(__dadd_rn(length, 0.01));
+    const float thr_lo = __double2float_ru(__dadd_rn(length, sc.min_ray_step));
+    const f3 dstep_hi = v_mul(dir, __double2float_rn(0.01));
+    const f3 dstep_lo = v_mul(dir, __double2float_rn(sc.min_ray_step));
+    const float w_hi = (float)(0.01 * 200.0), w_lo = (float)(sc.min_ray_step * 200.0);
+    float thr = __double2float_ru(__dadd_rn(length, sc.ray_step));     // the first test uses step = rayStep
+    // bulges of this galaxy in registers (fast path)
+    const bool fast_ok = g.fast_ok != 0;
+    float bk0 = 0.f, br0 = 0.f, bs0r = 0.f, bs0g = 0.f, bs0b = 0.f, bk1 = 0.f, br1 = 0.f, bs1r = 0.f, bs1g = 0.f, bs1b = 0.f;
+    if (g.n_bulge > 0) {
+        const DComp &c = sc.comp[g.bulge_idx[0]];
+        bk0 = c.strength * c.iscale * sc.ray_step_f; br0 = c.r0; bs0r = c.spec[0]; bs0g = c.spec[1]; bs0b = c.spec[2];
+    }
+    if (g.n_bulge > 1) {
+        const DComp &c = sc.comp[g.bulge_idx[1]];
+        bk1 = c.strength * c.iscale * sc.ray_step_f; br1 = c.r0; bs1r = c.spec[0]; bs1g = c.spec[1]; bs1b = c.spec[2];
+    }
     f3 p = origin;
     if (COUNT) cn.rays++;
-    while ((double)v_dot(v_sub(p, origin), ll) < __dadd_rn(length, step)) {
-        // step = clamp(|p - camera| * rayStep, minRayStep, 0.01)   (rasterizer.cpp:449)
-        f3 dc = v_sub(p, camrel);
-        float est = sqrtf(fmaf(dc.z, dc.z, fmaf(dc.y, dc.y, dc.x * dc.x))) * sc.ray_step_f;
-        if (est > step_hi) step = 0.01;
-        else if (est < step_lo) step = sc.min_ray_step;
+    while (v_dot(v_sub(p, origin), ll) < thr) {
+        // step = clamp(|p - camera| * rayStep, minRayStep, 0.01)
+        const f3 dc = v_sub(p, camrel);
+        const float e2 = fmaf(dc.z, dc.z, fmaf(dc.y, dc.y, dc.x * dc.x));
+        f3 dstep;
+        float weight;
+        if (e2 > sc.est2_hi) { dstep = dstep_hi; weight = w_hi; thr = thr_hi; }
+        else if (e2 < sc.est2_lo) { dstep = dstep_lo; weight = w_lo; thr = thr_lo; }
         else {
             double v = __dmul_rn((double)v_length(dc), sc.ray_step);
             v = (v < 0.01) ? v : 0.01;
-            step = (sc.min_ray_step < v) ? v : sc.min_ray_step;
+            const double step = (sc.min_ray_step < v) ? v : sc.min_ray_step;
+            dstep = v_mul(dir, __double2float_rn(step));
+            weight = (float)(step * 200.0);
+            thr = __double2float_ru(__dadd_rn(length, step));
         }
-        Shared1 s;
-        s.p = p;
-        s.dott = v_dot(p, orient);                       // getRadius (galaxycomponent.h:72-76)
-        s.P = v_sub(p, v_mul(orient, s.dott));
-        s.Plen = sqrtf(fmaf(s.P.z, s.P.z, fmaf(s.P.y, s.P.y, s.P.x * s.P.x)));
-        s.plen3 = sqrtf(fmaf(p.z, p.z, fmaf(p.y, p.y, p.x * p.x)));
-        s.weight = (float)(step * 200.0);
-        s.have_arm = false;
+        const float dott = v_dot(p, orient);                         // getRadius (galaxycomponent.h:72-76)
+        const float plen3 = sqrta(fmaf(p.z, p.z, fmaf(p.y, p.y, p.x * p.x)));
+        if (fast_ok && !(fabsf(dott) <= g.slab_gate)) {
+            bulge_add(bk0 * weight, br0, bs0r, bs0g, bs0b, plen3, Ir, Ig, Ib);
+            if (g.n_bulge > 1) bulge_add(bk1 * weight, br1, bs1r, bs1g, bs1b, plen3, Ir, Ig, Ib);
+            if (COUNT) cn.evals += g.n_bulge;
+        } else {
+            Shared1 s;
+            s.p = p;
+            s.dott = dott;
+            s.P = v_sub(p, v_mul(orient, dott));
+            s.Plen = sqrta(fmaf(s.P.z, s.P.z, fmaf(s.P.y, s.P.y, s.P.x * s.P.x)));
+            s.plen3 = plen3;
+            s.weight = weight;
+            s.have_arm = false;
 #pragma unroll 1
-        for (int k = 0; k < g.comp_count; k++)
-            eval_component<COUNT>(sc, g, sc.comp[g.comp_begin + k], s, nz, Ir, Ig, Ib, cn);
+            for (int k = 0; k < g.comp_count; k++)
+                eval_component<COUNT>(sc, g, sc.comp[g.comp_begin + k], s, nz, Ir, Ig, Ib, cn);
+        }
         if (COUNT) { cn.samples++; cn.gates += g.comp_count + g.noop_count; }
-        p = v_sub(p, v_mul(dir, __double2float_rn(step)));
+        p = v_sub(p, dstep);
         Ir = fmaxf(0.0f, Ir); Ig = fmaxf(0.0f, Ig); Ib = fmaxf(0.0f, Ib);   // Util::floor (util.h:62-64)
     }
 }
@@ -226,8 +265,7 @@ template <bool COUNT>
 __global__ void __launch_bounds__(K1_THREADS)
 k1_march(const __grid_constant__ DScene sc, float *__restrict__ out, unsigned long long *__restrict__ counters,
          const volatile int *abort_flag, unsigned int *progress) {
-    __shared__ __align__(128) uint32_t s_tbl[GN_TABLE_WORDS];
-    gnoise::table_init(s_tbl);
+    gnoise::table_init();
     __syncthreads();
     if (*abort_flag) return;            // rasterizer.cpp:296-297: skipped pixels keep their old value
 
@@ -235,7 +273,6 @@ k1_march(const __grid_constant__ DScene sc, float *__restrict__ out, unsigned lo
     const int lx = blockIdx.x * K1_BW + (warp & 3) * 8 + (lane & 7);
     const int ly = blockIdx.y * K1_BH + (warp >> 2) * 4 + (lane >> 3);
     NoiseCtx nz;
-    nz.tbl = reinterpret_cast<const char *>(s_tbl);
     nz.lane4 = (uint32_t)lane << 2;
     Counts cn = {0, 0, 0, 0, 0};
 
@@ -325,22 +362,20 @@ k2_tonemap(const float *__restrict__ rgb, const float *__restrict__ stars, uint3
 // ---- probes: the same device noise functions, one point per thread ----------------------------------
 __global__ void __launch_bounds__(256)
 kp_simplex(const float *__restrict__ xyz, int n, double frequency, int32_t *__restrict__ lat_out, float *__restrict__ val_out) {
-    __shared__ __align__(128) uint32_t s_tbl[GN_TABLE_WORDS];
-    gnoise::table_init(s_tbl);
+    gnoise::table_init();
     __syncthreads();
     int q = blockIdx.x * blockDim.x + threadIdx.x;
     if (q >= n) return;
-    const char *tbl = reinterpret_cast<const char *>(s_tbl);
     uint32_t lane4 = (threadIdx.x & 31) << 2;
     gnoise::Skewed su, sv, sw;
     gnoise::skew(__dmul_rn((double)xyz[3 * q], frequency), __dmul_rn((double)xyz[3 * q + 1], frequency),
                  __dmul_rn((double)xyz[3 * q + 2], frequency), su, sv, sw);
     gnoise::Lattice L;
     float fu, fv, fw;
-    gnoise::cell_of(su, 0, L.i, fu);
-    gnoise::cell_of(sv, 0, L.j, fv);
-    gnoise::cell_of(sw, 0, L.k, fw);
-    float v = gnoise::simplex_cell<true>(tbl, lane4, L.i, L.j, L.k, fu, fv, fw, &L);
+    gnoise::cell_of<true>(su, 0, L.i, fu);
+    gnoise::cell_of<true>(sv, 0, L.j, fv);
+    gnoise::cell_of<true>(sw, 0, L.k, fw);
+    float v = gnoise::simplex_cell<true>(lane4, L.i, L.j, L.k, fu, fv, fw, &L);
     if (val_out) val_out[q] = v;
     if (lat_out) {
         int32_t *o = lat_out + 10 * (size_t)q;
@@ -351,12 +386,11 @@ kp_simplex(const float *__restrict__ xyz, int n, double frequency, int32_t *__re
 
 __global__ void __launch_bounds__(256)
 kp_fbm(const float *__restrict__ xyz, int n, int octaves, float pers, float inv_maxamp, double scale, float *__restrict__ out) {
-    __shared__ __align__(128) uint32_t s_tbl[GN_TABLE_WORDS];
-    gnoise::table_init(s_tbl);
+    gnoise::table_init();
     __syncthreads();
     int q = blockIdx.x * blockDim.x + threadIdx.x;
     if (q >= n) return;
-    out[q] = gnoise::fbm(reinterpret_cast<const char *>(s_tbl), (threadIdx.x & 31) << 2, xyz[3 * q], xyz[3 * q + 1],
+    out[q] = gnoise::fbm((threadIdx.x & 31) << 2, xyz[3 * q], xyz[3 * q + 1],
                          xyz[3 * q + 2], scale, octaves, pers, inv_maxamp);
 }
 
@@ -364,12 +398,11 @@ struct RidgedW { float w[16]; };
 __global__ void __launch_bounds__(256)
 kp_ridged(const float *__restrict__ xyz, int n, int octaves, float lac, float offset, float gain, RidgedW rw,
           float *__restrict__ out) {
-    __shared__ __align__(128) uint32_t s_tbl[GN_TABLE_WORDS];
-    gnoise::table_init(s_tbl);
+    gnoise::table_init();
     __syncthreads();
     int q = blockIdx.x * blockDim.x + threadIdx.x;
     if (q >= n) return;
-    out[q] = gnoise::ridged(reinterpret_cast<const char *>(s_tbl), (threadIdx.x & 31) << 2, xyz[3 * q], xyz[3 * q + 1],
+    out[q] = gnoise::ridged((threadIdx.x & 31) << 2, xyz[3 * q], xyz[3 * q + 1],
                             xyz[3 * q + 2], octaves, lac, offset, gain, rw.w);
 }
 

@@ -54,18 +54,22 @@ __host__ __device__ inline uint32_t grad_code(uint32_t g) {
 #define GN_TABLE_WORDS (256 * 32)
 #define GN_ADDR_MASK 0x7F80u
 
+// The replicated table is a file-scope static __shared__ array so that a lookup compiles to one LOP3
+// ((off & mask) | lane*4) and one LDS with the array base as the instruction's immediate offset.
+__shared__ __align__(128) uint32_t s_tbl[GN_TABLE_WORDS];
+
 // Fill the replicated table; call from all threads of the block, then __syncthreads().
-__device__ __forceinline__ void table_init(uint32_t *tbl) {
+__device__ __forceinline__ void table_init() {
     for (uint32_t w = threadIdx.x + threadIdx.y * blockDim.x; w < GN_TABLE_WORDS; w += blockDim.x * blockDim.y) {
         uint32_t e = w >> 5;
         uint32_t p = c_perm[e];
-        tbl[w] = (p << 7) | grad_code(p % 12u);
+        s_tbl[w] = (p << 7) | grad_code(p % 12u);
     }
 }
 
 // one level of the hash walk: entry ((off7 >> 7) & 255) of this lane's bank
-__device__ __forceinline__ uint32_t look(const char *tbl_bytes, uint32_t lane4, uint32_t off7) {
-    return *reinterpret_cast<const uint32_t *>(tbl_bytes + ((off7 & GN_ADDR_MASK) | lane4));
+__device__ __forceinline__ uint32_t look(uint32_t lane4, uint32_t off7) {
+    return *reinterpret_cast<const uint32_t *>(reinterpret_cast<const char *>(s_tbl) + ((off7 & GN_ADDR_MASK) | lane4));
 }
 
 // ±a ± b from a table entry
@@ -96,12 +100,14 @@ __device__ __forceinline__ Skewed to_fixed(double u) {
     return s;
 }
 
-// integer cell and in-cell fraction of octave k (skewed coordinate 2^k * u)
+// integer cell and in-cell fraction of octave k (skewed coordinate 2^k * u). CHECK: also handle the
+// reference's fastfloor quirk; callers hoist the (almost never true) need for it out of their loops.
+template <bool CHECK>
 __device__ __forceinline__ void cell_of(const Skewed &s, int k, int &cell, float &frac) {
     uint32_t lo = s.lo << k;
     cell = (int)__funnelshift_l(s.lo, (uint32_t)s.hi, k);
     frac = __uint2float_rn(lo) * 2.3283064365386963e-10f;
-    if (lo == 0u) {   // rare: looks like an exact integer in fixed point
+    if (CHECK && lo == 0u) {   // rare: looks like an exact integer in fixed point
         double uk = s.d * (double)(1u << k);
         if (uk <= 0.0 && uk == rint(uk)) {   // simplexnoise.h:130 fastfloor: (int)x - 1 for exact x <= 0
             cell -= 1;
@@ -112,7 +118,7 @@ __device__ __forceinline__ void cell_of(const Skewed &s, int k, int &cell, float
 
 // One raw simplex value from cells (ci,cj,ck) and fractions (fu,fv,fw).  Returns 32*(n0+n1+n2+n3).
 template <bool PROBE>
-__device__ __forceinline__ float simplex_cell(const char *tbl, uint32_t lane4, int ci, int cj, int ck,
+__device__ __forceinline__ float simplex_cell(uint32_t lane4, int ci, int cj, int ck,
                                               float fu, float fv, float fw, Lattice *lat) {
     const float G3 = 1.0f / 6.0f;
     float t = (fu + fv + fw) * G3;
@@ -130,15 +136,15 @@ __device__ __forceinline__ float simplex_cell(const char *tbl, uint32_t lane4, i
 
     // hash walk: perm[ii+oi+perm[jj+oj+perm[kk+ok]]], offsets pre-scaled by 128
     uint32_t K7 = (uint32_t)ck << 7, J7 = (uint32_t)cj << 7, I7 = (uint32_t)ci << 7;
-    uint32_t A0 = look(tbl, lane4, K7), A1 = look(tbl, lane4, K7 + 128u);
-    uint32_t B0 = look(tbl, lane4, A0 + J7);
-    uint32_t B1 = look(tbl, lane4, (k1 ? A1 : A0) + J7 + (j1 ? 128u : 0u));
-    uint32_t B2 = look(tbl, lane4, (k2 ? A1 : A0) + J7 + (j2 ? 128u : 0u));
-    uint32_t B3 = look(tbl, lane4, A1 + J7 + 128u);
-    uint32_t C0 = look(tbl, lane4, B0 + I7);
-    uint32_t C1 = look(tbl, lane4, B1 + I7 + (i1 ? 128u : 0u));
-    uint32_t C2 = look(tbl, lane4, B2 + I7 + (i2 ? 128u : 0u));
-    uint32_t C3 = look(tbl, lane4, B3 + I7 + 128u);
+    uint32_t A0 = look(lane4, K7), A1 = look(lane4, K7 + 128u);
+    uint32_t B0 = look(lane4, A0 + J7);
+    uint32_t B1 = look(lane4, (k1 ? A1 : A0) + J7 + (j1 ? 128u : 0u));
+    uint32_t B2 = look(lane4, (k2 ? A1 : A0) + J7 + (j2 ? 128u : 0u));
+    uint32_t B3 = look(lane4, A1 + J7 + 128u);
+    uint32_t C0 = look(lane4, B0 + I7);
+    uint32_t C1 = look(lane4, B1 + I7 + (i1 ? 128u : 0u));
+    uint32_t C2 = look(lane4, B2 + I7 + (i2 ? 128u : 0u));
+    uint32_t C3 = look(lane4, B3 + I7 + 128u);
 
     float t0 = fmaxf(0.6f - x0 * x0 - y0 * y0 - z0 * z0, 0.0f);
     float t1 = fmaxf(0.6f - x1 * x1 - y1 * y1 - z1 * z1, 0.0f);
@@ -167,21 +173,39 @@ __device__ __forceinline__ void skew(double x, double y, double z, Skewed &su, S
     sw = to_fixed(__dadd_rn(z, s));
 }
 
+// one octave: cells/fractions of (2^k u, 2^k v, 2^k w) and the raw simplex value. `quirk` is a
+// per-call predicate (almost never true) that sends the point through the fastfloor-quirk check.
+__device__ __forceinline__ float octave(uint32_t lane4, const Skewed &su, const Skewed &sv, const Skewed &sw, int k, bool quirk) {
+    int ci, cj, ck;
+    float fu, fv, fw;
+    cell_of<false>(su, k, ci, fu);
+    cell_of<false>(sv, k, cj, fv);
+    cell_of<false>(sw, k, ck, fw);
+    if (quirk) {
+        cell_of<true>(su, k, ci, fu);
+        cell_of<true>(sv, k, cj, fv);
+        cell_of<true>(sw, k, ck, fw);
+    }
+    return simplex_cell<false>(lane4, ci, cj, ck, fu, fv, fw, nullptr);
+}
+
+// can an octave k <= kmax of this point hit an exact integer in fixed point? (needs the low 32-kmax bits zero)
+__device__ __forceinline__ bool maybe_integer(const Skewed &su, const Skewed &sv, const Skewed &sw, int kmax) {
+    const uint32_t m = 0xFFFFFFFFu >> kmax;
+    return ((su.lo & m) == 0u) | ((sv.lo & m) == 0u) | ((sw.lo & m) == 0u);
+}
+
 // Noise::octave_noise_3d (noise.cpp:162-180): sum_k raw(x f_k) a_k / sum a_k, f_k = scale 2^k, a_k = pers^k.
 // (px,py,pz) are the float coordinates the reference widens to double; scale is the double frequency.
-__device__ __forceinline__ float fbm(const char *tbl, uint32_t lane4, float px, float py, float pz, double scale,
+__device__ __forceinline__ float fbm(uint32_t lane4, float px, float py, float pz, double scale,
                                      int octaves, float pers, float inv_maxamp) {
     Skewed su, sv, sw;
     skew(__dmul_rn((double)px, scale), __dmul_rn((double)py, scale), __dmul_rn((double)pz, scale), su, sv, sw);
+    const bool quirk = maybe_integer(su, sv, sw, octaves - 1);
     float total = 0.0f, amp = 1.0f;
 #pragma unroll 1
     for (int k = 0; k < octaves; k++) {
-        int ci, cj, ck;
-        float fu, fv, fw;
-        cell_of(su, k, ci, fu);
-        cell_of(sv, k, cj, fv);
-        cell_of(sw, k, ck, fw);
-        total = fmaf(simplex_cell<false>(tbl, lane4, ci, cj, ck, fu, fv, fw, nullptr), amp, total);
+        total = fmaf(octave(lane4, su, sv, sw, k, quirk), amp, total);
         amp *= pers;
     }
     return total * inv_maxamp;
@@ -189,20 +213,15 @@ __device__ __forceinline__ float fbm(const char *tbl, uint32_t lane4, float px, 
 
 // Noise::getRidgedMf (noise.cpp:81-128). v is the float QVector3D (already r*scale); it is scaled by
 // float(lacunarity) per octave exactly like `vt = vt * lacunarity`. rw[o] = pow(frequency_o, -0.05f).
-__device__ __forceinline__ float ridged(const char *tbl, uint32_t lane4, float vx, float vy, float vz, int octaves,
+__device__ __forceinline__ float ridged(uint32_t lane4, float vx, float vy, float vz, int octaves,
                                         float lac, float offset, float gain, const float *rw) {
     float value = 0.0f, weight = 1.0f;
 #pragma unroll 1
     for (int o = 0; o < octaves; o++) {
         Skewed su, sv, sw;
         skew((double)vx, (double)vy, (double)vz, su, sv, sw);
-        int ci, cj, ck;
-        float fu, fv, fw;
-        cell_of(su, 0, ci, fu);
-        cell_of(sv, 0, cj, fv);
-        cell_of(sw, 0, ck, fw);
-        float signal = fabsf(simplex_cell<false>(tbl, lane4, ci, cj, ck, fu, fv, fw, nullptr));
-        signal = offset - signal;
+        float signal = octave(lane4, su, sv, sw, 0, maybe_integer(su, sv, sw, 0));
+        signal = offset - fabsf(signal);
         signal *= signal;
         signal *= weight;
         weight = fminf(fmaxf(signal * gain, 0.0f), 1.0f);

@@ -63,6 +63,11 @@ int gk_build_scene(const GamerFrame *f, const GamerGalaxy *gal, const GamerCompo
     s.ray_step_f = float(f->ray_step);
     s.min_ray_step = f->min_ray_step;
     s.final_mul = float(0.01);
+    {   // squared-distance bounds outside which clamp(|p-cam|*rayStep, min, 0.01) is certainly clamped
+        double hi = 0.01 * (1.0 + 2e-5) / f->ray_step, lo = f->min_ray_step * (1.0 - 2e-5) / f->ray_step;
+        s.est2_hi = float(hi * hi * (1.0 + 1e-6));
+        s.est2_lo = float(lo * lo * (1.0 - 1e-6));
+    }
 
     int nc = 0;
     for (int gi = 0; gi < f->n_galaxies; gi++) {
@@ -86,6 +91,8 @@ int gk_build_scene(const GamerFrame *f, const GamerGalaxy *gal, const GamerCompo
         d.winding_n = g.winding_n;
         d.no_arms = (g.no_arms == 1) ? 1 : (g.no_arms == 2) ? 2 : (g.no_arms == 3) ? 3 : 4;
         d.comp_begin = nc;
+        d.slab_gate = -1.0f;
+        d.n_bulge = 0;
         for (int k = 0; k < g.comp_count; k++) {
             const GamerComponent &c = comp[g.comp_begin + k];
             if (!(c.active == 1)) continue;                                   // rasterizer.cpp:458
@@ -121,6 +128,10 @@ int gk_build_scene(const GamerFrame *f, const GamerGalaxy *gal, const GamerCompo
             // slab gate (galaxycomponent.h:61-64): h = |height/z0|; h > 2 -> 0
             const double z0 = c.z0;
             q.h_gate = largest_passing([&](float a) { double h = std::fabs(double(a) / z0); return !(h > 2.0) && h == h; });
+            if (c.class_id == GAMER_CLASS_BULGE) {
+                if (d.n_bulge < 2) d.bulge_idx[d.n_bulge] = nc - 1;
+                d.n_bulge++;
+            } else if (q.h_gate > d.slab_gate) d.slab_gate = q.h_gate;
             // radial gate (galaxycomponent.h:72-81, galaxycomponent.cpp:58-65)
             const float ax = g.axis[0];
             const double r0h = c.r0 * 0.5f;
@@ -154,6 +165,7 @@ int gk_build_scene(const GamerFrame *f, const GamerGalaxy *gal, const GamerCompo
             for (int o = 0; o < DEV_RIDGED_OCTAVES; o++) { q.rw[o] = float(std::pow(freq, w)); freq *= 2.5; }
         }
         d.comp_count = nc - d.comp_begin;
+        d.fast_ok = d.n_bulge <= 2;
     }
     return GAMER_OK;
 }

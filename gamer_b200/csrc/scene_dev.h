@@ -64,6 +64,10 @@ struct DGalaxy {
     int32_t no_arms;         // 1,2,3 or 4 (anything else means 4: galaxycomponent.h:120-137)
     int32_t rot_identity;
     int32_t comp_begin, comp_count;   // ACTIVE components only, file order
+    int32_t n_bulge;                  // active bulges; the first two are also listed for the off-slab fast path
+    int32_t bulge_idx[2];
+    int32_t fast_ok;                  // n_bulge <= 2: off-slab samples may take the bulge-only path
+    float   slab_gate;                // max h_gate over the non-bulge components (-1 if none)
     int32_t noop_count;               // active "stars small" components: visited by the reference, no-op here
     int32_t _pad;
     double  winding_b, winding_n;     // getWinding is evaluated in double (its result feeds the twirl angle)
@@ -78,6 +82,7 @@ struct DScene {
     double  ray_step;
     double  min_ray_step;
     float   final_mul;       // float(0.01)
+    float   est2_hi, est2_lo; // |p-cam|^2 above / below which the step is certainly clamped to 0.01 / minRayStep
     float   _pad;
     DGalaxy gal[DEV_MAX_GALAXIES];
     DComp   comp[DEV_MAX_COMPONENTS];

@@ -92,6 +92,11 @@ class Context:
         _lib.check(self.h, self.lib.gamer_b200_launch_count(self.h, C.byref(n)))
         return n.value
 
+    def stream(self, which=0) -> int:
+        s = C.c_void_p()
+        _lib.check(self.h, self.lib.gamer_b200_stream(self.h, which, C.byref(s)))
+        return s.value
+
     def device_buffers(self, which=0):
         p = [C.c_void_p(), C.c_void_p(), C.c_void_p()]
         rows = C.c_int32()

@@ -157,6 +157,9 @@ int  gamer_b200_abort   (gamer_ctx *ctx);
  * ARGB images; rows_out = number of rows that device holds (its bands, in band order). */
 int  gamer_b200_device_buffers(gamer_ctx *ctx, int32_t which, void **rgb_dev, void **argb_dev,
                                void **argb_shadow_dev, int32_t *rows_out);
+/* The CUDA stream (cudaStream_t) device `which` of this context launches on, so a caller can order its
+ * own work (events, copies, collectives) with the kernels. */
+int  gamer_b200_stream(gamer_ctx *ctx, int32_t which, void **stream_out);
 /* CUDA-event time of the last K1 / K2 launch on device 0 (milliseconds). */
 int  gamer_b200_last_kernel_ms(gamer_ctx *ctx, float *k1_ms, float *k2_ms);
 /* number of kernel launches issued by this context since creation */
