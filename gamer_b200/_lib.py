@@ -7,7 +7,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libgamer_b200.so")
+LIB_PATH = os.environ.get("GAMER_B200_LIB") or os.path.join(_HERE, "lib", "libgamer_b200.so")   # env: A/B builds
 
 CNT_RAYS, CNT_SAMPLES, CNT_GATES, CNT_COMP_EVALS, CNT_OCTAVES, CNT_N = 0, 1, 2, 3, 4, 8
 E_ARG, E_CUDA, E_ABORTED, E_STATE = -1, -2, -3, -4

@@ -230,6 +230,7 @@ int gamer_b200_create(gamer_ctx **out, const int32_t *device_ids, int32_t n_devi
             gamer_b200_destroy(c);
             return set_err(nullptr, GAMER_E_CUDA, "device is not sm_100 (B200): kernels are built for sm_100a only");
         }
+        if (e == cudaSuccess) e = gk::prepare_device();
         if (e == cudaSuccess) { d.sm_count = prop.multiProcessorCount; e = cudaStreamCreateWithFlags(&d.st, cudaStreamNonBlocking); }
         if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&d.ctrl, cudaStreamNonBlocking);
         for (int k = 0; k < 4 && e == cudaSuccess; k++) e = cudaEventCreate(&d.ev[k]);

@@ -10,6 +10,9 @@ namespace {
 #define K1_THREADS 256   // 8 warps: 4 x 2 tiles of 8 x 4 pixels = a 32 x 8 pixel block
 #define K1_BW 32
 #define K1_BH 8
+#ifndef K1_MINBLOCKS
+#define K1_MINBLOCKS 2
+#endif
 
 struct NoiseCtx {
     uint32_t lane4;
@@ -262,7 +265,7 @@ __device__ __forceinline__ int image_row(const DScene &sc, int L) {
 }
 
 template <bool COUNT>
-__global__ void __launch_bounds__(K1_THREADS)
+__global__ void __launch_bounds__(K1_THREADS, K1_MINBLOCKS)
 k1_march(const __grid_constant__ DScene sc, float *__restrict__ out, unsigned long long *__restrict__ counters,
          const volatile int *abort_flag, unsigned int *progress) {
     gnoise::table_init();
@@ -273,7 +276,7 @@ k1_march(const __grid_constant__ DScene sc, float *__restrict__ out, unsigned lo
     const int lx = blockIdx.x * K1_BW + (warp & 3) * 8 + (lane & 7);
     const int ly = blockIdx.y * K1_BH + (warp >> 2) * 4 + (lane >> 3);
     NoiseCtx nz;
-    nz.lane4 = (uint32_t)lane << 2;
+    nz.lane4 = gnoise::lane_const();
     Counts cn = {0, 0, 0, 0, 0};
 
     if (lx < sc.width && ly < sc.height) {
@@ -366,7 +369,7 @@ kp_simplex(const float *__restrict__ xyz, int n, double frequency, int32_t *__re
     __syncthreads();
     int q = blockIdx.x * blockDim.x + threadIdx.x;
     if (q >= n) return;
-    uint32_t lane4 = (threadIdx.x & 31) << 2;
+    uint32_t lane4 = gnoise::lane_const();
     gnoise::Skewed su, sv, sw;
     gnoise::skew(__dmul_rn((double)xyz[3 * q], frequency), __dmul_rn((double)xyz[3 * q + 1], frequency),
                  __dmul_rn((double)xyz[3 * q + 2], frequency), su, sv, sw);
@@ -390,7 +393,7 @@ kp_fbm(const float *__restrict__ xyz, int n, int octaves, float pers, float inv_
     __syncthreads();
     int q = blockIdx.x * blockDim.x + threadIdx.x;
     if (q >= n) return;
-    out[q] = gnoise::fbm((threadIdx.x & 31) << 2, xyz[3 * q], xyz[3 * q + 1],
+    out[q] = gnoise::fbm(gnoise::lane_const(), xyz[3 * q], xyz[3 * q + 1],
                          xyz[3 * q + 2], scale, octaves, pers, inv_maxamp);
 }
 
@@ -402,7 +405,7 @@ kp_ridged(const float *__restrict__ xyz, int n, int octaves, float lac, float of
     __syncthreads();
     int q = blockIdx.x * blockDim.x + threadIdx.x;
     if (q >= n) return;
-    out[q] = gnoise::ridged((threadIdx.x & 31) << 2, xyz[3 * q], xyz[3 * q + 1],
+    out[q] = gnoise::ridged(gnoise::lane_const(), xyz[3 * q], xyz[3 * q + 1],
                             xyz[3 * q + 2], octaves, lac, offset, gain, rw.w);
 }
 
@@ -411,12 +414,22 @@ kp_ridged(const float *__restrict__ xyz, int n, int octaves, float lac, float of
 // ---- launchers (host) -----------------------------------------------------------------------------
 namespace gk {
 
+// kernels that use the noise table need > 48 KB of dynamic shared memory: opt in once per device
+cudaError_t prepare_device() {
+    cudaError_t e = cudaFuncSetAttribute(k1_march<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GN_DYN_SMEM);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k1_march<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GN_DYN_SMEM);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(kp_simplex, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GN_DYN_SMEM);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(kp_fbm, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GN_DYN_SMEM);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(kp_ridged, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GN_DYN_SMEM);
+    return e;
+}
+
 cudaError_t launch_k1(const DScene &sc, float *out_dev, unsigned long long *counters_dev, const int *abort_dev,
                       unsigned int *progress_dev, bool counted, cudaStream_t st, unsigned int *n_blocks) {
     dim3 grid((sc.width + K1_BW - 1) / K1_BW, (sc.height + K1_BH - 1) / K1_BH);
     if (n_blocks) *n_blocks = grid.x * grid.y;
-    if (counted) k1_march<true><<<grid, K1_THREADS, 0, st>>>(sc, out_dev, counters_dev, abort_dev, progress_dev);
-    else         k1_march<false><<<grid, K1_THREADS, 0, st>>>(sc, out_dev, counters_dev, abort_dev, progress_dev);
+    if (counted) k1_march<true><<<grid, K1_THREADS, GN_DYN_SMEM, st>>>(sc, out_dev, counters_dev, abort_dev, progress_dev);
+    else         k1_march<false><<<grid, K1_THREADS, GN_DYN_SMEM, st>>>(sc, out_dev, counters_dev, abort_dev, progress_dev);
     return cudaGetLastError();
 }
 
@@ -431,19 +444,19 @@ cudaError_t launch_k2(const float *rgb, const float *stars, uint32_t *argb, uint
 }
 
 cudaError_t launch_probe_simplex(const float *xyz, int n, double frequency, int32_t *lat, float *val, cudaStream_t st) {
-    kp_simplex<<<(n + 255) / 256, 256, 0, st>>>(xyz, n, frequency, lat, val);
+    kp_simplex<<<(n + 255) / 256, 256, GN_DYN_SMEM, st>>>(xyz, n, frequency, lat, val);
     return cudaGetLastError();
 }
 cudaError_t launch_probe_fbm(const float *xyz, int n, int octaves, float pers, float inv_maxamp, double scale, float *out,
                              cudaStream_t st) {
-    kp_fbm<<<(n + 255) / 256, 256, 0, st>>>(xyz, n, octaves, pers, inv_maxamp, scale, out);
+    kp_fbm<<<(n + 255) / 256, 256, GN_DYN_SMEM, st>>>(xyz, n, octaves, pers, inv_maxamp, scale, out);
     return cudaGetLastError();
 }
 cudaError_t launch_probe_ridged(const float *xyz, int n, int octaves, float lac, float offset, float gain, const float *rw,
                                 float *out, cudaStream_t st) {
     RidgedW w;
     for (int i = 0; i < 16; i++) w.w[i] = (i < octaves) ? rw[i] : 0.f;
-    kp_ridged<<<(n + 255) / 256, 256, 0, st>>>(xyz, n, octaves, lac, offset, gain, w, out);
+    kp_ridged<<<(n + 255) / 256, 256, GN_DYN_SMEM, st>>>(xyz, n, octaves, lac, offset, gain, w, out);
     return cudaGetLastError();
 }
 

@@ -5,6 +5,7 @@
 #include "scene_dev.h"
 
 namespace gk {
+cudaError_t prepare_device();   // per device, before the first launch
 cudaError_t launch_k1(const DScene &sc, float *out_dev, unsigned long long *counters_dev, const int *abort_dev,
                       unsigned int *progress_dev, bool counted, cudaStream_t st, unsigned int *n_blocks);
 cudaError_t launch_k2(const float *rgb, const float *stars, uint32_t *argb, uint32_t *shadow, size_t n, double exposure,

@@ -21,6 +21,12 @@
 #pragma once
 #include <stdint.h>
 
+#ifndef FBM_UNROLL
+#define FBM_UNROLL 1
+#endif
+#define GN_PRAGMA(x) _Pragma(#x)
+#define GN_UNROLL(n) GN_PRAGMA(unroll n)
+
 namespace gnoise {
 
 // Ken Perlin's permutation, as in simplexnoise.h:160-185 (first 256 entries; the second copy is &255).
@@ -41,41 +47,53 @@ __constant__ uint8_t c_perm[256] = {
 
 // Gradient code of g = perm % 12 for grad3 (simplexnoise.h:142-146): dot(grad3[g], (x,y,z)) = ±a ± b with
 //   g<4: (a,b)=(x,y)   4<=g<8: (x,z)   g>=8: (y,z);  sign(a) = g&1, sign(b) = (g>>1)&1.
-// Bit 31 = sign of a, bit 30 = sign of b, bit 0 = "a is y", bit 1 = "b is y"; bits 2..5 = g itself.
+// Bit 31 = sign of a, bit 30 = sign of b, bit 1 = "a is y", bit 2 = "b is y"; bits 3..6 = g itself.
 __host__ __device__ inline uint32_t grad_code(uint32_t g) {
-    uint32_t code = (g << 2);
+    uint32_t code = (g << 3);
     if (g & 1) code |= 0x80000000u;
     if (g & 2) code |= 0x40000000u;
-    if (g >= 8) code |= 1u;
-    if (g < 4) code |= 2u;
+    if (g >= 8) code |= 2u;
+    if (g < 4) code |= 4u;
     return code;
 }
 
 #define GN_TABLE_WORDS (256 * 32)
 #define GN_ADDR_MASK 0x7F80u
+// The replicated table must sit at a 32 KB-aligned address of the CTA's shared window so that a lookup
+// address is ONE LOP3: (off & 0x7F80) | (0x8000 | lane*4), followed by one LDS. Static shared memory
+// starts at window offset 0x400 (the first KB is reserved), so kernels that use the noise code take
+// GN_DYN_SMEM bytes of dynamic shared memory (and no static shared memory): the table occupies window
+// addresses 0x8000..0xFFFF. table_init() verifies the base and traps if the layout ever differs.
+#define GN_TABLE_ADDR 0x8000u
+#define GN_DYN_BASE 0x400u
+#define GN_DYN_SMEM (GN_TABLE_ADDR - GN_DYN_BASE + GN_TABLE_WORDS * 4u)
 
-// The replicated table is a file-scope static __shared__ array so that a lookup compiles to one LOP3
-// ((off & mask) | lane*4) and one LDS with the array base as the instruction's immediate offset.
-__shared__ __align__(128) uint32_t s_tbl[GN_TABLE_WORDS];
+extern __shared__ __align__(16) unsigned char gn_dyn_smem[];
 
 // Fill the replicated table; call from all threads of the block, then __syncthreads().
 __device__ __forceinline__ void table_init() {
+    if ((uint32_t)__cvta_generic_to_shared(gn_dyn_smem) != GN_DYN_BASE) __trap();
+    uint32_t *tbl = reinterpret_cast<uint32_t *>(gn_dyn_smem + (GN_TABLE_ADDR - GN_DYN_BASE));
     for (uint32_t w = threadIdx.x + threadIdx.y * blockDim.x; w < GN_TABLE_WORDS; w += blockDim.x * blockDim.y) {
         uint32_t e = w >> 5;
         uint32_t p = c_perm[e];
-        s_tbl[w] = (p << 7) | grad_code(p % 12u);
+        tbl[w] = (p << 7) | grad_code(p % 12u);
     }
 }
+// per-lane constant of the lookup address
+__device__ __forceinline__ uint32_t lane_const() { return GN_TABLE_ADDR | ((threadIdx.x & 31u) << 2); }
 
 // one level of the hash walk: entry ((off7 >> 7) & 255) of this lane's bank
 __device__ __forceinline__ uint32_t look(uint32_t lane4, uint32_t off7) {
-    return *reinterpret_cast<const uint32_t *>(reinterpret_cast<const char *>(s_tbl) + ((off7 & GN_ADDR_MASK) | lane4));
+    uint32_t v, a = (off7 & GN_ADDR_MASK) | lane4;
+    asm("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a));
+    return v;
 }
 
 // ±a ± b from a table entry
 __device__ __forceinline__ float grad_dot(uint32_t e, float x, float y, float z) {
-    float a = (e & 1u) ? y : x;
-    float b = (e & 2u) ? y : z;
+    float a = (e & 2u) ? y : x;
+    float b = (e & 4u) ? y : z;
     a = __uint_as_float(__float_as_uint(a) ^ (e & 0x80000000u));
     b = __uint_as_float(__float_as_uint(b) ^ ((e << 1) & 0x80000000u));
     return a + b;
@@ -129,9 +147,9 @@ __device__ __forceinline__ float simplex_cell(uint32_t lane4, int ci, int cj, in
     bool i1 = a && c, j1 = !a && b, k1 = !b && !c;
     bool i2 = a || c, j2 = !a || b, k2 = !(b && c);
 
-    float x1 = x0 - (i1 ? 1.0f : 0.0f) + G3, y1 = y0 - (j1 ? 1.0f : 0.0f) + G3, z1 = z0 - (k1 ? 1.0f : 0.0f) + G3;
-    float x2 = x0 - (i2 ? 1.0f : 0.0f) + 2.0f * G3, y2 = y0 - (j2 ? 1.0f : 0.0f) + 2.0f * G3,
-          z2 = z0 - (k2 ? 1.0f : 0.0f) + 2.0f * G3;
+    const float G3m = G3 - 1.0f, G6 = 2.0f * G3, G6m = 2.0f * G3 - 1.0f;
+    float x1 = x0 + (i1 ? G3m : G3), y1 = y0 + (j1 ? G3m : G3), z1 = z0 + (k1 ? G3m : G3);
+    float x2 = x0 + (i2 ? G6m : G6), y2 = y0 + (j2 ? G6m : G6), z2 = z0 + (k2 ? G6m : G6);
     float x3 = x0 - 0.5f, y3 = y0 - 0.5f, z3 = z0 - 0.5f;
 
     // hash walk: perm[ii+oi+perm[jj+oj+perm[kk+ok]]], offsets pre-scaled by 128
@@ -159,7 +177,7 @@ __device__ __forceinline__ float simplex_cell(uint32_t lane4, int ci, int cj, in
     if (PROBE) {
         lat->c1 = (int)i1 + 2 * (int)j1 + 4 * (int)k1;
         lat->c2 = (int)i2 + 2 * (int)j2 + 4 * (int)k2;
-        lat->g0 = (C0 >> 2) & 15; lat->g1 = (C1 >> 2) & 15; lat->g2 = (C2 >> 2) & 15; lat->g3 = (C3 >> 2) & 15;
+        lat->g0 = (C0 >> 3) & 15; lat->g1 = (C1 >> 3) & 15; lat->g2 = (C2 >> 3) & 15; lat->g3 = (C3 >> 3) & 15;
     }
     return 32.0f * n;
 }
@@ -203,7 +221,7 @@ __device__ __forceinline__ float fbm(uint32_t lane4, float px, float py, float p
     skew(__dmul_rn((double)px, scale), __dmul_rn((double)py, scale), __dmul_rn((double)pz, scale), su, sv, sw);
     const bool quirk = maybe_integer(su, sv, sw, octaves - 1);
     float total = 0.0f, amp = 1.0f;
-#pragma unroll 1
+GN_UNROLL(FBM_UNROLL)
     for (int k = 0; k < octaves; k++) {
         total = fmaf(octave(lane4, su, sv, sw, k, quirk), amp, total);
         amp *= pers;

@@ -1,0 +1,36 @@
+"""Summarise an ncu report per source line / region: python tools/ncu_lines.py rep.ncu-rep samples octaves"""
+import collections, csv, re, subprocess, sys
+rep, samples, octaves = sys.argv[1], float(sys.argv[2]) / 32, float(sys.argv[3]) / 32
+raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+rows = list(csv.reader(raw.splitlines()))
+hdr, vals = rows[0], rows[2]
+m = dict(zip(hdr, vals))
+for k in ("gpu__time_duration.sum", "smsp__inst_executed.sum", "smsp__issue_active.avg.pct_of_peak_sustained_active",
+          "sm__warps_active.avg.pct_of_peak_sustained_active", "smsp__thread_inst_executed_per_inst_executed.ratio",
+          "sm__pipe_fma_cycles_active.avg.pct_of_peak_sustained_active", "sm__pipe_alu_cycles_active.avg.pct_of_peak_sustained_active",
+          "sm__pipe_fp64_cycles_active.avg.pct_of_peak_sustained_active", "sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active",
+          "sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active", "launch__registers_per_thread",
+          "dram__bytes_read.sum", "dram__bytes_write.sum"):
+    print(k, m.get(k))
+src = subprocess.run(["ncu", "-i", rep, "--page", "source", "--print-source", "cuda,sass", "--csv"], capture_output=True, text=True).stdout
+cur = None; line = None
+lines = collections.Counter(); text = {}; ops = collections.defaultdict(collections.Counter); stall = collections.Counter()
+for r in csv.reader(src.splitlines()):
+    if len(r) >= 2 and r[0] == 'File Path': cur = r[1].split('/')[-1]; continue
+    if len(r) > 7 and r[0].isdigit():
+        line = (cur, int(r[0])); text[line] = r[1].strip()[:100]
+        try: stall[line] += int(r[4])
+        except ValueError: pass
+        continue
+    if len(r) > 7 and r[0] == '' and r[2].startswith('0x'):
+        mm = re.match(r'\s*(@!?U?P\d+\s+)?([A-Z0-9_.]+)', r[3])
+        op = mm.group(2).split('.')[0] if mm else '?'
+        n = int(r[7]); lines[line] += n; ops[line[0]][op] += n
+tot = sum(lines.values()); ts = sum(stall.values())
+byfile = collections.Counter()
+for (f, l), v in lines.items(): byfile[f] += v
+print("total warp-instr", tot, {f: round(100 * v / tot, 1) for f, v in byfile.items()})
+print("noise.cuh warp-instr per octave:", byfile['noise.cuh'] / octaves, " other per sample:", (tot - byfile['noise.cuh']) / samples)
+print("noise opcodes per octave:", {k: round(v / octaves, 1) for k, v in ops['noise.cuh'].most_common(16)})
+for (f, l), v in lines.most_common(int(sys.argv[4]) if len(sys.argv) > 4 else 45):
+    print(f"{f:11s} {l:4d} {100*v/tot:5.1f}% stall {100*stall[(f,l)]/max(ts,1):5.1f}%  {text[(f,l)]}")
