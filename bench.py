@@ -156,8 +156,14 @@ def run_ours(args):
     K, Wm = args.steps, args.warmup
     wl = args.workload
     size = WORKLOADS[wl][1]
-    frames = [s * world + rank for s in range(Wm + K)]
-    scenes_ = [make_scene(wl, f) for f in frames]
+    tiles = args.mode == "tiles"
+    if tiles:       # strong scaling: every rank renders its interleaved bands of the SAME frame, then one gather
+        from gamer_b200 import parallel
+        full = [make_scene(wl, s) for s in range(Wm + K)]
+        scenes_ = [parallel.band_tile(sc, rank, world) for sc in full]
+    else:           # weak scaling: step s renders frames s*world .. s*world+world-1, one per rank
+        frames = [s * world + rank for s in range(Wm + K)]
+        scenes_ = [make_scene(wl, f) for f in frames]
 
     # exact work of every timed frame (instrumented kernel, outside the timed region)
     counts = []
@@ -171,6 +177,8 @@ def run_ours(args):
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")       # > 126 MB L2
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
 
+    gathered = [None, None]
+
     def step_device(i, timed_idx=None):
         ctx.upload(scenes_[i])                      # host-side: scene -> kernel parameter block
         with torch.cuda.stream(stream):
@@ -179,6 +187,10 @@ def run_ours(args):
                 ev[timed_idx][0].record(stream)
             ctx.render_device()                     # K1
             ctx.tonemap_device(1.0, 1.0, 1.0)       # K2
+            if tiles and world > 1:                 # K3: the one exchange step — gather the disjoint bands
+                rgb_t, _, img_t = ctx.device_tensors()
+                gathered[0] = parallel.gather_bands(rgb_t, size, rank, world)
+                gathered[1] = parallel.gather_bands(img_t, size, rank, world)
             if timed_idx is not None:
                 ev[timed_idx][1].record(stream)
 
@@ -208,8 +220,16 @@ def run_ours(args):
 
     def step_e2e(i):
         ctx.upload(scenes_[i])
-        ctx.render_ptr(host_rgb.data_ptr())
-        ctx.tonemap_ptr(1.0, 1.0, 1.0, None, host_img.data_ptr())
+        if tiles and world > 1:                     # bands stay on the device, gather over NVLink, rank 0 reads the frame
+            step_device(i)
+            if rank == 0:
+                with torch.cuda.stream(stream):
+                    host_rgb.copy_(gathered[0], non_blocking=True)
+                    host_img.copy_(gathered[1], non_blocking=True)
+            stream.synchronize()
+        else:
+            ctx.render_ptr(host_rgb.data_ptr())
+            ctx.tonemap_ptr(1.0, 1.0, 1.0, None, host_img.data_ptr())
 
     for i in range(min(Wm, 3)):
         step_e2e(i)
@@ -250,16 +270,18 @@ def run_ours(args):
         k2_bytes = px * (12 + 4 + 4)
         out = {
             "metric": METRIC, "value": tot_samples / (dev_ms_max * 1e-3), "unit": UNIT, "n_gpus": world,
-            "steps": K, "warmup": Wm, "ms_per_step": dev_ms_max / K, "higher_is_better": True, "scaling": "weak",
+            "steps": K, "warmup": Wm, "ms_per_step": dev_ms_max / K, "higher_is_better": True, "scaling": "strong" if tiles else "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": wl, "galaxy": WORKLOADS[wl][0] + ".gax (tests/golden/gax)", "size": size,
-                       "ray_step": "0.025f", "frames_per_step": world, "parallelism": f"frames x{world}",
+            "config": {"workload": wl, "mode": args.mode, "galaxy": WORKLOADS[wl][0] + ".gax (tests/golden/gax)", "size": size,
+                       "ray_step": "0.025f", "frames_per_step": 1 if tiles else world,
+                       "parallelism": (f"interleaved {parallel.BAND}-row bands x{world} + NCCL gather to rank 0" if tiles
+                                       else f"frames x{world}"),
                        "l2": "256 MB device buffer zeroed between timed iterations (outside the event bracket); "
                              "inputs are a few KB of scene parameters",
                        "ray_samples_per_frame": my_samples / K, "octaves_per_frame": sum(c["octaves"] for c in counts) / K},
             "gpu_launches": int(tot_launches),
             "e2e": {"value": tot_samples / (e2e_ms_max * 1e-3), "unit": UNIT,
-                    "h2d_bytes_per_step": world * ctx_scene_bytes(scenes_[0]), "d2h_bytes_per_step": world * px * 16,
+                    "h2d_bytes_per_step": world * ctx_scene_bytes(scenes_[0]), "d2h_bytes_per_step": (1 if tiles else world) * px * 16,
                     "ms_per_step": e2e_ms_max / K, "checksum": checksum},
             "roofline": {"kernel": "k1_march", "bound": "fp32", "achieved": k1_tflops, "peak": fp32_peak, "unit": "TFLOP/s",
                          "frac": k1_tflops / fp32_peak, "traffic": None,
@@ -333,6 +355,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="spiral_2048_oblique_orbit", choices=list(WORKLOADS))
+    ap.add_argument("--mode", default="frames", choices=["frames", "tiles"],
+                    help="N>1: frames = one frame per rank per step (weak, no collective); tiles = one frame split "
+                         "into interleaved row bands + NCCL gather (strong)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--cpu-row-stride", type=int, default=16, help="cpu_baseline sample: every n-th row")
     ap.add_argument("--ref-row-stride", type=int, default=64, help="--impl reference step: every n-th row")

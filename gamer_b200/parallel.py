@@ -1,0 +1,84 @@
+"""Multi-GPU partitioning of the render path: one process per GPU (torch.distributed), no collective in
+the data path except the final gather of disjoint tiles.
+
+The reference is single-process; its two scheduling strategies are the shuffled render list
+(rasterizer.cpp:115-122) and RasterThread's equal chunks of that list (rasterthread.cpp:9-24).
+The multi-GPU analogue here:
+  * frames / galaxies: unit k -> rank k mod world (no exchange at all);
+  * image tiles: interleaved bands of BAND rows (band b -> rank b mod world), which balances the very
+    uneven cost per row of edge-on views the way the reference's shuffle does, followed by ONE gather
+    of the disjoint bands to rank 0 (NCCL over NVLink on GPUs; gloo in the CPU tests).
+Everything in this module is index arithmetic and torch plumbing and runs on CPU tensors as well.
+"""
+from typing import List, Tuple
+
+import torch
+import torch.distributed as dist
+
+BAND = 32
+_row_index_cache = {}
+
+
+def _row_index(r, world, height, band, device):
+    key = (r, world, height, band, str(device))
+    if key not in _row_index_cache:
+        _row_index_cache[key] = torch.as_tensor(band_rows(r, world, height, band), device=device, dtype=torch.long)
+    return _row_index_cache[key]
+
+
+def units_of(rank: int, world: int, n_units: int) -> List[int]:
+    """frame / galaxy sharding: unit k belongs to rank k mod world."""
+    return list(range(rank, n_units, world))
+
+
+def band_rows(rank: int, world: int, height: int, band: int = BAND) -> List[int]:
+    """image rows owned by `rank`, in the order its local framebuffer stores them."""
+    rows = []
+    for b in range(rank, (height + band - 1) // band, world):
+        rows.extend(range(b * band, min(height, (b + 1) * band)))
+    return rows
+
+
+def band_tile(scene, rank: int, world: int, band: int = BAND):
+    """The rank's share of `scene` (a gamer_b200.model.Scene covering the full frame) as a tile scene
+    using GamerFrame's band_rows/band_stride addressing."""
+    f = scene.frame
+    n = len(band_rows(rank, world, f.height, band))
+    if world == 1:
+        return scene.tile(f.x0, f.y0, f.width, f.height)
+    return scene.tile(f.x0, f.y0 + rank * band, f.width, max(n, 0), band_rows=band, band_stride=band * world)
+
+
+def gather_bands(local: torch.Tensor, height: int, rank: int, world: int, band: int = BAND, dst: int = 0):
+    """Gather every rank's band-ordered rows [rows_r, ...] to `dst` and return the frame [height, ...]
+    in image order there (None elsewhere). Ranks may own different row counts (ragged last band)."""
+    if world == 1:
+        return local
+    counts = [len(band_rows(r, world, height, band)) for r in range(world)]
+    pad = max(counts)
+    if local.shape[0] != pad:                       # gather needs equal shapes: pad the short ranks
+        padded = local.new_zeros((pad,) + tuple(local.shape[1:]))
+        padded[: local.shape[0]] = local
+        local = padded
+    bufs = [torch.empty_like(local) for _ in range(world)] if rank == dst else None
+    dist.gather(local, bufs, dst=dst)
+    if rank != dst:
+        return None
+    out = local.new_empty((height,) + tuple(local.shape[1:]))
+    for r in range(world):
+        out.index_copy_(0, _row_index(r, world, height, band, local.device), bufs[r][: counts[r]])
+    return out
+
+
+def max_over_ranks(values: List[float], device) -> List[float]:
+    t = torch.tensor(values, dtype=torch.float64, device=device)
+    if dist.is_initialized() and dist.get_world_size() > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return t.tolist()
+
+
+def sum_over_ranks(values: List[float], device) -> List[float]:
+    t = torch.tensor(values, dtype=torch.float64, device=device)
+    if dist.is_initialized() and dist.get_world_size() > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+    return t.tolist()

@@ -104,6 +104,22 @@ class Context:
                                                               C.byref(rows)))
         return p[0].value, p[1].value, p[2].value, rows.value
 
+    def device_tensors(self, which=0):
+        """Zero-copy torch views of the device framebuffers of the last render: (rgb [rows,W,3] float32,
+        argb [rows,W] int32, shadow [rows,W] int32). For callers that keep results on the GPU (NCCL gather)."""
+        import torch
+
+        class _Cai:
+            def __init__(self, ptr, shape, typestr):
+                self.__cuda_array_interface__ = {"shape": shape, "typestr": typestr, "data": (ptr, False), "version": 2}
+
+        rgb, argb, shadow, rows = self.device_buffers(which)
+        w = self.shape[1]
+        dev = torch.device("cuda", torch.cuda.current_device())
+        return (torch.as_tensor(_Cai(rgb, (rows, w, 3), "<f4"), device=dev),
+                torch.as_tensor(_Cai(argb, (rows, w), "<i4"), device=dev),
+                torch.as_tensor(_Cai(shadow, (rows, w), "<i4"), device=dev))
+
     def progress(self) -> float:
         f = C.c_double()
         _lib.check(self.h, self.lib.gamer_b200_progress(self.h, C.byref(f)))
