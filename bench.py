@@ -301,9 +301,15 @@ def run_ours(args):
             v, cores, desc, secs = time_cpu(wl, args.cpu_row_stride)
             out["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": desc, "seconds": secs}
         print(json.dumps(out), flush=True)
-    ctx.close()
+    # torch tensors that were used on the context's stream must be released while that stream still exists
+    gathered[:] = [None, None]
+    del flush, host_rgb, host_img
+    torch.cuda.synchronize()
+    torch.cuda.empty_cache()
     if world > 1:
+        dist.barrier()
         dist.destroy_process_group()
+    ctx.close()
 
 
 def ctx_scene_bytes(scene) -> int:
