@@ -1,0 +1,126 @@
+"""The Qt-free C++ host side (gamer_b200/host): .gax layer, PNG writer, and the `galaxy` CLI that is
+argument-compatible with the reference's consolerenderer (source/consolerenderer.cpp:16-101)."""
+import os
+import struct
+import subprocess
+import zlib
+
+import numpy as np
+import pytest
+
+import scenes
+from gamer_b200.gax import Galaxy
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+CLI = os.path.join(ROOT, "gamer_b200", "lib", "gamer_b200_cli")
+GAX = os.path.join(ROOT, "tests", "golden", "gax")
+
+
+def _run(*args, timeout=300):
+    return subprocess.run([CLI, *map(str, args)], capture_output=True, text=True, timeout=timeout)
+
+
+def _read_png_rgba(path):
+    d = open(path, "rb").read()
+    assert d[:8] == b"\x89PNG\r\n\x1a\n"
+    o, idat, w, h = 8, b"", 0, 0
+    while o < len(d):
+        n, typ = struct.unpack(">I4s", d[o:o + 8])
+        body = d[o + 8:o + 8 + n]
+        assert zlib.crc32(typ + body) == struct.unpack(">I", d[o + 8 + n:o + 12 + n])[0]
+        if typ == b"IHDR":
+            w, h, depth, ctype = struct.unpack(">IIBB", body[:10])
+            assert (depth, ctype) == (8, 6)
+        elif typ == b"IDAT":
+            idat += body
+        o += 12 + n
+    raw = np.frombuffer(zlib.decompress(idat), dtype=np.uint8).reshape(h, 1 + 4 * w)
+    assert not raw[:, 0].any()          # filter type None on every row
+    return raw[:, 1:].reshape(h, w, 4)
+
+
+def test_cli_exists():
+    assert os.access(CLI, os.X_OK), "build it: make -C gamer_b200/host"
+
+
+@pytest.mark.parametrize("name", scenes.FIXTURES)
+def test_gax_roundtrip_is_byte_exact(name, tmp_path):
+    src = os.path.join(GAX, name + ".gax")
+    out = tmp_path / "copy.gax"
+    assert _run("gaxcopy", src, out).returncode == 0
+    assert open(src, "rb").read() == open(out, "rb").read()
+
+
+@pytest.mark.parametrize("name", scenes.FIXTURES)
+def test_gax_dump_matches_python_reader(name):
+    p = _run("gaxdump", os.path.join(GAX, name + ".gax"))
+    assert p.returncode == 0
+    lines = p.stdout.splitlines()
+    g = Galaxy.Load(os.path.join(GAX, name + ".gax"))
+    assert lines[1] == "name=" + g.galaxyParams.name
+    n = int(lines[6].split("=")[1])
+    assert n == len(g.componentParams)
+    for line, c in zip(lines[7:], g.componentParams):
+        cls, strength, spectrum, nums, cname = line.split("|")
+        assert (cls, spectrum, cname) == (c.className, c.spectrum, c.name)
+        assert float(strength) == c.strength
+        want = [c.arm, c.z0, c.r0, c.active, c.delta, c.winding, c.scale, c.noiseOffset, c.noiseTilt, c.ks, c.inner]
+        assert [float(v) for v in nums.split()] == want
+
+
+def test_gax_truncated_file_is_an_error(tmp_path):
+    d = open(os.path.join(GAX, "Spiral.gax"), "rb").read()
+    bad = tmp_path / "bad.gax"
+    bad.write_bytes(d[:-5])
+    p = _run("gaxdump", bad)
+    assert p.returncode == 1 and "ERROR" in p.stdout
+
+
+def test_png_writer(tmp_path):
+    out = tmp_path / "t.png"
+    assert _run("pngtest", out, 300, 250).returncode == 0
+    img = _read_png_rgba(out)
+    y, x = np.mgrid[0:250, 0:300]
+    assert np.array_equal(img[..., 0], (x * 7 + y) & 255)
+    assert np.array_equal(img[..., 1], (y * 5) & 255)
+    assert np.array_equal(img[..., 2], (x ^ y) & 255)
+    assert (img[..., 3] == 255).all()
+
+
+def test_cli_usage_errors(tmp_path):
+    assert _run().returncode == 1
+    p = _run("galaxy", "omp", 1, 2, 3)                      # consolerenderer.cpp:31-37: exactly 19 words
+    assert p.returncode == 1 and "Incorrect usage" in p.stdout
+    args = ["galaxy", "cuda", 0.5, 0, 0, 0, 0, 0, 0, 1, 0, 90, 1, 1, 1.0, 0.025, os.path.join(GAX, "Spiral.gax"), 64, tmp_path / "o"]
+    p = _run(*args)
+    assert p.returncode == 1 and "Cannot recognize" in p.stdout
+    args[1], args[16] = "omp", tmp_path / "missing.gax"
+    p = _run(*args)
+    assert p.returncode == 1 and "Cannot open" in p.stdout
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name,size,gamma", [("Spiral", 128, 1.0), ("Sombrero", 96, 0.8)])
+def test_cli_image_equals_python_pipeline(name, size, gamma, tmp_path):
+    """singleGalaxy.sh's command line -> PNG; pixels equal the ctypes pipeline's shadow image."""
+    from gamer_b200.model import GalaxyInstance, RenderingParams
+    from gamer_b200.rasterizer import Rasterizer
+    out = tmp_path / "img"
+    p = _run("galaxy", "omp", 0.5, 0, 0, 0, 0, 0, 0, 1, 0, 90, 1.2, gamma, 1.1, 0.025, os.path.join(GAX, name + ".gax"), size, out)
+    assert p.returncode == 0, p.stdout + p.stderr
+    png = _read_png_rgba(str(out) + ".png")
+    rp = RenderingParams(m_size=size, m_exposure=float(np.float32(1.2)), m_gamma=float(np.float32(gamma)),
+                         m_saturation=float(np.float32(1.1)), m_rayStep=float(np.float32(0.025)))
+    rp.camera().m_camera, rp.camera().m_target, rp.camera().m_up, rp.camera().m_perspective = (0.5, 0, 0), (0, 0, 0), (0, 1, 0), 90.0
+    rp.spectra().PopulateSpectra()
+    r = Rasterizer()
+    r.setRenderingParams(rp)
+    r.AddGalaxy(GalaxyInstance(Galaxy.Load(os.path.join(GAX, name + ".gax"))))
+    r.Render()
+    while r.getState() != Rasterizer.State.done:
+        pass
+    r.AssembleImage()
+    sh = r.getImageShadowBuffer()
+    want = np.stack([(sh >> 16) & 255, (sh >> 8) & 255, sh & 255, sh >> 24], axis=-1).astype(np.uint8)
+    assert np.array_equal(png, want)
+    assert want[..., :3].max() > 50        # a real image, not black
