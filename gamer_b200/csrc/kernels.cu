@@ -74,9 +74,20 @@ __device__ __forceinline__ void bulge_add(float k, float r0, float sr, float sg,
                                           float &Ir, float &Ig, float &Ib) {
     float rad = fmaf(plen3 + 0.01f, r0, 0.01f);
     float L = lg2a(rad);
-    float v = fmaf(ex2a(-0.855f * L), ex2a(-1.4426950408889634f * ex2a(0.25f * L)), -0.05f);
+    float v = ex2a(fmaf(-1.4426950408889634f, ex2a(0.25f * L), -0.855f * L)) - 0.05f;
     float i = fmaxf(k * v, 0.0f);
     Ir = fmaf(i, sr, Ir); Ig = fmaf(i, sg, Ig); Ib = fmaf(i, sb, Ib);
+}
+
+// Stars with noiseOffset != 0 (galaxycomponents.cpp:144-148): two 4-octave helpers, persistence -2
+// (amplitudes 1,-2,4,-8, sum -5). No shipped galaxy uses it: kept out of line so the hot loop stays small.
+__device__ __noinline__ float stars_helper_octaves(const DGalaxy &g, const DComp &c, const Shared1 &s, const NoiseCtx &nz,
+                                                   double winding) {
+    f3 r1 = twirl_qt(g.axis_n, s.p, winding);
+    f3 r2 = twirl_qt(g.axis_n, s.p, __dmul_rn(winding, 0.5));
+    float add = c.noise_offset * gnoise::fbm(nz.lane4, r1.x, r1.y, r1.z, 2.0 * (double)0.1f, 4, -2.0f, -0.2f);
+    add += 0.5f * (c.noise_offset * gnoise::fbm(nz.lane4, r2.x, r2.y, r2.z, 4.0 * (double)0.1f, 4, -2.0f, -0.2f));
+    return add;
 }
 
 template <bool COUNT>
@@ -121,66 +132,66 @@ __device__ __forceinline__ void eval_component(const DScene &sc, const DGalaxy &
     if (!(ival > 0.0005f)) return;
     if (COUNT) cn.evals++;
 
-    switch (c.cls) {
+    // One twirl and ONE noise evaluation site for every class (keeps the hot loop small enough for the
+    // instruction cache); the class-specific use of the noise value follows.
+    const int cls = c.cls;
+    if (cls > GAMER_CLASS_STARS) return;              // "stars small": no-op (see gamer_b200.h)
+    const bool is_ridged = (cls == GAMER_CLASS_DUST2) | (cls == GAMER_CLASS_DUST_POSITIVE);
+    f3 r = s.p;
+    if (cls != GAMER_CLASS_STARS) r = twirl_qt(g.axis_n, s.p, winding);
+    float n;
+    if (is_ridged) {                    // getRidgedMf(r * scale, ks, 9, 2.5, noiseOffset, noiseTilt)
+        n = gnoise::ridged(nz.lane4, __fmul_rn(r.x, c.rscale), __fmul_rn(r.y, c.rscale), __fmul_rn(r.z, c.rscale),
+                           DEV_RIDGED_OCTAVES, 2.5f, c.noise_offset, c.noise_tilt, c.rw);
+        if (COUNT) cn.octaves += DEV_RIDGED_OCTAVES;
+    } else {                            // getPerlinCloudNoise / octave_noise_3d
+        n = gnoise::fbm(nz.lane4, r.x, r.y, r.z, c.nscale, c.octaves, c.pers, c.inv_maxamp);
+        if (COUNT) cn.octaves += c.octaves;
+    }
+
+    float k;                            // emission coefficient (k >= 0 classes) or absorption exponent
+    bool absorb = false;
+    switch (cls) {
     case GAMER_CLASS_DISK: {            // galaxycomponents.cpp:41-59
-        f3 r = twirl_qt(g.axis_n, s.p, winding);
-        float n = gnoise::fbm(nz.lane4, r.x, r.y, r.z, c.nscale, 10, c.pers, c.inv_maxamp);
-        if (COUNT) cn.octaves += 10;
         float p2 = fpow(fmaxf(fabsf(n), 0.01f), c.noise_tilt) + c.noise_offset;
         if (p2 < 0.0f) return;
-        float k = ival * p2 * rs;
-        Ir = fmaf(k, c.spec[0], Ir); Ig = fmaf(k, c.spec[1], Ig); Ib = fmaf(k, c.spec[2], Ib);
+        k = ival * p2 * rs;
         break;
     }
     case GAMER_CLASS_DUST: {            // galaxycomponents.cpp:64-84
-        f3 r = twirl_qt(g.axis_n, s.p, winding);
-        float n = gnoise::fbm(nz.lane4, r.x, r.y, r.z, c.nscale, 9, c.pers, c.inv_maxamp);
-        if (COUNT) cn.octaves += 9;
         float p2 = fmaxf(n - c.noise_offset, 0.0f);
         p2 = (p2 > 0.0f) ? fpow(5.0f * p2, c.noise_tilt) : (c.noise_tilt > 0.0f ? 0.0f : (c.noise_tilt == 0.0f ? 1.0f : 10.0f));
         p2 = fminf(fmaxf(p2, -10.0f), 10.0f);
-        float k = -p2 * ival * 0.01f;
-        Ir *= fexp(k * c.spec[0]); Ig *= fexp(k * c.spec[1]); Ib *= fexp(k * c.spec[2]);
+        k = -p2 * ival * 0.01f;
+        absorb = true;
         break;
     }
-    case GAMER_CLASS_DUST2:             // galaxycomponents.cpp:85-114
+    case GAMER_CLASS_DUST2: {           // galaxycomponents.cpp:85-114
+        k = -fmaxf(n, 0.0f) * ival * 0.01f;
+        absorb = true;
+        break;
+    }
     case GAMER_CLASS_DUST_POSITIVE: {   // galaxycomponents.cpp:116-136
-        f3 r = twirl_qt(g.axis_n, s.p, winding);
-        float p2 = gnoise::ridged(nz.lane4, __fmul_rn(r.x, c.rscale), __fmul_rn(r.y, c.rscale),
-                                  __fmul_rn(r.z, c.rscale), DEV_RIDGED_OCTAVES, 2.5f, c.noise_offset, c.noise_tilt, c.rw);
-        if (COUNT) cn.octaves += DEV_RIDGED_OCTAVES;
-        p2 = fmaxf(p2, 0.0f);
-        if (c.cls == GAMER_CLASS_DUST2) {
-            float k = -p2 * ival * 0.01f;
-            Ir *= fexp(k * c.spec[0]); Ig *= fexp(k * c.spec[1]); Ib *= fexp(k * c.spec[2]);
-        } else {
-            float k = ival * p2 * rs;
-            Ir = fmaf(k, c.spec[0], Ir); Ig = fmaf(k, c.spec[1], Ig); Ib = fmaf(k, c.spec[2], Ib);
-        }
+        k = ival * fmaxf(n, 0.0f) * rs;
         break;
     }
-    case GAMER_CLASS_STARS: {           // galaxycomponents.cpp:139-155
-        float n = fabsf(gnoise::fbm(nz.lane4, s.p.x, s.p.y, s.p.z, c.nscale, 10, c.pers, c.inv_maxamp));
-        if (COUNT) cn.octaves += 10;
+    default: {                          // GAMER_CLASS_STARS, galaxycomponents.cpp:139-155
         float add = 0.0f;
-        if (c.flags & DC_HAS_NOFF) {    // two 4-octave helpers, persistence -2: amplitudes 1,-2,4,-8, sum -5
-            f3 r1 = twirl_qt(g.axis_n, s.p, winding);
-            f3 r2 = twirl_qt(g.axis_n, s.p, __dmul_rn(winding, 0.5));
-            add = c.noise_offset * gnoise::fbm(nz.lane4, r1.x, r1.y, r1.z, 2.0 * (double)0.1f, 4, -2.0f, -0.2f);
-            add += 0.5f * (c.noise_offset * gnoise::fbm(nz.lane4, r2.x, r2.y, r2.z, 4.0 * (double)0.1f, 4, -2.0f, -0.2f));
+        if (c.flags & DC_HAS_NOFF) {
+            add = stars_helper_octaves(g, c, s, nz, winding);
             if (COUNT) cn.octaves += 8;
         }
-        float base = n + 1.0f + add;
+        float base = fabsf(n) + 1.0f + add;
         float val2;
         if (base >= 0.0f) val2 = fpow(base, c.noise_tilt);
         else if (c.flags & DC_TILT_INT) val2 = fpow(-base, c.noise_tilt);        // |pow(neg, int)|
         else { Ir = Ig = Ib = 0.0f; return; }   // pow -> NaN poisons I; Util::floor's fmax(0,NaN) then zeroes it
-        float k = ival * val2 * rs;
-        Ir = fmaf(k, c.spec[0], Ir); Ig = fmaf(k, c.spec[1], Ig); Ib = fmaf(k, c.spec[2], Ib);
+        k = ival * val2 * rs;
         break;
     }
-    default: break;                      // "stars small": no-op (see gamer_b200.h)
     }
+    if (absorb) { Ir *= fexp(k * c.spec[0]); Ig *= fexp(k * c.spec[1]); Ib *= fexp(k * c.spec[2]); }
+    else { Ir = fmaf(k, c.spec[0], Ir); Ig = fmaf(k, c.spec[1], Ig); Ib = fmaf(k, c.spec[2], Ib); }
 }
 
 // Rasterizer::getIntensity (rasterizer.cpp:422-483) for one galaxy.
@@ -256,6 +267,7 @@ __device__ __forceinline__ void march(const DScene &sc, const DGalaxy &g, f3 isp
         if (COUNT) { cn.samples++; cn.gates += g.comp_count + g.noop_count; }
         p = v_sub(p, dstep);
         Ir = fmaxf(0.0f, Ir); Ig = fmaxf(0.0f, Ig); Ib = fmaxf(0.0f, Ib);   // Util::floor (util.h:62-64)
+
     }
 }
 

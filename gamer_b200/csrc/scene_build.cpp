@@ -156,6 +156,7 @@ int gk_build_scene(const GamerFrame *f, const GamerGalaxy *gal, const GamerCompo
             if (c.class_id == GAMER_CLASS_DUST) { oct = 9;  q.nscale = c.scale * 0.1f; }
             if (c.class_id == GAMER_CLASS_STARS) { oct = 10; q.nscale = 0.01f * c.scale * 100; } // galaxycomponents.cpp:141
             q.pers = float(c.ks);
+            q.octaves = oct;
             double amp = 1, maxamp = 0;
             for (int o = 0; o < oct; o++) { maxamp += amp; amp *= c.ks; }
             q.inv_maxamp = oct ? float(1.0 / maxamp) : 0.f;

@@ -45,7 +45,7 @@ struct DComp {
     float   r0;
     float   spec[3];
     float   rw[DEV_RIDGED_OCTAVES];   // pow(ks * 2.5^o, -0.05f)  (noise.cpp:119)
-    float   _pad;
+    int32_t octaves;         // fBm octave count of the class (10 disk/stars, 9 dust; 0 otherwise)
     double  nscale;          // fBm start frequency, as a double the way the reference forms it
     double  winding_d;       // cp.winding as the double the reference multiplies getWinding() with
 };

@@ -34,3 +34,9 @@ print("noise.cuh warp-instr per octave:", byfile['noise.cuh'] / octaves, " other
 print("noise opcodes per octave:", {k: round(v / octaves, 1) for k, v in ops['noise.cuh'].most_common(16)})
 for (f, l), v in lines.most_common(int(sys.argv[4]) if len(sys.argv) > 4 else 45):
     print(f"{f:11s} {l:4d} {100*v/tot:5.1f}% stall {100*stall[(f,l)]/max(ts,1):5.1f}%  {text[(f,l)]}")
+if len(sys.argv) > 5:        # extra: every line of the named files in line order, warp-instr per sample
+    for f in sys.argv[5].split(','):
+        print("----", f, "(warp-instr per ray sample)")
+        for (ff, l), v in sorted(lines.items()):
+            if ff == f and v / samples >= 0.05:
+                print(f"{l:4d} {v/samples:7.2f}  {text[(ff,l)]}")
