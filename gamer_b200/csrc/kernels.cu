@@ -11,7 +11,7 @@ namespace {
 #define K1_BW 32
 #define K1_BH 8
 #ifndef K1_MINBLOCKS
-#define K1_MINBLOCKS 2
+#define K1_MINBLOCKS 3
 #endif
 
 struct NoiseCtx {
@@ -207,13 +207,13 @@ __device__ __forceinline__ void march(const DScene &sc, const DGalaxy &g, f3 isp
     const f3 dseg = v_sub(isp1, isp2);
     const double length = (double)v_length(dseg);
     const f3 dir = v_normalized(dseg);
-    const f3 ll = v_normalized(v_sub(isp2, origin));
+    // ll = normalized(isp2 - origin) of the reference is -dir bit for bit (negation commutes with every
+    // rounding involved), so the loop test dot(p - origin, ll) < thr is evaluated as -dot(p - origin, dir) < thr.
     const f3 orient = {g.orient[0], g.orient[1], g.orient[2]};
     // the two clamped step states (rasterizer.cpp:449): step = 0.01 and step = minRayStep
     const float thr_hi = __double2float_ru(__dadd_rn(length, 0.01));
     const float thr_lo = __double2float_ru(__dadd_rn(length, sc.min_ray_step));
-    const f3 dstep_hi = v_mul(dir, __double2float_rn(0.01));
-    const f3 dstep_lo = v_mul(dir, __double2float_rn(sc.min_ray_step));
+    const float s_hi = __double2float_rn(0.01), s_lo = __double2float_rn(sc.min_ray_step);
     const float w_hi = (float)(0.01 * 200.0), w_lo = (float)(sc.min_ray_step * 200.0);
     float thr = __double2float_ru(__dadd_rn(length, sc.ray_step));     // the first test uses step = rayStep
     // bulges of this galaxy in registers (fast path)
@@ -229,19 +229,18 @@ __device__ __forceinline__ void march(const DScene &sc, const DGalaxy &g, f3 isp
     }
     f3 p = origin;
     if (COUNT) cn.rays++;
-    while (v_dot(v_sub(p, origin), ll) < thr) {
+    while (-v_dot(v_sub(p, origin), dir) < thr) {
         // step = clamp(|p - camera| * rayStep, minRayStep, 0.01)
         const f3 dc = v_sub(p, camrel);
         const float e2 = fmaf(dc.z, dc.z, fmaf(dc.y, dc.y, dc.x * dc.x));
-        f3 dstep;
-        float weight;
-        if (e2 > sc.est2_hi) { dstep = dstep_hi; weight = w_hi; thr = thr_hi; }
-        else if (e2 < sc.est2_lo) { dstep = dstep_lo; weight = w_lo; thr = thr_lo; }
+        float stepf, weight;
+        if (e2 > sc.est2_hi) { stepf = s_hi; weight = w_hi; thr = thr_hi; }
+        else if (e2 < sc.est2_lo) { stepf = s_lo; weight = w_lo; thr = thr_lo; }
         else {
             double v = __dmul_rn((double)v_length(dc), sc.ray_step);
             v = (v < 0.01) ? v : 0.01;
             const double step = (sc.min_ray_step < v) ? v : sc.min_ray_step;
-            dstep = v_mul(dir, __double2float_rn(step));
+            stepf = __double2float_rn(step);
             weight = (float)(step * 200.0);
             thr = __double2float_ru(__dadd_rn(length, step));
         }
@@ -265,7 +264,7 @@ __device__ __forceinline__ void march(const DScene &sc, const DGalaxy &g, f3 isp
                 eval_component<COUNT>(sc, g, sc.comp[g.comp_begin + k], s, nz, Ir, Ig, Ib, cn);
         }
         if (COUNT) { cn.samples++; cn.gates += g.comp_count + g.noop_count; }
-        p = v_sub(p, dstep);
+        p = v_sub(p, v_mul(dir, stepf));
         Ir = fmaxf(0.0f, Ir); Ig = fmaxf(0.0f, Ig); Ib = fmaxf(0.0f, Ib);   // Util::floor (util.h:62-64)
 
     }

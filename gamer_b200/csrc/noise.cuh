@@ -118,18 +118,19 @@ __device__ __forceinline__ Skewed to_fixed(double u) {
     return s;
 }
 
-// integer cell and in-cell fraction of octave k (skewed coordinate 2^k * u). CHECK: also handle the
+// integer cell and in-cell fraction of octave k (skewed coordinate 2^k * u); the fraction is returned
+// BIASED BY +1 (simplex_cell removes the bias inside an FMA it needs anyway). CHECK: also handle the
 // reference's fastfloor quirk; callers hoist the (almost never true) need for it out of their loops.
 template <bool CHECK>
 __device__ __forceinline__ void cell_of(const Skewed &s, int k, int &cell, float &frac) {
     uint32_t lo = s.lo << k;
     cell = (int)__funnelshift_l(s.lo, (uint32_t)s.hi, k);
-    frac = __uint2float_rn(lo) * 2.3283064365386963e-10f;
+    frac = __uint_as_float((lo >> 9) | 0x3F800000u);   // 1 + fraction (top 23 bits): no int->float conversion
     if (CHECK && lo == 0u) {   // rare: looks like an exact integer in fixed point
         double uk = s.d * (double)(1u << k);
         if (uk <= 0.0 && uk == rint(uk)) {   // simplexnoise.h:130 fastfloor: (int)x - 1 for exact x <= 0
             cell -= 1;
-            frac = 1.0f;
+            frac = 2.0f;
         }
     }
 }
@@ -139,7 +140,7 @@ template <bool PROBE>
 __device__ __forceinline__ float simplex_cell(uint32_t lane4, int ci, int cj, int ck,
                                               float fu, float fv, float fw, Lattice *lat) {
     const float G3 = 1.0f / 6.0f;
-    float t = (fu + fv + fw) * G3;
+    float t = fmaf(fu + fv + fw, G3, 0.5f);      // fu,fv,fw carry a +1 bias: (sum-3)/6 + 1
     float x0 = fu - t, y0 = fv - t, z0 = fw - t;
 
     // the six orderings of simplexnoise.cpp:267-276 as three comparisons
