@@ -81,12 +81,13 @@ __device__ __forceinline__ void bulge_add(float k, float r0, float sr, float sg,
 
 // Stars with noiseOffset != 0 (galaxycomponents.cpp:144-148): two 4-octave helpers, persistence -2
 // (amplitudes 1,-2,4,-8, sum -5). No shipped galaxy uses it: kept out of line so the hot loop stays small.
-__device__ __noinline__ float stars_helper_octaves(const DGalaxy &g, const DComp &c, const Shared1 &s, const NoiseCtx &nz,
-                                                   double winding) {
-    f3 r1 = twirl_qt(g.axis_n, s.p, winding);
-    f3 r2 = twirl_qt(g.axis_n, s.p, __dmul_rn(winding, 0.5));
-    float add = c.noise_offset * gnoise::fbm(nz.lane4, r1.x, r1.y, r1.z, 2.0 * (double)0.1f, 4, -2.0f, -0.2f);
-    add += 0.5f * (c.noise_offset * gnoise::fbm(nz.lane4, r2.x, r2.y, r2.z, 4.0 * (double)0.1f, 4, -2.0f, -0.2f));
+__device__ __noinline__ float stars_helper_octaves(const DGalaxy &g, float noise_offset, float px, float py, float pz,
+                                                   uint32_t lane4, double winding) {
+    const f3 p = {px, py, pz};          // by value: a reference would pin the caller's per-sample state in local memory
+    f3 r1 = twirl_qt(g.axis_n, p, winding);
+    f3 r2 = twirl_qt(g.axis_n, p, __dmul_rn(winding, 0.5));
+    float add = noise_offset * gnoise::fbm(lane4, r1.x, r1.y, r1.z, 2.0 * (double)0.1f, 4, -2.0f, -0.2f);
+    add += 0.5f * (noise_offset * gnoise::fbm(lane4, r2.x, r2.y, r2.z, 4.0 * (double)0.1f, 4, -2.0f, -0.2f));
     return add;
 }
 
@@ -178,7 +179,7 @@ __device__ __forceinline__ void eval_component(const DScene &sc, const DGalaxy &
     default: {                          // GAMER_CLASS_STARS, galaxycomponents.cpp:139-155
         float add = 0.0f;
         if (c.flags & DC_HAS_NOFF) {
-            add = stars_helper_octaves(g, c, s, nz, winding);
+            add = stars_helper_octaves(g, c.noise_offset, s.p.x, s.p.y, s.p.z, nz.lane4, winding);
             if (COUNT) cn.octaves += 8;
         }
         float base = fabsf(n) + 1.0f + add;

@@ -192,19 +192,15 @@ __device__ __forceinline__ void skew(double x, double y, double z, Skewed &su, S
     sw = to_fixed(__dadd_rn(z, s));
 }
 
-// one octave: cells/fractions of (2^k u, 2^k v, 2^k w) and the raw simplex value. `quirk` is a
-// per-call predicate (almost never true) that sends the point through the fastfloor-quirk check.
-__device__ __forceinline__ float octave(uint32_t lane4, const Skewed &su, const Skewed &sv, const Skewed &sw, int k, bool quirk) {
+// one octave: cells/fractions of (2^k u, 2^k v, 2^k w) and the raw simplex value. QUIRK selects the
+// (almost never needed) variant that checks for the reference's fastfloor behaviour at exact integers.
+template <bool QUIRK>
+__device__ __forceinline__ float octave(uint32_t lane4, const Skewed &su, const Skewed &sv, const Skewed &sw, int k) {
     int ci, cj, ck;
     float fu, fv, fw;
-    cell_of<false>(su, k, ci, fu);
-    cell_of<false>(sv, k, cj, fv);
-    cell_of<false>(sw, k, ck, fw);
-    if (quirk) {
-        cell_of<true>(su, k, ci, fu);
-        cell_of<true>(sv, k, cj, fv);
-        cell_of<true>(sw, k, ck, fw);
-    }
+    cell_of<QUIRK>(su, k, ci, fu);
+    cell_of<QUIRK>(sv, k, cj, fv);
+    cell_of<QUIRK>(sw, k, ck, fw);
     return simplex_cell<false>(lane4, ci, cj, ck, fu, fv, fw, nullptr);
 }
 
@@ -214,19 +210,39 @@ __device__ __forceinline__ bool maybe_integer(const Skewed &su, const Skewed &sv
     return ((su.lo & m) == 0u) | ((sv.lo & m) == 0u) | ((sw.lo & m) == 0u);
 }
 
+template <bool QUIRK>
+__device__ __forceinline__ float fbm_sum(uint32_t lane4, const Skewed &su, const Skewed &sv, const Skewed &sw,
+                                         int octaves, float pers) {
+    float total = 0.0f, amp = 1.0f;
+GN_UNROLL(FBM_UNROLL)
+    for (int k = 0; k < octaves; k++) {
+        total = fmaf(octave<QUIRK>(lane4, su, sv, sw, k), amp, total);
+        amp *= pers;
+    }
+    return total;
+}
+// out of line: points on the exact-integer planes of the skewed lattice (fastfloor quirk, simplexnoise.h:130)
+__device__ __noinline__ float fbm_quirk(uint32_t lane4, double x, double y, double z, int octaves, float pers) {
+    Skewed su, sv, sw;
+    skew(x, y, z, su, sv, sw);
+    return fbm_sum<true>(lane4, su, sv, sw, octaves, pers);
+}
+__device__ __noinline__ float octave_quirk(uint32_t lane4, float vx, float vy, float vz) {
+    Skewed su, sv, sw;
+    skew((double)vx, (double)vy, (double)vz, su, sv, sw);
+    return octave<true>(lane4, su, sv, sw, 0);
+}
+
 // Noise::octave_noise_3d (noise.cpp:162-180): sum_k raw(x f_k) a_k / sum a_k, f_k = scale 2^k, a_k = pers^k.
 // (px,py,pz) are the float coordinates the reference widens to double; scale is the double frequency.
 __device__ __forceinline__ float fbm(uint32_t lane4, float px, float py, float pz, double scale,
                                      int octaves, float pers, float inv_maxamp) {
+    const double x = __dmul_rn((double)px, scale), y = __dmul_rn((double)py, scale), z = __dmul_rn((double)pz, scale);
     Skewed su, sv, sw;
-    skew(__dmul_rn((double)px, scale), __dmul_rn((double)py, scale), __dmul_rn((double)pz, scale), su, sv, sw);
-    const bool quirk = maybe_integer(su, sv, sw, octaves - 1);
-    float total = 0.0f, amp = 1.0f;
-GN_UNROLL(FBM_UNROLL)
-    for (int k = 0; k < octaves; k++) {
-        total = fmaf(octave(lane4, su, sv, sw, k, quirk), amp, total);
-        amp *= pers;
-    }
+    skew(x, y, z, su, sv, sw);
+    float total;
+    if (maybe_integer(su, sv, sw, octaves - 1)) total = fbm_quirk(lane4, x, y, z, octaves, pers);
+    else total = fbm_sum<false>(lane4, su, sv, sw, octaves, pers);
     return total * inv_maxamp;
 }
 
@@ -239,7 +255,9 @@ __device__ __forceinline__ float ridged(uint32_t lane4, float vx, float vy, floa
     for (int o = 0; o < octaves; o++) {
         Skewed su, sv, sw;
         skew((double)vx, (double)vy, (double)vz, su, sv, sw);
-        float signal = octave(lane4, su, sv, sw, 0, maybe_integer(su, sv, sw, 0));
+        float signal;
+        if (maybe_integer(su, sv, sw, 0)) signal = octave_quirk(lane4, vx, vy, vz);
+        else signal = octave<false>(lane4, su, sv, sw, 0);
         signal = offset - fabsf(signal);
         signal *= signal;
         signal *= weight;
