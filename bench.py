@@ -135,6 +135,12 @@ def time_cpu(workload: str, row_stride: int, repeats: int = 1):
     return samples / best, o.max_threads(), desc, best
 
 
+# dram__bytes_read.sum + dram__bytes_write.sum of one k1_march launch, from the `ncu --set full` capture
+# summarised in profiles/r01_k1_ncu_summary.csv (the 50 MB framebuffer is still in the 126 MB L2 when the
+# kernel ends, so DRAM sees ~2 MB; the algorithmic bytes are 12 B/pixel = 50 MB)
+K1_DRAM_TRAFFIC = {"spiral_2048_oblique_orbit": 69632 + 1789440}
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -284,7 +290,7 @@ def run_ours(args):
                     "h2d_bytes_per_step": world * ctx_scene_bytes(scenes_[0]), "d2h_bytes_per_step": (1 if tiles else world) * px * 16,
                     "ms_per_step": e2e_ms_max / K, "checksum": checksum},
             "roofline": {"kernel": "k1_march", "bound": "fp32", "achieved": k1_tflops, "peak": fp32_peak, "unit": "TFLOP/s",
-                         "frac": k1_tflops / fp32_peak, "traffic": None,
+                         "frac": k1_tflops / fp32_peak, "traffic": K1_DRAM_TRAFFIC.get(wl),
                          "peak_source": f"{sm_count} SMs x 128 FP32 lanes x 2 flop x {sm_max:.0f} MHz (sm_max_mhz of "
                                         f"MEASURED_PEAKS.json, {peak_src}); the path is FP32/SFU-pipe bound, not HBM or tensor",
                          "algorithmic_flop_per_launch": my_flop / K, "launch_ms": k1_avg_ms},

@@ -42,6 +42,13 @@ class GamerFrame(C.Structure):
                 ("n_galaxies", C.c_int32), ("n_components", C.c_int32), ("_pad2", C.c_int32 * 2)]
 
 
+class GamerStar(C.Structure):
+    _fields_ = [("x", C.c_int32), ("y", C.c_int32), ("w", C.c_int32), ("cs", C.c_float * 3)]
+
+
+STARS_LAYER = C.c_void_p(1)          # GAMER_STARS_LAYER
+
+
 # every symbol include/gamer_b200.h declares (tests check the library exports all of them)
 SYMBOLS = [
     "gamer_b200_abi_version", "gamer_b200_device_count", "gamer_b200_create", "gamer_b200_destroy",
@@ -51,6 +58,7 @@ SYMBOLS = [
     "gamer_b200_launch_count", "gamer_b200_stream", "gamer_b200_camera_inv_vp", "gamer_b200_rotation_to_orientation",
     "gamer_b200_host_alloc", "gamer_b200_host_free",
     "gamer_b200_probe_simplex", "gamer_b200_probe_fbm", "gamer_b200_probe_ridged",
+    "gamer_b200_star_list", "gamer_b200_render_stars",
 ]
 
 _lib = None
@@ -100,6 +108,9 @@ def load():
     lib.gamer_b200_probe_simplex.argtypes = [p, p, C.c_int32, C.c_double, p, p]
     lib.gamer_b200_probe_fbm.argtypes = [p, p, C.c_int32, C.c_int32, C.c_double, C.c_double, p]
     lib.gamer_b200_probe_ridged.argtypes = [p, p, C.c_int32, C.c_double, C.c_int32, C.c_double, C.c_double, C.c_double, p]
+    lib.gamer_b200_star_list.argtypes = [C.c_int32, C.c_int32, C.c_double, C.c_double, C.c_double, C.c_uint64,
+                                         C.POINTER(GamerStar)]
+    lib.gamer_b200_render_stars.argtypes = [p, C.POINTER(GamerStar), C.c_int32, p]
     _lib = lib
     return lib
 

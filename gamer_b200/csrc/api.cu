@@ -23,6 +23,9 @@ struct Dev {
     cudaStream_t st = nullptr, ctrl = nullptr;
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};   // K1 begin/end, K2 begin/end
     float *rgb = nullptr, *stars = nullptr;
+    GamerStar *star_list = nullptr;            // device copy of the last star list (K4 input)
+    size_t cap_star_list = 0;
+    bool layer_valid = false;                  // d.stars holds a K4 layer for the uploaded frame
     uint32_t *argb = nullptr, *shadow = nullptr;
     size_t cap_px = 0, cap_stars = 0;
     unsigned long long *counters = nullptr;
@@ -72,6 +75,7 @@ void free_dev(Dev &d) {
     cudaSetDevice(d.device);
     if (d.rgb) cudaFree(d.rgb);
     if (d.stars) cudaFree(d.stars);
+    if (d.star_list) cudaFree(d.star_list);
     if (d.argb) cudaFree(d.argb);
     if (d.shadow) cudaFree(d.shadow);
     if (d.counters) cudaFree(d.counters);
@@ -163,7 +167,8 @@ int gather_to_host(gamer_ctx *ctx, char *host, size_t elem, int which_buf) {
         Dev &d = ctx->devs[di];
         if (d.rows <= 0) continue;
         CK(cudaSetDevice(d.device));
-        const char *src = which_buf == 0 ? (const char *)d.rgb : which_buf == 1 ? (const char *)d.argb : (const char *)d.shadow;
+        const char *src = which_buf == 0 ? (const char *)d.rgb : which_buf == 1 ? (const char *)d.argb
+                        : which_buf == 2 ? (const char *)d.shadow : (const char *)d.stars;
         if (n == 1) {
             CK(cudaMemcpyAsync(host, src, (size_t)W * H * elem, cudaMemcpyDeviceToHost, d.st));
             continue;
@@ -273,6 +278,7 @@ int gamer_b200_upload(gamer_ctx *ctx, const GamerFrame *frame, const GamerGalaxy
         }
     }
     ctx->frame = *frame;
+    for (Dev &d : ctx->devs) d.layer_valid = false;      // the star layer belongs to one uploaded frame
     ctx->uploaded = true;
     ctx->rendered = false;
     return GAMER_OK;
@@ -318,7 +324,11 @@ static int tonemap_common(gamer_ctx *ctx, double exposure, double gamma, double 
         CK(cudaSetDevice(d.device));
         size_t px = (size_t)d.rows * W;
         const float *stars_dev = nullptr;
-        if (stars_host) {
+        if (stars_host == GAMER_STARS_LAYER) {
+            if (!d.layer_valid) return set_err(ctx, GAMER_E_STATE, "GAMER_STARS_LAYER without a preceding render_stars for this frame");
+            stars_dev = d.stars;
+        } else if (stars_host) {
+            d.layer_valid = false;
             if (d.cap_stars < px) {
                 if (d.stars) cudaFree(d.stars);
                 d.stars = nullptr; d.cap_stars = 0;
@@ -359,6 +369,43 @@ int gamer_b200_tonemap(gamer_ctx *ctx, double exposure, double gamma, double sat
 }
 int gamer_b200_tonemap_device(gamer_ctx *ctx, double exposure, double gamma, double saturation) {
     return tonemap_common(ctx, exposure, gamma, saturation, nullptr, nullptr, nullptr);
+}
+
+// Rasterizer::RenderStars (rasterizer.cpp:215-225): K4 stamps the list into the device star layer.
+int gamer_b200_render_stars(gamer_ctx *ctx, const GamerStar *stars, int32_t n_stars, float *stars_rgb_out_or_null) {
+    if (!ctx || n_stars < 0 || (n_stars > 0 && !stars)) return GAMER_E_ARG;
+    std::lock_guard<std::mutex> lock(ctx->mu);
+    if (!ctx->uploaded) return set_err(ctx, GAMER_E_STATE, "render_stars before upload");
+    const int W = ctx->frame.width;
+    for (Dev &d : ctx->devs) {
+        d.layer_valid = false;
+        if (d.rows <= 0) continue;
+        CK(cudaSetDevice(d.device));
+        const size_t px = (size_t)d.rows * W;
+        if (d.cap_stars < px) {
+            if (d.stars) cudaFree(d.stars);
+            d.stars = nullptr; d.cap_stars = 0;
+            CK(cudaMalloc(&d.stars, px * 3 * sizeof(float)));
+            d.cap_stars = px;
+        }
+        if (d.cap_star_list < (size_t)n_stars) {
+            if (d.star_list) cudaFree(d.star_list);
+            d.star_list = nullptr; d.cap_star_list = 0;
+            CK(cudaMalloc(&d.star_list, (size_t)n_stars * sizeof(GamerStar)));
+            d.cap_star_list = (size_t)n_stars;
+        }
+        CK(cudaMemsetAsync(d.stars, 0, px * 3 * sizeof(float), d.st));                     // fill(QVector3D(0,0,0))
+        if (n_stars > 0) {
+            CK(cudaMemcpyAsync(d.star_list, stars, (size_t)n_stars * sizeof(GamerStar), cudaMemcpyHostToDevice, d.st));
+            CK(gk::launch_k4(d.star_list, n_stars, d.stars, d.scene, d.st));
+            ctx->launches += 1;
+        }
+        d.layer_valid = true;
+    }
+    int rc = sync_all(ctx);
+    if (rc) return rc;
+    if (stars_rgb_out_or_null) { rc = gather_to_host(ctx, (char *)stars_rgb_out_or_null, 3 * sizeof(float), 3); if (rc) return rc; }
+    return GAMER_OK;
 }
 
 // Rasterizer::getPercentDone (rasterizer.h:112-118): fraction of pixel blocks finished. Any thread.

@@ -130,4 +130,47 @@ int gamer_b200_rotation_to_orientation(const float orient[3], float q[4]) {
     return GAMER_OK;
 }
 
+// ---- star list: the expressions of Buffer2D::RenderStars (util/buffer2d.cpp:140-160)
+// over a counter-based generator. Draw j of star i is splitmix64(seed, 16 i + j): no hidden state.
+namespace {
+inline uint64_t splitmix64(uint64_t x) {
+    x += 0x9E3779B97F4A7C15ull;
+    x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
+    x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
+    return x ^ (x >> 31);
+}
+struct StarDraws {
+    uint64_t seed, base;
+    int j = 0;
+    uint64_t next() { return splitmix64(splitmix64(seed) ^ (base + uint64_t(j++))); }
+    double uniform() { return double(next() >> 11) * (1.0 / 9007199254740992.0); }            // [0,1)
+    double gaussian(double mean, double sigma) {                                              // Box-Muller
+        const double u1 = 1.0 - uniform(), u2 = uniform();                                    // u1 in (0,1]
+        return mean + sigma * std::sqrt(-2.0 * std::log(u1)) * std::cos(6.283185307179586 * u2);
+    }
+};
+}  // namespace
+
+int gamer_b200_star_list(int32_t size, int32_t no_stars, double base_size_d, double size_spread_d, double strength,
+                         uint64_t seed, GamerStar *out) {
+    if (size <= 0 || no_stars < 0 || (no_stars > 0 && !out)) return GAMER_E_ARG;
+    const int baseSize = int(base_size_d), sizeSpread = int(size_spread_d);   // RenderStars takes ints (buffer2d.cpp:140)
+    for (int32_t i = 0; i < no_stars; i++) {
+        StarDraws r{seed, uint64_t(i) * 16};
+        GamerStar &s = out[i];
+        s.x = int32_t(r.next() % uint64_t(size));
+        s.y = int32_t(r.next() % uint64_t(size));
+        const double cx = std::fmin(r.uniform() + 0.6, 1.0);
+        const double cy = std::fmin(r.uniform() + double(0.6f), cx);
+        const double cz = std::fmin(r.uniform() + 0.6, 1.0);
+        const double sz = std::fmax(r.gaussian(baseSize, sizeSpread), baseSize / 3.0);
+        s.w = int32_t(int(sz * size) / 245.0);
+        const double ss = sz * std::fabs(r.gaussian(strength, strength));
+        s.cs[0] = float(ss) * float(cx);        // double * QVector3D narrows the scalar first
+        s.cs[1] = float(ss) * float(cy);
+        s.cs[2] = float(ss) * float(cz);
+    }
+    return GAMER_OK;
+}
+
 }  // extern "C"

@@ -349,28 +349,109 @@ k1_march(const __grid_constant__ DScene sc, float *__restrict__ out, unsigned lo
 // ---- K2: Buffer2D::PostProcess + ToColorBuffer (buffer2d.cpp:65-85,106-126) -------------------------
 // HBM-bound: 12 B (+12 B stars) read, 8 B written per pixel. pow is evaluated in double like the
 // reference (3 per pixel; the kernel stays memory-bound).
-__global__ void __launch_bounds__(256)
+__device__ __forceinline__ void tone_px(float x, float y, float z, float inv_exposure, double gamma, double saturation,
+                                        uint32_t &argb, uint32_t &shadow) {
+    x = __fmul_rn(x, inv_exposure); y = __fmul_rn(y, inv_exposure); z = __fmul_rn(z, inv_exposure);
+    if (gamma != 1.0) { x = (float)pow((double)x, gamma); y = (float)pow((double)y, gamma); z = (float)pow((double)z, gamma); }
+    // center = double(float sum) / 3.0, correctly rounded without the generic division: q = RN(s/3) up to an
+    // ulp, r = s - 3q exactly (FMA), q + r/3 rounded once. s has a 24-bit significand, so s/3 is either exact
+    // or continues in the period-2 pattern 0101.../1010... and is never close to a rounding boundary.
+    const double s3 = (double)__fadd_rn(__fadd_rn(x, y), z);
+    const double inv3 = 1.0 / 3.0;
+    const double q3 = __dmul_rn(s3, inv3);
+    double center = __fma_rn(__fma_rn(-3.0, q3, s3), inv3, q3);
+    float tx = (float)(center - x), ty = (float)(center - y), tz = (float)(center - z);
+    x = (float)__dsub_rn(center, __dmul_rn(saturation, (double)tx));
+    y = (float)__dsub_rn(center, __dmul_rn(saturation, (double)ty));
+    z = (float)__dsub_rn(center, __dmul_rn(saturation, (double)tz));
+    x = __fmul_rn(x, 10.0f); y = __fmul_rn(y, 10.0f); z = __fmul_rn(z, 10.0f);
+    // Util::clamp: std::min(255, v) then std::max(0, v) — NaN becomes 255
+    x = (x < 255.0f) ? x : 255.0f; x = (0.0f < x) ? x : 0.0f;
+    y = (y < 255.0f) ? y : 255.0f; y = (0.0f < y) ? y : 0.0f;
+    z = (z < 255.0f) ? z : 255.0f; z = (0.0f < z) ? z : 0.0f;
+    uint32_t r = (uint32_t)(int)x, g = (uint32_t)(int)y, b = (uint32_t)(int)z;
+    argb   = 0xFF000000u | (b << 16) | (g << 8) | r;
+    shadow = 0xFF000000u | (r << 16) | (g << 8) | b;
+}
+
+__global__ void __launch_bounds__(256, 4)
 k2_tonemap(const float *__restrict__ rgb, const float *__restrict__ stars, uint32_t *__restrict__ argb,
            uint32_t *__restrict__ shadow, size_t n, double inv_exposure_d, double gamma, double saturation) {
+    // Persistent grid (4 CTAs per SM, 64 registers per thread), grid-stride, FOUR independent pixels per thread and iteration with all
+    // loads issued before the arithmetic: a single pixel per iteration is a chain of dependent load
+    // latencies. The three 4-byte loads of a warp cover the same 384 contiguous bytes, so every fetched
+    // sector is fully used. Once HBM is fed, the bound is the reference's float<->double traffic:
+    // 16 conversions per pixel on the quarter-rate XU pipe.
     const float inv_exposure = (float)inv_exposure_d;
-    for (size_t k = blockIdx.x * (size_t)blockDim.x + threadIdx.x; k < n; k += (size_t)gridDim.x * blockDim.x) {
+    const size_t nth = (size_t)gridDim.x * blockDim.x;
+    size_t k = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    for (; k + 3 * nth < n; k += 4 * nth) {
+        float v[4][3];
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const size_t q = 3 * (k + u * nth);
+            v[u][0] = rgb[q]; v[u][1] = rgb[q + 1]; v[u][2] = rgb[q + 2];
+        }
+        if (stars) {
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                const size_t q = 3 * (k + u * nth);
+                v[u][0] = __fadd_rn(v[u][0], stars[q]); v[u][1] = __fadd_rn(v[u][1], stars[q + 1]); v[u][2] = __fadd_rn(v[u][2], stars[q + 2]);
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            uint32_t o, h;
+            tone_px(v[u][0], v[u][1], v[u][2], inv_exposure, gamma, saturation, o, h);
+            if (argb)   argb[k + u * nth] = o;
+            if (shadow) shadow[k + u * nth] = h;
+        }
+    }
+    for (; k < n; k += nth) {
         float x = rgb[3 * k], y = rgb[3 * k + 1], z = rgb[3 * k + 2];
         if (stars) { x = __fadd_rn(x, stars[3 * k]); y = __fadd_rn(y, stars[3 * k + 1]); z = __fadd_rn(z, stars[3 * k + 2]); }
-        x = __fmul_rn(x, inv_exposure); y = __fmul_rn(y, inv_exposure); z = __fmul_rn(z, inv_exposure);
-        if (gamma != 1.0) { x = (float)pow((double)x, gamma); y = (float)pow((double)y, gamma); z = (float)pow((double)z, gamma); }
-        double center = (double)__fadd_rn(__fadd_rn(x, y), z) / 3.0;
-        float tx = (float)(center - x), ty = (float)(center - y), tz = (float)(center - z);
-        x = (float)__dsub_rn(center, __dmul_rn(saturation, (double)tx));
-        y = (float)__dsub_rn(center, __dmul_rn(saturation, (double)ty));
-        z = (float)__dsub_rn(center, __dmul_rn(saturation, (double)tz));
-        x = __fmul_rn(x, 10.0f); y = __fmul_rn(y, 10.0f); z = __fmul_rn(z, 10.0f);
-        // Util::clamp: std::min(255, v) then std::max(0, v) — NaN becomes 255
-        x = (x < 255.0f) ? x : 255.0f; x = (0.0f < x) ? x : 0.0f;
-        y = (y < 255.0f) ? y : 255.0f; y = (0.0f < y) ? y : 0.0f;
-        z = (z < 255.0f) ? z : 255.0f; z = (0.0f < z) ? z : 0.0f;
-        uint32_t r = (uint32_t)(int)x, g = (uint32_t)(int)y, b = (uint32_t)(int)z;
-        if (argb)   argb[k]   = 0xFF000000u | (b << 16) | (g << 8) | r;
-        if (shadow) shadow[k] = 0xFF000000u | (r << 16) | (g << 8) | b;
+        uint32_t o, h;
+        tone_px(x, y, z, inv_exposure, gamma, saturation, o, h);
+        if (argb)   argb[k] = o;
+        if (shadow) shadow[k] = h;
+    }
+}
+
+// ---- K4: background star layer. Buffer2D::RenderGaussian (buffer2d.cpp:224-243) for every star --------
+// One warp per star, lanes over the stamp. The reference combines stamps with a per-channel max, which
+// commutes: an atomicMax on the bit pattern of the (non-negative) float gives the identical layer.
+__global__ void __launch_bounds__(256)
+k4_stars(const GamerStar *__restrict__ stars, int n, float *__restrict__ layer, int full_size, int x0, int y0,
+         int width, int height, int band_rows, int band_stride) {
+    const int star = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (star >= n) return;
+    const GamerStar s = stars[star];
+    const int w = s.w, half = w / 2, side = 2 * half;           // for (x = -w/2; x < w/2; x++)
+    if (side <= 0) return;
+    const double ss = (double)0.01f;
+    for (int idx = lane; idx < side * side; idx += 32) {
+        const int x = idx / side - half, y = idx % side - half;
+        const int xx = s.x + x, yy = s.y + y;
+        if (xx < 0 || xx >= full_size || yy < 0 || yy >= full_size) continue;
+        // image pixel -> this context's local framebuffer (tile origin, interleaved bands)
+        const int lx = xx - x0;
+        int rel = yy - y0, ly;
+        if (lx < 0 || lx >= width || rel < 0) continue;
+        if (band_rows > 0) {
+            const int r = rel % band_stride;
+            if (r >= band_rows) continue;
+            ly = (rel / band_stride) * band_rows + r;
+        } else ly = rel;
+        if (ly >= height) continue;
+        const double dx = x / (double)w, dy = y / (double)w;
+        const double d = __dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy));
+        const float v = (float)exp(-d / ss);
+        unsigned int *dst = reinterpret_cast<unsigned int *>(layer + 3 * ((size_t)ly * width + lx));
+#pragma unroll
+        for (int c = 0; c < 3; c++) {
+            const float val = __fmul_rn(v, s.cs[c]);
+            if (val > 0.0f) atomicMax(dst + c, __float_as_uint(val));
+        }
     }
 }
 
@@ -448,10 +529,17 @@ cudaError_t launch_k1(const DScene &sc, float *out_dev, unsigned long long *coun
 cudaError_t launch_k2(const float *rgb, const float *stars, uint32_t *argb, uint32_t *shadow, size_t n, double exposure,
                       double gamma, double saturation, int sm_count, cudaStream_t st) {
     size_t want = (n + 255) / 256;
-    size_t cap = (size_t)sm_count * 8;          // 8 resident CTAs of 256 threads per SM, grid-stride
+    size_t cap = (size_t)sm_count * 4;          // 4 resident CTAs of 256 threads per SM (64 registers each), grid-stride
     int blocks = (int)(want < cap ? want : cap);
     if (blocks < 1) blocks = 1;
     k2_tonemap<<<blocks, 256, 0, st>>>(rgb, stars, argb, shadow, n, 1.0 / exposure, gamma, saturation);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_k4(const GamerStar *stars, int n, float *layer, const DScene &sc, cudaStream_t st) {
+    if (n <= 0) return cudaSuccess;
+    k4_stars<<<(n + 7) / 8, 256, 0, st>>>(stars, n, layer, sc.full_size, sc.x0, sc.y0, sc.width, sc.height, sc.band_rows,
+                                          sc.band_stride);
     return cudaGetLastError();
 }
 

@@ -189,6 +189,14 @@ int RasterizerB200::AssembleImage() {
     m_imageBuffer.assign(px, 0);
     m_imageShadowBuffer.assign(px, 0);
     const float* stars = (!m_isPreview && m_starsBuffer.size() == px * 3) ? m_starsBuffer.data() : nullptr;
+    if (!m_isPreview && m_deviceStars && rp.m_noStars > 0) {
+        std::vector<GamerStar> list(size_t(rp.m_noStars));
+        int rc = gamer_b200_star_list(rp.size(), rp.m_noStars, rp.m_starSize, rp.m_starSizeSpread, rp.m_starStrength, m_starSeed,
+                                      list.data());
+        if (rc == GAMER_OK) rc = gamer_b200_render_stars(m_ctx, list.data(), int32_t(list.size()), nullptr);
+        if (rc != GAMER_OK) return rc;
+        stars = GAMER_STARS_LAYER;
+    }
     return gamer_b200_tonemap(m_ctx, double(rp.m_exposure), double(rp.m_gamma), double(rp.m_saturation), stars,
                               m_imageBuffer.data(), m_imageShadowBuffer.data());
 }

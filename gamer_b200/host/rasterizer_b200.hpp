@@ -50,6 +50,7 @@ public:
     int m_size = 128;
     float m_exposure = 1, m_gamma = 1, m_saturation = 1, m_rayStep = 0.001f;
     int m_noStars = 0;
+    double m_starSize = 1, m_starSizeSpread = 1, m_starStrength = 1;   // renderingparams.h:28-30
     GamerCamera m_camera;
     Spectra m_spectra;
     GamerCamera& camera() { return m_camera; }
@@ -111,7 +112,9 @@ public:
     const char* lastError() const;
 
     // post-process (rasterizer.cpp:315-327)
-    void RenderStars(const std::vector<float>& stars_rgb) { m_starsBuffer = stars_rgb; }
+    void RenderStars(const std::vector<float>& stars_rgb) { m_starsBuffer = stars_rgb; m_deviceStars = false; }
+    // rasterizer.cpp:215-225: layer from noStars/starSize/starSizeSpread/starStrength, stamped on the device (K4)
+    void RenderStars(uint64_t seed = 0) { m_deviceStars = true; m_starSeed = seed; }
     int AssembleImage();
 
     // outputs
@@ -132,6 +135,8 @@ private:
     std::atomic<State> m_state{idle};
     std::atomic<int> m_status{0};
     bool m_isPreview = false;
+    bool m_deviceStars = false;
+    uint64_t m_starSeed = 0;
     int m_width = 0, m_height = 0;
     std::thread m_thread;
 };

@@ -67,6 +67,9 @@ class RenderingParams:
     m_saturation: float = 1.0
     m_rayStep: float = 0.001
     m_noStars: int = 0
+    m_starSize: float = 1.0            # renderingparams.h:29-30
+    m_starSizeSpread: float = 1.0
+    m_starStrength: float = 1.0
     m_camera: GamerCamera = field(default_factory=GamerCamera)
     m_spectra: Spectra = field(default_factory=Spectra)
 

@@ -76,6 +76,22 @@ class Context:
                                                        argb.ctypes.data, shadow.ctypes.data))
         return argb, shadow
 
+    def render_stars(self, stars, want_layer=False):
+        """K4: stamp a GamerStar array (see star_list) into the device star layer of the uploaded frame."""
+        n = len(stars)
+        out = np.empty(self.shape + (3,), dtype=np.float32) if want_layer else None
+        _lib.check(self.h, self.lib.gamer_b200_render_stars(self.h, stars, n, out.ctypes.data if want_layer else None))
+        return out
+
+    def tonemap_layer(self, exposure=1.0, gamma=1.0, saturation=1.0):
+        """AssembleImage with the device star layer (GAMER_STARS_LAYER)."""
+        h, w = self.shape
+        argb = np.empty((h, w), dtype=np.uint32)
+        shadow = np.empty((h, w), dtype=np.uint32)
+        _lib.check(self.h, self.lib.gamer_b200_tonemap(self.h, exposure, gamma, saturation, _lib.STARS_LAYER,
+                                                       argb.ctypes.data, shadow.ctypes.data))
+        return argb, shadow
+
     def tonemap_ptr(self, exposure, gamma, saturation, argb_ptr, shadow_ptr):
         _lib.check(self.h, self.lib.gamer_b200_tonemap(self.h, exposure, gamma, saturation, None, argb_ptr, shadow_ptr))
 
@@ -149,6 +165,15 @@ class Context:
         _lib.check(self.h, self.lib.gamer_b200_probe_ridged(self.h, xyz.ctypes.data, xyz.shape[0], frequency, octaves, lacunarity,
                                                             offset, gain, val.ctypes.data))
         return val
+
+
+def star_list(size, no_stars, base_size, size_spread, strength, seed=0):
+    """gamer_b200_star_list: the deterministic stand-in for the reference's rand()-driven star parameters."""
+    lib = _lib.load()
+    arr = (_lib.GamerStar * max(1, int(no_stars)))()
+    _lib.check(None, lib.gamer_b200_star_list(int(size), int(no_stars), float(base_size), float(size_spread), float(strength),
+                                              int(seed), arr))
+    return (_lib.GamerStar * int(no_stars)).from_buffer(arr) if no_stars > 0 else (_lib.GamerStar * 0)()
 
 
 class Rasterizer:
@@ -239,13 +264,23 @@ class Rasterizer:
     def Abort(self):
         self._ctx.abort()
 
-    def RenderStars(self, stars: np.ndarray):
-        """The star layer is rand()-driven host code in the reference (buffer2d.cpp:140-173); a caller
-        supplies the buffer and AssembleImage adds it (rasterizer.cpp:320-321)."""
+    def RenderStars(self, stars: Optional[np.ndarray] = None, seed: int = 0):
+        """Rasterizer::RenderStars (rasterizer.cpp:215-225). Without an argument the layer is generated on the
+        device from RenderingParams' noStars / starSize / starSizeSpread / starStrength (K4; the star
+        parameters come from the documented counter-based generator, the reference's are rand()-driven and
+        not reproducible). A caller may instead hand in its own float layer [N,N,3]."""
         self.m_starsBuffer = stars
+        self._star_seed = seed
+        self._device_stars = stars is None
 
     def AssembleImage(self):
         rp = self.m_renderingParams
+        if not self.m_isPreview and getattr(self, "_device_stars", False) and rp.m_noStars > 0:
+            n = self._ctx.shape[0] if self._ctx.shape else rp.m_size
+            lst = star_list(rp.m_size, rp.m_noStars, rp.m_starSize, rp.m_starSizeSpread, rp.m_starStrength, self._star_seed)
+            self._ctx.render_stars(lst)
+            self.m_imageBuffer, self.m_imageShadowBuffer = self._ctx.tonemap_layer(rp.m_exposure, rp.m_gamma, rp.m_saturation)
+            return
         stars = None if self.m_isPreview else self.m_starsBuffer
         self.m_imageBuffer, self.m_imageShadowBuffer = self._ctx.tonemap(rp.m_exposure, rp.m_gamma, rp.m_saturation, stars)
 

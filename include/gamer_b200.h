@@ -148,6 +148,36 @@ int  gamer_b200_tonemap(gamer_ctx *ctx, double exposure, double gamma, double sa
                         uint32_t *argb_out, uint32_t *argb_shadow_out);
 int  gamer_b200_tonemap_device(gamer_ctx *ctx, double exposure, double gamma, double saturation);
 
+/* ---- background star layer ---------------------------------------------------
+ * Rasterizer::RenderStars (rasterizer.cpp:215-225) -> Buffer2D::RenderStars (util/buffer2d.cpp:140-173)
+ * -> Buffer2D::RenderGaussian (:224-243): every star is a w x w Gaussian stamp exp(-(dx^2+dy^2)/0.01f)
+ * times an RGB strength, combined into the layer with a per-channel MAX, so the layer does not depend
+ * on the order of the stars. AssembleImage adds the layer to the frame (rasterizer.cpp:320-321).
+ *
+ * The reference draws the star parameters from libc rand() and a process-global std::mt19937
+ * (util/random.h:49-53) whose state depends on everything drawn before: that sequence is not
+ * reproducible, so parity of the star LIST can only be statistical. gamer_b200_star_list defines it
+ * instead by a counter-based generator (splitmix64 of (seed, star index, draw index); Gaussians by
+ * Box-Muller), with the reference's expressions for position, colour, size and strength — including
+ * RenderStars' `int baseSize, int sizeSpread` parameters, which truncate the doubles it is called with.
+ * The STAMPING (gamer_b200_render_stars) follows the reference exactly and is checked against the oracle. */
+typedef struct {
+    int32_t x, y;               /* centre pixel, in the full_size x full_size image              */
+    int32_t w;                  /* stamp width `asz` (pixels); 0 draws nothing                   */
+    float   cs[3];              /* ss * (cx, cy, cz) as the float QVector3D RenderGaussian gets  */
+} GamerStar;
+
+/* Host: fill out[no_stars] for an image of `size` pixels. Deterministic in all arguments. */
+int  gamer_b200_star_list(int32_t size, int32_t no_stars, double base_size, double size_spread,
+                          double strength, uint64_t seed, GamerStar *out);
+/* K4: stamp the stars into the context's device star layer for the uploaded frame (tile and band
+ * addressing honoured); optionally copy the layer to the host (width*height*3 floats). */
+int  gamer_b200_render_stars(gamer_ctx *ctx, const GamerStar *stars, int32_t n_stars,
+                             float *stars_rgb_out_or_null);
+/* Pass this as `stars_rgb_or_null` of gamer_b200_tonemap to add the device layer made by
+ * gamer_b200_render_stars instead of a host buffer. */
+#define GAMER_STARS_LAYER ((const float *)(uintptr_t)1)
+
 /* control (callable from any thread; rasterizer.h:91-118) ----------------------------------- */
 int  gamer_b200_progress(gamer_ctx *ctx, double *fraction);
 int  gamer_b200_abort   (gamer_ctx *ctx);

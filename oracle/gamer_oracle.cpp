@@ -547,6 +547,32 @@ int go_tonemap(const float *rgb, int width, int height, double exposure, double 
     return GAMER_OK;
 }
 
+// Buffer2D::RenderStars' drawing part (util/buffer2d.cpp:140-143,161) + Buffer2D::RenderGaussian
+// (:224-243) + Util::maxQvector3D (util/util.h:175-177), in star order, sequentially like the reference.
+// The star parameters themselves come from the caller (gamer_b200_star_list documents why).
+int go_stamp_stars(int size, const GamerStar *stars, int n, float *layer_out) {
+    if (size <= 0 || !layer_out || (n > 0 && !stars)) return GAMER_E_ARG;
+    std::fill(layer_out, layer_out + (size_t)size * size * 3, 0.0f);            // fill(QVector3D(0,0,0))
+    for (int q = 0; q < n; q++) {
+        const int i = stars[q].x, j = stars[q].y, w = stars[q].w;
+        const float *cs = stars[q].cs;
+        for (int x = -w / 2; x < w / 2; x++)
+            for (int y = -w / 2; y < w / 2; y++) {
+                int xx = i + x, yy = j + y;
+                double dx = x / (double)w, dy = y / (double)w;
+                if (xx >= 0 && xx < size && yy >= 0 && yy < size) {
+                    double d = (dx * dx + dy * dy);
+                    double ss = 0.01f;
+                    double v = exp(-d / ss);
+                    float *px = layer_out + 3 * ((size_t)xx + (size_t)yy * size);
+                    const float vf = (float)v;                                  // double * QVector3D narrows first
+                    for (int c = 0; c < 3; c++) px[c] = (float)fmax(vf * cs[c], px[c]);
+                }
+            }
+    }
+    return GAMER_OK;
+}
+
 double go_raw3d(double x, double y, double z) { return simplex3(x, y, z); }
 
 int go_simplex(const float *xyz, int n, double frequency, int32_t *lattice_out, double *value_out) {

@@ -28,6 +28,7 @@ class Oracle:
         lib.go_camera_inv_vp.argtypes = [p, p, p, C.c_double, p]
         lib.go_rotation_to_orientation.argtypes = [p, p]
         lib.go_coord2ray.argtypes = [p, C.c_int, C.c_int, p]
+        lib.go_stamp_stars.argtypes = [C.c_int, p, C.c_int, p]
 
     def max_threads(self):
         return self.lib.go_max_threads()
@@ -53,6 +54,12 @@ class Oracle:
             sp = stars.ctypes.data
         assert self.lib.go_tonemap(rgb.ctypes.data, w, h, exposure, gamma, saturation, sp, a.ctypes.data, s.ctypes.data) == 0
         return a, s
+
+    def stamp_stars(self, size, stars):
+        """stars: ctypes array of gamer_b200._lib.GamerStar. Returns the star layer [size,size,3] float32."""
+        out = np.empty((size, size, 3), dtype=np.float32)
+        assert self.lib.go_stamp_stars(size, C.addressof(stars) if len(stars) else None, len(stars), out.ctypes.data) == 0
+        return out
 
     def simplex(self, xyz, frequency=1.0):
         xyz = np.ascontiguousarray(xyz, dtype=np.float32)

@@ -142,3 +142,44 @@ def test_oracle_tonemap(oracle):
     assert s[0, 0] == 0xFF000000 | (0 << 16) | (10 << 8) | 25
     assert s[0, 1] == 0xFF000000 | (255 << 16) | (0 << 8) | 123
     assert a[0, 1] == 0xFF000000 | (123 << 16) | (0 << 8) | 255
+
+
+def test_star_list_is_deterministic_and_follows_renderstars():
+    """gamer_b200_star_list: buffer2d.cpp:140-160's expressions over a counter-based generator."""
+    from gamer_b200.rasterizer import star_list
+    a = star_list(512, 4000, 0.51, 1.5, 1.0, seed=3)
+    b = star_list(512, 4000, 0.51, 1.5, 1.0, seed=3)
+    c = star_list(512, 4000, 0.51, 1.5, 1.0, seed=4)
+    assert bytes(a) == bytes(b) and bytes(a) != bytes(c)
+    assert bytes(star_list(512, 10, 0.51, 1.5, 1.0, seed=3)) == bytes(a)[:10 * 24]      # star i does not depend on n
+    x = np.array([s.x for s in a]); y = np.array([s.y for s in a]); w = np.array([s.w for s in a])
+    cs = np.array([list(s.cs) for s in a])
+    assert x.min() >= 0 and x.max() < 512 and y.min() >= 0 and y.max() < 512
+    assert abs(x.mean() - 255.5) < 10 and abs(y.mean() - 255.5) < 10
+    # int baseSize = 0, int sizeSpread = 1: sz = max(N(0,1), 0); w = int(int(sz*512)/245.0) is 0 below sz = 245/512
+    import math
+    p0 = 0.5 * (1 + math.erf((245 / 512) / math.sqrt(2)))
+    assert abs((w == 0).mean() - p0) < 0.03 and w.min() == 0
+    assert (cs >= 0).all() and (cs[:, 1] <= cs[:, 0] + 1e-6).all()        # cy = min(u + 0.6f, cx)
+    big = star_list(2048, 2000, 3.0, 1.0, 2.0, seed=1)                      # baseSize 3: sz >= 1
+    assert min(s.w for s in big) >= int(int(1.0 * 2048) / 245.0)
+
+
+def test_oracle_star_stamp(oracle):
+    """RenderGaussian: peak = cs at the centre pixel, per-channel max where stamps overlap, clipped at the border."""
+    from gamer_b200._lib import GamerStar
+    stars = (GamerStar * 3)()
+    stars[0].x, stars[0].y, stars[0].w = 10, 12, 8
+    stars[0].cs[:] = [1.0, 0.5, 0.25]
+    stars[1].x, stars[1].y, stars[1].w = 12, 12, 8
+    stars[1].cs[:] = [0.5, 2.0, 0.25]
+    stars[2].x, stars[2].y, stars[2].w = 0, 31, 6              # clipped at two borders
+    stars[2].cs[:] = [3.0, 3.0, 3.0]
+    layer = oracle.stamp_stars(32, stars)
+    g = np.float32(np.exp(-(2 / 8) ** 2 / np.float64(np.float32(0.01))))      # two pixels from a centre, w = 8
+    assert np.array_equal(layer[12, 10], np.float32([1.0, 0.5, 0.25]))          # max(own centre, neighbour's tail)
+    assert np.array_equal(layer[12, 12], np.float32([0.5, 2.0, 0.25]))
+    assert layer[31, 0, 0] == 3.0
+    assert layer[12, 14, 0] == np.float32(0.5) * g        # star 0 stops at x < 4: only star 1 reaches column 14
+    assert layer[12 + 4].sum() == 0 and layer[:, 20:].sum() == 0
+    assert oracle.stamp_stars(16, (GamerStar * 0)()).sum() == 0

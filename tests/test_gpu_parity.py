@@ -208,6 +208,49 @@ def test_tonemap_exact(gpu_ctx, oracle):
     assert d.max() <= 1 and (d > 0).mean() < 1e-3
 
 
+def test_tonemap_ragged_sizes(gpu_ctx, oracle):
+    """pixel counts that are not a multiple of the kernel's 4-pixel vector width (tail path), with stars"""
+    for size in (33, 35, 37):
+        sc = scenes.single_galaxy_scene("Sombrero", size, "oblique")
+        gpu_ctx.upload(sc)
+        img = gpu_ctx.render()
+        stars = np.random.default_rng(size).uniform(0, 2, img.shape).astype(np.float32)
+        a_g, s_g = gpu_ctx.tonemap(0.9, 1.0, 1.2, stars)
+        a_c, s_c = oracle.tonemap(img, 0.9, 1.0, 1.2, stars)
+        assert np.array_equal(a_g, a_c) and np.array_equal(s_g, s_c), size
+
+
+def test_star_layer_matches_oracle(gpu_ctx, oracle):
+    """K4 against Buffer2D::RenderGaussian restated on the CPU: full frame, a tile, and interleaved bands."""
+    from gamer_b200.rasterizer import star_list
+    size = 160
+    lst = star_list(size, 3000, 3.0, 2.0, 1.0, seed=11)
+    want = oracle.stamp_stars(size, lst)
+    assert (want > 0).mean() > 0.02
+    full = scenes.single_galaxy_scene("Spiral", size, "oblique")
+
+    def close(a, b):          # libdevice exp vs glibc exp: at most one float ulp after narrowing
+        return np.all(np.abs(a - b) <= 1.2e-7 * np.abs(b) + 1e-37)
+
+    gpu_ctx.upload(full)
+    assert close(gpu_ctx.render_stars(lst, want_layer=True), want)
+    gpu_ctx.upload(full.tile(24, 40, 100, 64))
+    assert close(gpu_ctx.render_stars(lst, want_layer=True), want[40:104, 24:124])
+    B, G = 32, 3
+    for r in range(G):
+        rows = [y for y in range(size) if (y // B) % G == r]
+        gpu_ctx.upload(full.tile(0, r * B, size, len(rows), band_rows=B, band_stride=B * G))
+        assert close(gpu_ctx.render_stars(lst, want_layer=True), want[rows])
+    # AssembleImage with the device layer == tonemap with the same layer handed in from the host
+    gpu_ctx.upload(full)
+    gpu_ctx.render()
+    layer = gpu_ctx.render_stars(lst, want_layer=True)
+    a1, s1 = gpu_ctx.tonemap_layer(0.9, 1.0, 1.2)
+    a2, s2 = gpu_ctx.tonemap(0.9, 1.0, 1.2, layer)
+    assert np.array_equal(a1, a2) and np.array_equal(s1, s2)
+    assert (s1 != gpu_ctx.tonemap(0.9, 1.0, 1.2)[1]).mean() > 0.01
+
+
 def test_rasterizer_api(oracle):
     """Drive the reference-shaped class the way ConsoleRenderer::RenderSingleGalaxy does."""
     import time
