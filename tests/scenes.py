@@ -74,3 +74,66 @@ def synthetic_galaxy(kind="allclasses") -> Galaxy:
         C("disk", 300.0, "White", 0.5, 0.02, 0.3, 0.0, 0.0, 0.1, 3.0, 0.0, 1.0, 1.0, 0.0, "inactive"),
     ]
     return g
+
+
+# ---- BASELINE configs 4 and 5 as concrete inputs -----------------------------------------
+
+def orbit_camera(k, n_frames=360):
+    """C4: cam_k = 0.9 (cos t cos 0.35, sin 0.35, sin t cos 0.35), t = 2 pi k / n, target origin, fov 60."""
+    t = 2.0 * math.pi * k / n_frames
+    return ((0.9 * math.cos(t) * math.cos(0.35), 0.9 * math.sin(0.35), 0.9 * math.sin(t) * math.cos(0.35)),
+            (0, 0, 0), (0, 1, 0), 60.0)
+
+
+def hd_frame_scene(k, width=1920, height=1080, galaxy="Spiral", n_frames=360):
+    """C4: the reference only renders squares, so 1920x1080 is the centred crop (rows 420..1499) of the
+    full_size = 1920 square image: every pixel is the reference's pixel at size 1920."""
+    full = single_galaxy_scene(galaxy, width, orbit_camera(k, n_frames))
+    return full.tile(0, (width - height) // 2, width, height)
+
+
+def random_galaxy(rng) -> Galaxy:
+    """C5: one galaxy of the seeded sweep (ranges from SURVEY.md §8d, row C5)."""
+    def logu(a, b):
+        return float(math.exp(rng.uniform(math.log(a), math.log(b))))
+    g = Galaxy()
+    p = g.galaxyParams
+    p.name = "random"
+    p.windingB = float(rng.uniform(0.4, 3.0))
+    p.windingN = float(rng.choice([2, 4, 5]))
+    p.noArms = float(rng.choice([1, 2, 3, 4]))
+    p.arm1, p.arm2, p.arm3, p.arm4 = 0.0, 3.14, 1.57, 4.71
+    spectra = ["Red", "Yellow", "Blue", "White", "Cyan", "Purple"]
+    n = int(rng.integers(3, 9))
+    classes = ["bulge", "disk"] + [str(rng.choice(["bulge", "disk", "dust", "dust2", "stars"])) for _ in range(n - 2)]
+    comps = []
+    for cls in classes:
+        c = ComponentParams(className=cls, name=cls, spectrum=str(rng.choice(spectra)))
+        c.strength = {"bulge": logu(5, 5000), "disk": logu(5, 5000), "dust": logu(10, 500), "dust2": logu(10, 500),
+                      "stars": logu(0.5, 100)}[cls]
+        c.arm = float(rng.uniform(0.01, 1.0))
+        c.z0 = float(rng.uniform(0.01, 0.07))
+        c.r0 = float(rng.uniform(3, 25)) if cls == "bulge" else float(rng.uniform(0.15, 0.6))
+        c.inner = float(rng.uniform(0, 0.6))
+        c.active = 1.0
+        c.delta = float(rng.uniform(0, 2.5))
+        c.winding = float(rng.uniform(0, 0.5))
+        c.scale = float(rng.uniform(5, 150)) if cls == "stars" else float(rng.uniform(1, 20))
+        c.noiseOffset = float(rng.uniform(1, 1.5)) if cls == "dust2" else 0.0
+        c.noiseTilt = {"disk": float(rng.uniform(0.01, 1.0)), "dust2": float(rng.uniform(1, 1.5)),
+                       "stars": float(rng.uniform(8, 20))}.get(cls, 1.0)
+        c.ks = 1.0 if rng.uniform() < 0.5 else float(rng.choice([-0.5, -0.8]))
+        comps.append(c)
+    g.componentParams = comps
+    return g
+
+
+def random_galaxy_scene(index, size=1024, seed=20261104):
+    """C5: galaxy `index` of the sweep and its camera (uniform on the |cam| = 0.9 sphere, fov 60).
+    Every galaxy has its own generator stream, so any rank can build any galaxy."""
+    rng = np.random.default_rng([seed, index])
+    g = random_galaxy(rng)
+    v = rng.normal(size=3)
+    v = 0.9 * v / np.linalg.norm(v)
+    up = (0, 1, 0) if abs(v[1]) < 0.85 else (1, 0, 0)
+    return single_galaxy_scene(g, size, ((float(v[0]), float(v[1]), float(v[2])), (0, 0, 0), up, 60.0))

@@ -220,6 +220,28 @@ def test_tonemap_ragged_sizes(gpu_ctx, oracle):
         assert np.array_equal(a_g, a_c) and np.array_equal(s_g, s_c), size
 
 
+def test_c4_hd_crop_frames(gpu_ctx, oracle):
+    """BASELINE config 4 (rotating camera, 16:9): a 16:9 frame is the centred crop of the square image, checked at
+    small size for several orbit angles; sample counts exact, pixels equal the same rows of the square frame."""
+    for k in (0, 77, 200):
+        sc = scenes.hd_frame_scene(k, width=160, height=90)
+        assert (sc.frame.width, sc.frame.height, sc.frame.full_size, sc.frame.y0) == (160, 90, 160, 35)
+        what = f"C4 frame {k}"
+        check_scene(gpu_ctx, oracle, sc, what)
+    sq = scenes.single_galaxy_scene("Spiral", 160, scenes.orbit_camera(77))
+    gpu_ctx.upload(sq)
+    whole = gpu_ctx.render()
+    gpu_ctx.upload(scenes.hd_frame_scene(77, width=160, height=90))
+    assert np.array_equal(gpu_ctx.render(), whole[35:125])
+
+
+@pytest.mark.parametrize("index", [0, 1, 2, 3, 5, 8, 13, 21])
+def test_c5_random_galaxies(gpu_ctx, oracle, index):
+    """BASELINE config 5: galaxies of the seeded randomised sweep (3-8 components, all classes, negative
+    persistence, 1-4 arms, random exterior cameras)."""
+    check_scene(gpu_ctx, oracle, scenes.random_galaxy_scene(index, size=72), f"C5 galaxy {index}")
+
+
 def test_star_layer_matches_oracle(gpu_ctx, oracle):
     """K4 against Buffer2D::RenderGaussian restated on the CPU: full frame, a tile, and interleaved bands."""
     from gamer_b200.rasterizer import star_list
