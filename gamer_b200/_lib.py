@@ -11,6 +11,8 @@ LIB_PATH = os.environ.get("GAMER_B200_LIB") or os.path.join(_HERE, "lib", "libga
 
 CNT_RAYS, CNT_SAMPLES, CNT_GATES, CNT_COMP_EVALS, CNT_OCTAVES, CNT_N = 0, 1, 2, 3, 4, 8
 E_ARG, E_CUDA, E_ABORTED, E_STATE = -1, -2, -3, -4
+FRAME_CONTINUE, FRAME_PARTIAL = 1, 2
+MAX_GALAXIES, MAX_COMPONENTS = 8, 64
 
 CLASS_IDS = {          # factory strings of source/galaxy/galaxy.cpp:15-42
     "bulge": 0, "disk": 1, "dust": 2, "dust2": 3, "dust positive": 4, "stars": 5, "stars small": 6,
@@ -36,7 +38,7 @@ class GamerGalaxy(C.Structure):
 class GamerFrame(C.Structure):
     _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("full_size", C.c_int32),
                 ("x0", C.c_int32), ("y0", C.c_int32), ("band_rows", C.c_int32), ("band_stride", C.c_int32),
-                ("_pad0", C.c_int32),
+                ("flags", C.c_int32),
                 ("inv_vp", C.c_float * 16), ("cam", C.c_float * 3), ("_pad1", C.c_float),
                 ("ray_step", C.c_double), ("min_ray_step", C.c_double),
                 ("n_galaxies", C.c_int32), ("n_components", C.c_int32), ("_pad2", C.c_int32 * 2)]

@@ -121,7 +121,8 @@ int launch_render(gamer_ctx *ctx, bool counted) {
         CK(cudaMemsetAsync(d.progress, 0, sizeof(unsigned int), d.st));
         CK(cudaMemsetAsync(d.abort_flag, 0, sizeof(int), d.st));
         if (counted) CK(cudaMemsetAsync(d.counters, 0, GAMER_CNT_N * sizeof(unsigned long long), d.st));
-        CK(cudaMemsetAsync(d.rgb, 0, (size_t)d.rows * d.scene.width * 3 * sizeof(float), d.st));
+        if (!(d.scene.flags & GAMER_FRAME_CONTINUE))
+            CK(cudaMemsetAsync(d.rgb, 0, (size_t)d.rows * d.scene.width * 3 * sizeof(float), d.st));
         CK(cudaEventRecord(d.ev[0], d.st));
         CK(gk::launch_k1(d.scene, d.rgb, d.counters, d.abort_flag, d.progress, counted, d.st, &d.n_blocks));
         CK(cudaEventRecord(d.ev[1], d.st));
@@ -259,6 +260,13 @@ int gamer_b200_upload(gamer_ctx *ctx, const GamerFrame *frame, const GamerGalaxy
     std::lock_guard<std::mutex> lock(ctx->mu);
     const int n = (int)ctx->devs.size();
     if (n > 1 && frame->band_rows != 0) return set_err(ctx, GAMER_E_ARG, "a multi-device context splits bands itself: band_rows must be 0");
+    if (frame->flags & GAMER_FRAME_CONTINUE) {     // a later pass of a multi-pass frame: same geometry, previous pass left raw I
+        const GamerFrame &p = ctx->frame;
+        if (!ctx->rendered || !(p.flags & GAMER_FRAME_PARTIAL) || p.width != frame->width || p.height != frame->height ||
+            p.full_size != frame->full_size || p.x0 != frame->x0 || p.y0 != frame->y0 || p.band_rows != frame->band_rows ||
+            p.band_stride != frame->band_stride)
+            return set_err(ctx, GAMER_E_STATE, "GAMER_FRAME_CONTINUE needs a rendered GAMER_FRAME_PARTIAL pass of the same frame geometry");
+    }
     char msg[256] = {0};
     for (int di = 0; di < n; di++) {
         Dev &d = ctx->devs[di];

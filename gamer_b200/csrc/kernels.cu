@@ -305,7 +305,9 @@ k1_march(const __grid_constant__ DScene sc, float *__restrict__ out, unsigned lo
             w.z = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(v0, m[8]), __fmul_rn(v1, m[9])), m[10]), m[11]);
         }
         const f3 d = v_normalized(w);
+        float *dst = out + 3 * ((size_t)ly * sc.width + lx);
         float Ir = 0.f, Ig = 0.f, Ib = 0.f;
+        if (sc.flags & GAMER_FRAME_CONTINUE) { Ir = dst[0]; Ig = dst[1]; Ib = dst[2]; }   // unscaled I of the farther galaxies
         // ---- Rasterizer::renderPixel (rasterizer.cpp:379-416) --------------------------------
         for (int gi = 0; gi < sc.n_galaxies; gi++) {
             const DGalaxy &g = sc.gal[gi];
@@ -328,10 +330,12 @@ k1_march(const __grid_constant__ DScene sc, float *__restrict__ out, unsigned lo
             march<COUNT>(sc, g, isp1, isp2, o, nz, Ir, Ig, Ib, cn);
         }
         // rp.I * 0.01 / rayStep  (rasterizer.cpp:409): QVector3D*float then QVector3D/float
-        float *dst = out + 3 * ((size_t)ly * sc.width + lx);
-        dst[0] = __fdiv_rn(__fmul_rn(Ir, sc.final_mul), sc.ray_step_f);
-        dst[1] = __fdiv_rn(__fmul_rn(Ig, sc.final_mul), sc.ray_step_f);
-        dst[2] = __fdiv_rn(__fmul_rn(Ib, sc.final_mul), sc.ray_step_f);
+        if (sc.flags & GAMER_FRAME_PARTIAL) { dst[0] = Ir; dst[1] = Ig; dst[2] = Ib; }
+        else {
+            dst[0] = __fdiv_rn(__fmul_rn(Ir, sc.final_mul), sc.ray_step_f);
+            dst[1] = __fdiv_rn(__fmul_rn(Ig, sc.final_mul), sc.ray_step_f);
+            dst[2] = __fdiv_rn(__fmul_rn(Ib, sc.final_mul), sc.ray_step_f);
+        }
     }
     if (COUNT) {
         unsigned long long v[5] = {cn.rays, cn.samples, cn.gates, cn.evals, cn.octaves};

@@ -49,6 +49,7 @@ int gk_build_scene(const GamerFrame *f, const GamerGalaxy *gal, const GamerCompo
     if (f->n_galaxies < 0 || f->n_galaxies > DEV_MAX_GALAXIES) return fail("n_galaxies out of range (max 8 per frame)");
     if (f->n_components < 0) return fail("n_components negative");
     if ((f->n_galaxies && !gal) || (f->n_components && !comp)) return fail("null galaxy/component array");
+    if (f->flags & ~(GAMER_FRAME_CONTINUE | GAMER_FRAME_PARTIAL)) return fail("unknown frame flags");
     if (f->band_rows < 0 || (f->band_rows > 0 && f->band_stride < f->band_rows)) return fail("bad band_rows/band_stride");
     if (!(f->ray_step > 0.0) || !(f->min_ray_step > 0.0) || f->min_ray_step > 0.01) return fail("ray_step/min_ray_step out of range");
 
@@ -57,6 +58,7 @@ int gk_build_scene(const GamerFrame *f, const GamerGalaxy *gal, const GamerCompo
     s.width = f->width; s.height = f->height; s.full_size = f->full_size;
     s.x0 = f->x0; s.y0 = f->y0; s.band_rows = f->band_rows; s.band_stride = f->band_stride;
     s.n_galaxies = f->n_galaxies;
+    s.flags = f->flags;
     for (int i = 0; i < 16; i++) s.inv_vp[i] = f->inv_vp[i];
     for (int i = 0; i < 3; i++) s.cam[i] = f->cam[i];
     s.ray_step = f->ray_step;

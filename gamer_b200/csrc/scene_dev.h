@@ -76,6 +76,8 @@ struct DGalaxy {
 struct DScene {
     int32_t width, height, full_size, x0, y0, band_rows, band_stride;
     int32_t n_galaxies;
+    int32_t flags;           // GAMER_FRAME_*
+    int32_t _padf;
     float   inv_vp[16];
     float   cam[3];
     float   ray_step_f;      // float(rayStep)

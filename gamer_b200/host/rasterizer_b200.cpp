@@ -123,15 +123,43 @@ Scene RasterizerB200::Prepare() const {
 
 int RasterizerB200::RenderPixels() {
     Scene sc = Prepare();
-    static const GamerGalaxy no_gal{};
-    static const GamerComponent no_comp{};
-    int rc = gamer_b200_upload(m_ctx, &sc.frame, sc.galaxies.empty() ? &no_gal : sc.galaxies.data(),
-                               sc.components.empty() ? &no_comp : sc.components.data());
-    if (rc != GAMER_OK) return rc;
     m_width = sc.frame.width;
     m_height = sc.frame.height;
     m_renderBuffer.assign(size_t(m_width) * m_height * 3, 0.0f);
-    rc = gamer_b200_render(m_ctx, m_renderBuffer.data());
+    // Far -> near passes of at most GAMER_MAX_GALAXIES galaxies / GAMER_MAX_COMPONENTS active components;
+    // the unscaled accumulation stays in the device framebuffer between passes (gamer_b200.h).
+    static const GamerGalaxy no_gal{};
+    static const GamerComponent no_comp{};
+    const size_t ng = sc.galaxies.size();
+    size_t first = 0;
+    int rc = GAMER_OK;
+    do {
+        size_t last = first, active = 0;
+        while (last < ng && last - first < GAMER_MAX_GALAXIES) {
+            size_t a = 0;
+            const GamerGalaxy& g = sc.galaxies[last];
+            for (int k = g.comp_begin; k < g.comp_begin + g.comp_count; ++k) a += sc.components[size_t(k)].active == 1.0;
+            if (last > first && active + a > GAMER_MAX_COMPONENTS) break;
+            active += a;
+            ++last;
+        }
+        std::vector<GamerGalaxy> gals(sc.galaxies.begin() + long(first), sc.galaxies.begin() + long(last));
+        std::vector<GamerComponent> comps;
+        for (GamerGalaxy& g : gals) {
+            const int begin = int(comps.size());
+            comps.insert(comps.end(), sc.components.begin() + g.comp_begin, sc.components.begin() + g.comp_begin + g.comp_count);
+            g.comp_begin = begin;
+        }
+        GamerFrame f = sc.frame;
+        f.n_galaxies = int32_t(gals.size());
+        f.n_components = int32_t(comps.size());
+        f.flags = (first > 0 ? GAMER_FRAME_CONTINUE : 0) | (last < ng ? GAMER_FRAME_PARTIAL : 0);
+        rc = gamer_b200_upload(m_ctx, &f, gals.empty() ? &no_gal : gals.data(), comps.empty() ? &no_comp : comps.data());
+        if (rc != GAMER_OK) return rc;
+        rc = last < ng ? gamer_b200_render_device(m_ctx) : gamer_b200_render(m_ctx, m_renderBuffer.data());
+        if (rc != GAMER_OK) break;
+        first = last;
+    } while (first < ng);
     if (rc == GAMER_E_ABORTED) std::fill(m_renderBuffer.begin(), m_renderBuffer.end(), 0.0f);
     return rc;
 }

@@ -166,3 +166,40 @@ def build_scene(rp: RenderingParams, instances: List[GalaxyInstance], preview: b
     ga = (_lib.GamerGalaxy * max(1, len(gals)))(*gals)
     ca = (_lib.GamerComponent * max(1, len(comps)))(*comps)
     return Scene(f, ga, ca)
+
+
+def split_passes(scene: Scene) -> List[Scene]:
+    """Scenes beyond the per-pass limits of the kernel (8 galaxies / 64 active components) as a list of
+    far -> near chunks with GAMER_FRAME_CONTINUE / GAMER_FRAME_PARTIAL set, to be rendered in order into the
+    same context (Context.render_passes). One chunk (no flags) when the scene fits."""
+    f = scene.frame
+    chunks, cur, cur_active = [], [], 0
+    for gi in range(f.n_galaxies):
+        g = scene.galaxies[gi]
+        active = sum(1 for k in range(g.comp_begin, g.comp_begin + g.comp_count) if scene.components[k].active == 1.0)
+        if active > _lib.MAX_COMPONENTS:
+            raise ValueError(f"galaxy {gi} has {active} active components (limit {_lib.MAX_COMPONENTS})")
+        if cur and (len(cur) == _lib.MAX_GALAXIES or cur_active + active > _lib.MAX_COMPONENTS):
+            chunks.append(cur)
+            cur, cur_active = [], 0
+        cur.append(gi)
+        cur_active += active
+    if cur or not chunks:
+        chunks.append(cur)
+    if len(chunks) == 1:
+        return [scene]
+    out = []
+    for ci, idxs in enumerate(chunks):
+        comps, gals = [], []
+        for gi in idxs:
+            g = _lib.GamerGalaxy.from_buffer_copy(scene.galaxies[gi])
+            begin = len(comps)
+            for k in range(g.comp_begin, g.comp_begin + g.comp_count):
+                comps.append(_lib.GamerComponent.from_buffer_copy(scene.components[k]))
+            g.comp_begin = begin
+            gals.append(g)
+        fr = _lib.GamerFrame.from_buffer_copy(f)
+        fr.n_galaxies, fr.n_components = len(gals), len(comps)
+        fr.flags = (_lib.FRAME_CONTINUE if ci > 0 else 0) | (_lib.FRAME_PARTIAL if ci < len(chunks) - 1 else 0)
+        out.append(Scene(fr, (_lib.GamerGalaxy * max(1, len(gals)))(*gals), (_lib.GamerComponent * max(1, len(comps)))(*comps)))
+    return out

@@ -14,7 +14,7 @@ import numpy as np
 
 from . import _lib
 from .gax import Galaxy
-from .model import GalaxyInstance, RenderingParams, Scene, build_scene
+from .model import GalaxyInstance, RenderingParams, Scene, build_scene, split_passes
 
 
 class Context:
@@ -50,6 +50,25 @@ class Context:
         assert out.dtype == np.float32 and out.size == h * w * 3 and out.flags.c_contiguous
         _lib.check(self.h, self.lib.gamer_b200_render(self.h, out.ctypes.data))
         return out
+
+    def render_passes(self, scene: Scene, out: Optional[np.ndarray] = None, counted=False):
+        """Render a scene of any number of galaxies: far -> near chunks accumulate in the device framebuffer
+        (GAMER_FRAME_CONTINUE / _PARTIAL), the last pass applies the final scale and copies the frame out."""
+        passes = split_passes(scene)
+        total = {}
+        for p in passes[:-1]:
+            self.upload(p)
+            if counted:
+                for k, v in self.render_counted().items():
+                    total[k] = total.get(k, 0) + v
+            else:
+                self.render_device()
+        self.upload(passes[-1])
+        if counted:
+            for k, v in self.render_counted().items():
+                total[k] = total.get(k, 0) + v
+            return total
+        return self.render(out)
 
     def render_ptr(self, host_ptr: int):
         _lib.check(self.h, self.lib.gamer_b200_render(self.h, host_ptr))
@@ -221,9 +240,8 @@ class Rasterizer:
 
     def RenderPixels(self):
         scene = self.Prepare()
-        self._ctx.upload(scene)
         try:
-            self.m_renderBuffer = self._ctx.render()
+            self.m_renderBuffer = self._ctx.render_passes(scene)
         except _lib.GamerError as e:
             if e.code != _lib.E_ABORTED:
                 raise

@@ -84,6 +84,13 @@ typedef struct GamerGalaxy {
     int32_t comp_count;
 } GamerGalaxy;
 
+/* Scenes with more than GAMER_MAX_GALAXIES galaxies (or GAMER_MAX_COMPONENTS components) are rendered in
+ * several passes over far -> near chunks of the sorted galaxy list: the reference accumulates rp.I across
+ * galaxies in one float triple per pixel (rasterizer.cpp:383-409); the passes keep that triple in the device
+ * framebuffer between them, unscaled, so the result is bit-identical to a single pass. */
+#define GAMER_FRAME_CONTINUE 1   /* start every pixel from the unscaled I the previous pass left          */
+#define GAMER_FRAME_PARTIAL  2   /* leave the unscaled I (skip the final * 0.01 / rayStep): more to come  */
+
 /* One frame: camera + size + step (RenderingParams, GamerCamera). Galaxies must already be sorted
  * far -> near as Rasterizer::Prepare does (rasterizer.cpp:190-201). */
 typedef struct GamerFrame {
@@ -92,7 +99,7 @@ typedef struct GamerFrame {
     int32_t x0, y0;             /* tile origin inside the full_size x full_size image                 */
     int32_t band_rows;          /* 0: rows y0..y0+height-1. >0: interleaved bands — local row L is image */
     int32_t band_stride;        /* row y0 + (L / band_rows) * band_stride + (L % band_rows)            */
-    int32_t _pad0;
+    int32_t flags;              /* GAMER_FRAME_*: multi-pass rendering of scenes beyond the per-pass limits */
     float   inv_vp[16];         /* inverse(projection*view), element [row*4+col] = QMatrix4x4(row,col)*/
     float   cam[3];             /* GamerCamera::camera                                                */
     float   _pad1;

@@ -137,3 +137,16 @@ def random_galaxy_scene(index, size=1024, seed=20261104):
     v = 0.9 * v / np.linalg.norm(v)
     up = (0, 1, 0) if abs(v[1]) < 0.85 else (1, 0, 0)
     return single_galaxy_scene(g, size, ((float(v[0]), float(v[1]), float(v[2])), (0, 0, 0), up, 60.0))
+
+
+def many_galaxy_scene(size, n=11, view="outside", ray_step=RAY_STEP):
+    """More galaxies than one kernel pass holds (8): a ring of fixtures with varied orientations, so the
+    host has to split the sorted list into far -> near passes."""
+    rp = rendering_params(size, view, ray_step)
+    gis = []
+    for i in range(n):
+        a = 2.0 * math.pi * i / n
+        pos = (1.1 * math.cos(a), 0.35 * math.sin(3 * a), 1.1 * math.sin(a))
+        ori = (math.sin(a + 0.3), 0.4 + 0.6 * math.cos(2 * a) ** 2, math.cos(1.7 * a))
+        gis.append(GalaxyInstance(load_galaxy(FIXTURES[i % len(FIXTURES)]), f"g{i}", pos, ori, 0.6 + 0.1 * (i % 5), 0.0))
+    return build_scene(rp, gis)

@@ -183,3 +183,18 @@ def test_oracle_star_stamp(oracle):
     assert layer[12, 14, 0] == np.float32(0.5) * g        # star 0 stops at x < 4: only star 1 reaches column 14
     assert layer[12 + 4].sum() == 0 and layer[:, 20:].sum() == 0
     assert oracle.stamp_stars(16, (GamerStar * 0)()).sum() == 0
+
+
+def test_fits_export_roundtrip(tmp_path):
+    """FitsIO::Savedouble's content (one BITPIX -64 plane per channel, rows bottom-up) as valid FITS."""
+    from gamer_b200 import fits
+    rgb = np.random.default_rng(3).uniform(0, 40, (37, 37, 3)).astype(np.float32)
+    names = fits.save_rgb(str(tmp_path / "img"), rgb)
+    assert [os.path.basename(n) for n in names] == ["img_red.fits", "img_green.fits", "img_blue.fits"]
+    for no, n in enumerate(names):
+        raw = open(n, "rb").read()
+        assert len(raw) % 2880 == 0 and raw[:30] == b"SIMPLE  =                    T"
+        assert np.array_equal(fits.read_plane(n), rgb[:, :, no].astype(np.float64))
+        # first stored value is the bottom-left pixel, big-endian double
+        first = np.frombuffer(raw, dtype=">f8", count=1, offset=2880)[0]
+        assert first == np.float64(rgb[-1, 0, no])

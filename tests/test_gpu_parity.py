@@ -220,6 +220,54 @@ def test_tonemap_ragged_sizes(gpu_ctx, oracle):
         assert np.array_equal(a_g, a_c) and np.array_equal(s_g, s_c), size
 
 
+def test_more_galaxies_than_one_pass(gpu_ctx, oracle):
+    """11 galaxies / 70 active components: rendered in far -> near passes that keep the unscaled accumulation in
+    the device framebuffer; must equal the oracle's single pass (exact sample counts, pixels within tolerance)
+    and be independent of where the list is cut."""
+    from gamer_b200.model import split_passes
+    sc = scenes.many_galaxy_scene(72, n=11)
+    passes = split_passes(sc)
+    assert len(passes) >= 2 and sum(p.frame.n_galaxies for p in passes) == 11
+    assert all(p.frame.n_galaxies <= 8 for p in passes)
+    cnt_g = gpu_ctx.render_passes(sc, counted=True)
+    img_g = gpu_ctx.render_passes(sc)
+    img_c, cnt_c = oracle.render(sc)
+    for k in ("rays", "samples", "gates"):
+        assert cnt_g[k] == cnt_c[k], k
+    assert_pixels_close(img_g, img_c, "11 galaxies")
+    # a scene that fits one pass gives the same bits whether or not it is cut: 3 galaxies, cut after the first
+    three = scenes.multi_galaxy_scene(64)
+    gpu_ctx.upload(three)
+    whole = gpu_ctx.render()
+    import gamer_b200._lib as L
+    import gamer_b200.model as M
+    old = L.MAX_GALAXIES
+    try:
+        L.MAX_GALAXIES = 1
+        parts = M.split_passes(three)
+    finally:
+        L.MAX_GALAXIES = old
+    assert len(parts) == 3
+    for p in parts[:-1]:
+        gpu_ctx.upload(p)
+        gpu_ctx.render_device()
+    gpu_ctx.upload(parts[-1])
+    assert np.array_equal(gpu_ctx.render(), whole)
+
+
+def test_continue_pass_needs_a_partial_pass(gpu_ctx):
+    import gamer_b200._lib as L
+    from gamer_b200.model import Scene
+    sc = scenes.single_galaxy_scene("Spiral", 32, "oblique")
+    f = L.GamerFrame.from_buffer_copy(sc.frame)
+    f.flags = L.FRAME_CONTINUE
+    gpu_ctx.upload(sc)
+    gpu_ctx.render()
+    with pytest.raises(L.GamerError) as e:
+        gpu_ctx.upload(Scene(f, sc.galaxies, sc.components))
+    assert e.value.code == L.E_STATE
+
+
 def test_c4_hd_crop_frames(gpu_ctx, oracle):
     """BASELINE config 4 (rotating camera, 16:9): a 16:9 frame is the centred crop of the square image, checked at
     small size for several orbit angles; sample counts exact, pixels equal the same rows of the square frame."""
