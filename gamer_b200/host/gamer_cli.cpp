@@ -14,6 +14,7 @@
 #include "gax.hpp"
 #include "png_write.hpp"
 #include "rasterizer_b200.hpp"
+#include "renderparams.hpp"
 
 using namespace gamer;
 
@@ -24,6 +25,7 @@ static void PrintUsage() {
                  "       [ method = omp/thread/b200 ] [ camera = 1 0 0  ] [ target = 0 0 0  ] [ up = 0 1 0 ] [ fov = 90 ]"
                  "  [ exposure = 1 ] [ gamma = 1 ] [ saturation = 1 ] [ ray step = 0.025 ] [ galaxy gax file ]"
                  " [ size = 256 ] [ filename = test{.png} ]\n"
+                 "   - skybox [ method = omp/thread/b200 ] [ Renderingparams ] [ galaxy file ] [ png size ]\n"
                  "   - gaxdump [ galaxy gax file ]\n"
                  "   - gaxcopy [ galaxy gax file ] [ out file ]\n";
 }
@@ -121,6 +123,78 @@ static int RenderSingleGalaxy(int n, char** param) {
     return 0;
 }
 
+// ConsoleRenderer::RenderSkybox (consolerenderer.cpp:103-172) + RenderQueue::RenderSkybox
+// (galaxy/renderqueue.cpp:129-173): six fov-90 views from the camera position of the RenderingParams file
+// along -z +z +y -y +x -x, saved as SkyboxZ-.png ... SkyboxX+.png (the reference's own file names).
+static int RenderSkybox(int n, char** param) {
+    if (n != 5) {
+        std::cout << n << "\nIncorrect usage/parameters for galaxy. Usage: \n";
+        PrintUsage();
+        return 1;
+    }
+    std::string method = param[1];
+    for (char& c : method) c = char(std::tolower((unsigned char)c));
+    if (method != "omp" && method != "thread" && method != "b200") {
+        std::cout << "ERROR! Cannot recognize " << param[1] << "\nMust be 'omp', 'thread' or 'b200'\n";
+        return 1;
+    }
+    RenderingParams rp;
+    try {
+        if (!LoadRenderingParams(param[2], rp)) {
+            std::cout << "ERROR! Cannot open " << param[2] << "\n";
+            return 1;
+        }
+    } catch (const std::exception& e) {
+        std::cout << "ERROR! " << param[2] << ": " << e.what() << "\n";
+        return 1;
+    }
+    rp.setSize(int(toFloat(param[4])));
+    Galaxy galaxy;
+    try {
+        if (!galaxy.Load(param[3])) {
+            std::cout << "ERROR! Cannot open " << param[3] << "\n";
+            return 1;
+        }
+    } catch (const std::exception& e) {
+        std::cout << "ERROR! " << param[3] << ": " << e.what() << "\n";
+        return 1;
+    }
+    const Vec3 planes[6] = {{0, 0, -1}, {0, 0, 1}, {0, 1, 0}, {0, -1, 0}, {1, 0, 0}, {-1, 0, 0}};
+    const Vec3 ups[6] = {{0, 1, 0}, {0, 1, 0}, {0, 0, -1}, {0, 0, 1}, {0, 1, 0}, {0, 1, 0}};
+    const char* names[6] = {"Z-", "Z+", "Y-", "Y+", "X-", "X+"};
+    try {
+        RasterizerB200 rasterizer(devices_from_env());
+        GalaxyInstance gi(&galaxy, galaxy.galaxyParams.name, Vec3{0, 0, 0}, Vec3{0, 1, 0}, 1, 0);
+        rasterizer.AddGalaxy(&gi);
+        const Vec3 cam = rp.camera().m_camera;
+        for (int i = 0; i < 6; ++i) {
+            RenderingParams face = rp;
+            face.camera().setCamera(cam);
+            face.camera().setTarget(Vec3{cam.x + planes[i].x, cam.y + planes[i].y, cam.z + planes[i].z});
+            face.camera().setUp(ups[i]);
+            face.camera().setPerspective(90);
+            rasterizer.setRenderingParams(&face);
+            rasterizer.RenderStars(uint64_t(i));          // PrepareBuffer renders the star layer (rasterizer.cpp:174)
+            rasterizer.Render();
+            while (rasterizer.getState() != RasterizerB200::done) std::this_thread::sleep_for(std::chrono::milliseconds(1));
+            if (rasterizer.lastStatus() != GAMER_OK || rasterizer.AssembleImage() != GAMER_OK) {
+                std::cout << "ERROR! render failed: " << rasterizer.lastError() << "\n";
+                return 2;
+            }
+            const std::string file = std::string("Skybox") + names[i] + ".png";
+            if (!save_png_argb32(file, rasterizer.getImageShadowBuffer().data(), rasterizer.width(), rasterizer.height())) {
+                std::cout << "ERROR! cannot write " << file << "\n";
+                return 1;
+            }
+            std::cout << "Image saved to file Skybox" << names[i] << ".png" << std::endl;
+        }
+    } catch (const std::exception& e) {
+        std::cout << "ERROR! " << e.what() << "\n";
+        return 2;
+    }
+    return 0;
+}
+
 static int GaxDump(const char* path) {
     Galaxy g;
     if (!g.Load(path)) {
@@ -149,6 +223,19 @@ int main(int argc, char** argv) {
     const std::string cmd = argv[1];
     try {
         if (cmd == "galaxy") return RenderSingleGalaxy(argc - 1, argv + 1);
+        if (cmd == "skybox") return RenderSkybox(argc - 1, argv + 1);
+        if (cmd == "rpdump" && argc == 3) {
+            RenderingParams rp;
+            if (!LoadRenderingParams(argv[2], rp)) return 1;
+            std::printf("camera=%.9g %.9g %.9g target=%.9g %.9g %.9g up=%.9g %.9g %.9g fov=%.9g\n", rp.m_camera.m_camera.x,
+                        rp.m_camera.m_camera.y, rp.m_camera.m_camera.z, rp.m_camera.m_target.x, rp.m_camera.m_target.y,
+                        rp.m_camera.m_target.z, rp.m_camera.m_up.x, rp.m_camera.m_up.y, rp.m_camera.m_up.z, rp.m_camera.m_perspective);
+            std::printf("size=%d preview=%d exposure=%.9g gamma=%.9g saturation=%.9g noStars=%d starSize=%.17g spread=%.17g "
+                        "strength=%.17g rayStep=%.9g spectra=%zu galaxy=%s\n", rp.m_size, rp.m_previewSize, rp.m_exposure, rp.m_gamma,
+                        rp.m_saturation, rp.m_noStars, rp.m_starSize, rp.m_starSizeSpread, rp.m_starStrength, rp.m_rayStep,
+                        rp.m_spectra.m_spectra.size(), rp.m_currentGalaxy.c_str());
+            return 0;
+        }
         if (cmd == "gaxdump" && argc == 3) return GaxDump(argv[2]);
         if (cmd == "pngtest" && argc == 5) {  // deterministic pattern through the PNG encoder (CPU test of the writer)
             const int w = std::atoi(argv[3]), h = std::atoi(argv[4]);

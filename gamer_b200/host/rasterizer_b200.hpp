@@ -51,6 +51,11 @@ public:
     float m_exposure = 1, m_gamma = 1, m_saturation = 1, m_rayStep = 0.001f;
     int m_noStars = 0;
     double m_starSize = 1, m_starSizeSpread = 1, m_starStrength = 1;   // renderingparams.h:28-30
+    // carried for file round trips only (renderingparams.h:20-37)
+    int m_previewSize = 64, m_nside = 32;
+    double m_detailLevel = 0.01, m_noiseDetail = 1;
+    std::string m_renderType, m_galaxyDirectory = "galaxies/", m_sceneDirectory = "scenes/", m_imageDirectory = "images/",
+        m_currentGalaxy, m_sceneMode = "galaxy";
     GamerCamera m_camera;
     Spectra m_spectra;
     GamerCamera& camera() { return m_camera; }

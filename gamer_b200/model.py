@@ -70,6 +70,16 @@ class RenderingParams:
     m_starSize: float = 1.0            # renderingparams.h:29-30
     m_starSizeSpread: float = 1.0
     m_starStrength: float = 1.0
+    m_previewSize: int = 64            # the rest of renderingparams.h:19-39 (file round trips; not used by the path)
+    m_detailLevel: float = 0.01
+    m_noiseDetail: float = 1.0
+    m_nside: int = 32
+    m_renderType: str = ""
+    m_galaxyDirectory: str = "galaxies/"
+    m_sceneDirectory: str = "scenes/"
+    m_imageDirectory: str = "images/"
+    m_currentGalaxy: str = ""
+    m_sceneMode: str = "galaxy"
     m_camera: GamerCamera = field(default_factory=GamerCamera)
     m_spectra: Spectra = field(default_factory=Spectra)
 

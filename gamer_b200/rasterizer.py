@@ -311,3 +311,29 @@ class Rasterizer:
 
     def getImageShadowBuffer(self):
         return self.m_imageShadowBuffer
+
+
+SKYBOX_FACES = [("Z-", (0, 0, -1), (0, 1, 0)), ("Z+", (0, 0, 1), (0, 1, 0)), ("Y-", (0, 1, 0), (0, 0, -1)),
+                ("Y+", (0, -1, 0), (0, 0, 1)), ("X-", (1, 0, 0), (0, 1, 0)), ("X+", (-1, 0, 0), (0, 1, 0))]
+
+
+def RenderSkybox(rasterizer: "Rasterizer", rp: RenderingParams):
+    """RenderQueue::RenderSkybox (galaxy/renderqueue.cpp:129-173) driven like ConsoleRenderer::RenderSkybox
+    (consolerenderer.cpp:103-172): six fov-90 views from rp's camera position; returns {"SkyboxZ-": image, ...}
+    with the ARGB32 shadow image the reference saves as <name>.png. The star layer (PrepareBuffer renders one,
+    rasterizer.cpp:174) uses face index as seed."""
+    import copy
+    out = {}
+    cam = tuple(rp.camera().m_camera)
+    for i, (name, plane, up) in enumerate(SKYBOX_FACES):
+        face = copy.deepcopy(rp)
+        c = face.camera()
+        c.m_camera, c.m_target, c.m_up, c.m_perspective = cam, tuple(a + b for a, b in zip(cam, plane)), up, 90.0
+        rasterizer.setRenderingParams(face)
+        rasterizer.RenderStars(seed=i)
+        rasterizer.Render()
+        while rasterizer.getState() != Rasterizer.State.done:
+            pass
+        rasterizer.AssembleImage()
+        out["Skybox" + name] = rasterizer.getImageShadowBuffer()
+    return out

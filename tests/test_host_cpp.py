@@ -99,6 +99,55 @@ def test_cli_usage_errors(tmp_path):
     assert p.returncode == 1 and "Cannot open" in p.stdout
 
 
+def test_rendering_params_file_cpp_equals_python():
+    """RenderParams.dat (the reference's shipped file, older layout without nside/renderType)."""
+    from gamer_b200 import renderparams
+    path = os.path.join(ROOT, "tests", "golden", "RenderParams.dat")
+    p = _run("rpdump", path)
+    assert p.returncode == 0
+    rp = renderparams.Load(path)
+    l1, l2 = p.stdout.splitlines()
+    cam = [float(v) for v in l1.split("target=")[0].replace("camera=", "").split()]
+    assert np.allclose(cam, rp.camera().m_camera, rtol=1e-7)
+    kv = dict(t.split("=") for t in l2.split())
+    assert int(kv["size"]) == rp.m_size == 384 and int(kv["noStars"]) == rp.m_noStars == 25000
+    assert float(kv["starSize"]) == rp.m_starSize and float(kv["spread"]) == rp.m_starSizeSpread == 1.5
+    assert int(kv["spectra"]) == len(rp.m_spectra.m_spectra) == 7 and kv["galaxy"] == rp.m_currentGalaxy == "Spiral"
+    assert np.isclose(float(kv["gamma"]), rp.m_gamma) and np.isclose(float(kv["rayStep"]), rp.m_rayStep)
+    # SURVEY.md Appendix A's decoding of the same file
+    assert np.allclose(rp.camera().m_up, (-0.527, 0.342, -0.778), atol=1e-3) and rp.camera().m_perspective == 90
+    assert np.allclose((rp.m_exposure, rp.m_gamma, rp.m_saturation, rp.m_rayStep), (0.767, 0.867, 1.467, 0.02), atol=1e-3)
+    assert rp.m_spectra.FindSpectrum("green") == (np.float32(0.7), 1.0, np.float32(0.7))
+    # write -> read is the identity; the writer always emits the current layout (with nside/renderType)
+    b = renderparams.to_bytes(rp)
+    assert renderparams.to_bytes(renderparams.from_bytes(b)) == b and len(b) == 520 + 4 + 4
+
+
+@pytest.mark.gpu
+def test_cli_skybox_equals_python_pipeline(tmp_path):
+    """`skybox omp RenderParams.dat Spiral.gax 48`: six PNGs, each equal to the ctypes pipeline's face."""
+    from gamer_b200 import renderparams
+    from gamer_b200.model import GalaxyInstance
+    from gamer_b200.rasterizer import Rasterizer, RenderSkybox
+    rpfile = os.path.join(ROOT, "tests", "golden", "RenderParams.dat")
+    p = subprocess.run([CLI, "skybox", "omp", rpfile, os.path.join(GAX, "Spiral.gax"), "48"], capture_output=True, text=True,
+                       timeout=300, cwd=tmp_path)
+    assert p.returncode == 0, p.stdout + p.stderr
+    rp = renderparams.Load(rpfile)
+    rp.m_size = 48
+    r = Rasterizer()
+    r.AddGalaxy(GalaxyInstance(Galaxy.Load(os.path.join(GAX, "Spiral.gax"))))
+    faces = RenderSkybox(r, rp)
+    assert sorted(faces) == ["SkyboxX+", "SkyboxX-", "SkyboxY+", "SkyboxY-", "SkyboxZ+", "SkyboxZ-"]
+    lit = 0
+    for name, sh in faces.items():
+        png = _read_png_rgba(str(tmp_path / (name + ".png")))
+        want = np.stack([(sh >> 16) & 255, (sh >> 8) & 255, sh & 255, sh >> 24], axis=-1).astype(np.uint8)
+        assert np.array_equal(png, want), name
+        lit += int(want[..., :3].max() > 20)
+    assert lit >= 2          # the camera sits off-centre: some faces look away from the galaxy
+
+
 @pytest.mark.gpu
 @pytest.mark.parametrize("name,size,gamma", [("Spiral", 128, 1.0), ("Sombrero", 96, 0.8)])
 def test_cli_image_equals_python_pipeline(name, size, gamma, tmp_path):
