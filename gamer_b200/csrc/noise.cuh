@@ -47,23 +47,29 @@ __constant__ uint8_t c_perm[256] = {
 
 // Gradient code of g = perm % 12 for grad3 (simplexnoise.h:142-146): dot(grad3[g], (x,y,z)) = ±a ± b with
 //   g<4: (a,b)=(x,y)   4<=g<8: (x,z)   g>=8: (y,z);  sign(a) = g&1, sign(b) = (g>>1)&1.
-// Bit 31 = sign of a, bit 30 = sign of b, bit 1 = "a is y", bit 2 = "b is y"; bits 3..6 = g itself.
+// ±a ± b = sa (a + (sa sb) b): bit 31 = sign(a) XOR sign(b) (flips b with one LOP3), bit 3 = sign(a) (applied to the
+// sum through a predicate), bit 1 = "a is y", bit 2 = "b is y"; bits 16..19 = g itself (probe only).
 __host__ __device__ inline uint32_t grad_code(uint32_t g) {
-    uint32_t code = (g << 3);
-    if (g & 1) code |= 0x80000000u;
-    if (g & 2) code |= 0x40000000u;
+    uint32_t code = (g << 16);
+    const uint32_t sa = g & 1u, sb = (g >> 1) & 1u;
+    if (sa ^ sb) code |= 0x80000000u;
+    if (sa) code |= 8u;
     if (g >= 8) code |= 2u;
     if (g < 4) code |= 4u;
     return code;
 }
 
-#define GN_TABLE_WORDS (256 * 32)
+// 257 entries (entry 256 repeats entry 0, like perm[256] of the reference's doubled table): the "+1" of a
+// corner offset is then a +128-byte displacement AFTER the index has been wrapped, i.e. an immediate of the
+// load instead of index arithmetic.
+#define GN_TABLE_ENTRIES 257
+#define GN_TABLE_WORDS (GN_TABLE_ENTRIES * 32)
 #define GN_ADDR_MASK 0x7F80u
 // The replicated table must sit at a 32 KB-aligned address of the CTA's shared window so that a lookup
 // address is ONE LOP3: (off & 0x7F80) | (0x8000 | lane*4), followed by one LDS. Static shared memory
 // starts at window offset 0x400 (the first KB is reserved), so kernels that use the noise code take
 // GN_DYN_SMEM bytes of dynamic shared memory (and no static shared memory): the table occupies window
-// addresses 0x8000..0xFFFF. table_init() verifies the base and traps if the layout ever differs.
+// addresses 0x8000..0x1007F. table_init() verifies the base and traps if the layout ever differs.
 #define GN_TABLE_ADDR 0x8000u
 #define GN_DYN_BASE 0x400u
 #define GN_DYN_SMEM (GN_TABLE_ADDR - GN_DYN_BASE + GN_TABLE_WORDS * 4u)
@@ -75,7 +81,7 @@ __device__ __forceinline__ void table_init() {
     if ((uint32_t)__cvta_generic_to_shared(gn_dyn_smem) != GN_DYN_BASE) __trap();
     uint32_t *tbl = reinterpret_cast<uint32_t *>(gn_dyn_smem + (GN_TABLE_ADDR - GN_DYN_BASE));
     for (uint32_t w = threadIdx.x + threadIdx.y * blockDim.x; w < GN_TABLE_WORDS; w += blockDim.x * blockDim.y) {
-        uint32_t e = w >> 5;
+        uint32_t e = (w >> 5) & 255u;
         uint32_t p = c_perm[e];
         tbl[w] = (p << 7) | grad_code(p % 12u);
     }
@@ -83,20 +89,19 @@ __device__ __forceinline__ void table_init() {
 // per-lane constant of the lookup address
 __device__ __forceinline__ uint32_t lane_const() { return GN_TABLE_ADDR | ((threadIdx.x & 31u) << 2); }
 
-// one level of the hash walk: entry ((off7 >> 7) & 255) of this lane's bank
-__device__ __forceinline__ uint32_t look(uint32_t lane4, uint32_t off7) {
-    uint32_t v, a = (off7 & GN_ADDR_MASK) | lane4;
-    asm("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a));
-    return v;
-}
+// one level of the hash walk: shared-window address of entry ((off7 >> 7) & 255) of this lane's bank ...
+__device__ __forceinline__ uint32_t addr_of(uint32_t lane4, uint32_t off7) { return (off7 & GN_ADDR_MASK) | lane4; }
+// ... and the entry at that address, or the one after it
+__device__ __forceinline__ uint32_t ld0(uint32_t a) { uint32_t v; asm("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a)); return v; }
+__device__ __forceinline__ uint32_t ld1(uint32_t a) { uint32_t v; asm("ld.shared.u32 %0, [%1+128];" : "=r"(v) : "r"(a)); return v; }
 
 // ±a ± b from a table entry
 __device__ __forceinline__ float grad_dot(uint32_t e, float x, float y, float z) {
     float a = (e & 2u) ? y : x;
     float b = (e & 4u) ? y : z;
-    a = __uint_as_float(__float_as_uint(a) ^ (e & 0x80000000u));
-    b = __uint_as_float(__float_as_uint(b) ^ ((e << 1) & 0x80000000u));
-    return a + b;
+    b = __uint_as_float(__float_as_uint(b) ^ (e & 0x80000000u));
+    const float w = a + b;
+    return (e & 8u) ? -w : w;
 }
 
 struct Lattice {   // filled only by the probe path
@@ -153,17 +158,22 @@ __device__ __forceinline__ float simplex_cell(uint32_t lane4, int ci, int cj, in
     float x2 = x0 + (i2 ? G6m : G6), y2 = y0 + (j2 ? G6m : G6), z2 = z0 + (k2 ? G6m : G6);
     float x3 = x0 - 0.5f, y3 = y0 - 0.5f, z3 = z0 - 0.5f;
 
-    // hash walk: perm[ii+oi+perm[jj+oj+perm[kk+ok]]], offsets pre-scaled by 128
-    uint32_t K7 = (uint32_t)ck << 7, J7 = (uint32_t)cj << 7, I7 = (uint32_t)ci << 7;
-    uint32_t A0 = look(lane4, K7), A1 = look(lane4, K7 + 128u);
-    uint32_t B0 = look(lane4, A0 + J7);
-    uint32_t B1 = look(lane4, (k1 ? A1 : A0) + J7 + (j1 ? 128u : 0u));
-    uint32_t B2 = look(lane4, (k2 ? A1 : A0) + J7 + (j2 ? 128u : 0u));
-    uint32_t B3 = look(lane4, A1 + J7 + 128u);
-    uint32_t C0 = look(lane4, B0 + I7);
-    uint32_t C1 = look(lane4, B1 + I7 + (i1 ? 128u : 0u));
-    uint32_t C2 = look(lane4, B2 + I7 + (i2 ? 128u : 0u));
-    uint32_t C3 = look(lane4, B3 + I7 + 128u);
+    // hash walk: perm[ii+oi+perm[jj+oj+perm[kk+ok]]], offsets pre-scaled by 128. An address is the wrapped index
+    // of the corner WITHOUT its +1 offsets; the offsets pick the entry at the address or the one after it.
+    const uint32_t K7 = (uint32_t)ck << 7, J7 = (uint32_t)cj << 7, I7 = (uint32_t)ci << 7;
+    const uint32_t aK = addr_of(lane4, K7);
+    const uint32_t A0 = ld0(aK), A1 = ld1(aK);
+    const uint32_t aJ0 = addr_of(lane4, A0 + J7), aJ1 = addr_of(lane4, A1 + J7);
+    const uint32_t aB1 = k1 ? aJ1 : aJ0, aB2 = k2 ? aJ1 : aJ0;
+    const uint32_t B0 = ld0(aJ0);
+    const uint32_t B1 = j1 ? ld1(aB1) : ld0(aB1);
+    const uint32_t B2 = j2 ? ld1(aB2) : ld0(aB2);
+    const uint32_t B3 = ld1(aJ1);
+    const uint32_t aC1 = addr_of(lane4, B1 + I7), aC2 = addr_of(lane4, B2 + I7);
+    const uint32_t C0 = ld0(addr_of(lane4, B0 + I7));
+    const uint32_t C1 = i1 ? ld1(aC1) : ld0(aC1);
+    const uint32_t C2 = i2 ? ld1(aC2) : ld0(aC2);
+    const uint32_t C3 = ld1(addr_of(lane4, B3 + I7));
 
     float t0 = fmaxf(0.6f - x0 * x0 - y0 * y0 - z0 * z0, 0.0f);
     float t1 = fmaxf(0.6f - x1 * x1 - y1 * y1 - z1 * z1, 0.0f);
@@ -178,7 +188,7 @@ __device__ __forceinline__ float simplex_cell(uint32_t lane4, int ci, int cj, in
     if (PROBE) {
         lat->c1 = (int)i1 + 2 * (int)j1 + 4 * (int)k1;
         lat->c2 = (int)i2 + 2 * (int)j2 + 4 * (int)k2;
-        lat->g0 = (C0 >> 3) & 15; lat->g1 = (C1 >> 3) & 15; lat->g2 = (C2 >> 3) & 15; lat->g3 = (C3 >> 3) & 15;
+        lat->g0 = (C0 >> 16) & 15; lat->g1 = (C1 >> 16) & 15; lat->g2 = (C2 >> 16) & 15; lat->g3 = (C3 >> 16) & 15;
     }
     return 32.0f * n;
 }
