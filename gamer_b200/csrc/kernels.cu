@@ -472,10 +472,15 @@ kp_simplex(const float *__restrict__ xyz, int n, double frequency, int32_t *__re
                  __dmul_rn((double)xyz[3 * q + 2], frequency), su, sv, sw);
     gnoise::Lattice L;
     float fu, fv, fw;
-    gnoise::cell_of<true>(su, 0, L.i, fu);
-    gnoise::cell_of<true>(sv, 0, L.j, fv);
-    gnoise::cell_of<true>(sw, 0, L.k, fw);
-    float v = gnoise::simplex_cell<true>(lane4, L.i, L.j, L.k, fu, fv, fw, &L);
+    uint32_t i7, j7, k7;
+    gnoise::cell_of<true>(su, 0, i7, fu);
+    gnoise::cell_of<true>(sv, 0, j7, fv);
+    gnoise::cell_of<true>(sw, 0, k7, fw);
+    // full 32-bit cells for the parity test: the plain cell, minus one where the fastfloor quirk fired
+    L.i = su.hi - (int)((__funnelshift_l(su.lo, (uint32_t)su.hi, 7) - i7) >> 7);
+    L.j = sv.hi - (int)((__funnelshift_l(sv.lo, (uint32_t)sv.hi, 7) - j7) >> 7);
+    L.k = sw.hi - (int)((__funnelshift_l(sw.lo, (uint32_t)sw.hi, 7) - k7) >> 7);
+    float v = 32.0f * gnoise::simplex_cell<true>(lane4, i7, j7, k7, fu, fv, fw, &L);
     if (val_out) val_out[q] = v;
     if (lat_out) {
         int32_t *o = lat_out + 10 * (size_t)q;

@@ -47,15 +47,17 @@ __constant__ uint8_t c_perm[256] = {
 
 // Gradient code of g = perm % 12 for grad3 (simplexnoise.h:142-146): dot(grad3[g], (x,y,z)) = ±a ± b with
 //   g<4: (a,b)=(x,y)   4<=g<8: (x,z)   g>=8: (y,z);  sign(a) = g&1, sign(b) = (g>>1)&1.
-// ±a ± b = sa (a + (sa sb) b): bit 31 = sign(a) XOR sign(b) (flips b with one LOP3), bit 3 = sign(a) (applied to the
-// sum through a predicate), bit 1 = "a is y", bit 2 = "b is y"; bits 16..19 = g itself (probe only).
+// ±a ± b = sa (a + (sa sb) b): bit 31 = sign(a) XOR sign(b) (flips b with one LOP3), bit 19 = sign(a) (applied to the
+// sum through a predicate), bit 17 = "a is y", bit 18 = "b is y"; bits 20..23 = g itself (probe only). The low
+// 7 bits of an entry stay ZERO: an index operand may then carry 7 garbage bits below the <<7 position (the
+// fraction bits a funnel shift brings along) without a carry into the index.
 __host__ __device__ inline uint32_t grad_code(uint32_t g) {
-    uint32_t code = (g << 16);
+    uint32_t code = (g << 20);
     const uint32_t sa = g & 1u, sb = (g >> 1) & 1u;
     if (sa ^ sb) code |= 0x80000000u;
-    if (sa) code |= 8u;
-    if (g >= 8) code |= 2u;
-    if (g < 4) code |= 4u;
+    if (sa) code |= 0x80000u;
+    if (g >= 8) code |= 0x20000u;
+    if (g < 4) code |= 0x40000u;
     return code;
 }
 
@@ -97,11 +99,11 @@ __device__ __forceinline__ uint32_t ld1(uint32_t a) { uint32_t v; asm("ld.shared
 
 // ±a ± b from a table entry
 __device__ __forceinline__ float grad_dot(uint32_t e, float x, float y, float z) {
-    float a = (e & 2u) ? y : x;
-    float b = (e & 4u) ? y : z;
+    float a = (e & 0x20000u) ? y : x;
+    float b = (e & 0x40000u) ? y : z;
     b = __uint_as_float(__float_as_uint(b) ^ (e & 0x80000000u));
     const float w = a + b;
-    return (e & 8u) ? -w : w;
+    return (e & 0x80000u) ? -w : w;
 }
 
 struct Lattice {   // filled only by the probe path
@@ -127,14 +129,16 @@ __device__ __forceinline__ Skewed to_fixed(double u) {
 // BIASED BY +1 (simplex_cell removes the bias inside an FMA it needs anyway). CHECK: also handle the
 // reference's fastfloor quirk; callers hoist the (almost never true) need for it out of their loops.
 template <bool CHECK>
-__device__ __forceinline__ void cell_of(const Skewed &s, int k, int &cell, float &frac) {
+__device__ __forceinline__ void cell_of(const Skewed &s, int k, uint32_t &cell7, float &frac) {
     uint32_t lo = s.lo << k;
-    cell = (int)__funnelshift_l(s.lo, (uint32_t)s.hi, k);
+    // (cell << 7) | 7 fraction bits: the upper word of the 64-bit value shifted by k + 7. The 7 low bits are
+    // harmless (table entries have zeros there and the address mask drops them).
+    cell7 = __funnelshift_l(s.lo, (uint32_t)s.hi, k + 7);
     frac = __uint_as_float((lo >> 9) | 0x3F800000u);   // 1 + fraction (top 23 bits): no int->float conversion
     if (CHECK && lo == 0u) {   // rare: looks like an exact integer in fixed point
         double uk = s.d * (double)(1u << k);
         if (uk <= 0.0 && uk == rint(uk)) {   // simplexnoise.h:130 fastfloor: (int)x - 1 for exact x <= 0
-            cell -= 1;
+            cell7 -= 128u;
             frac = 2.0f;
         }
     }
@@ -142,7 +146,7 @@ __device__ __forceinline__ void cell_of(const Skewed &s, int k, int &cell, float
 
 // One raw simplex value from cells (ci,cj,ck) and fractions (fu,fv,fw).  Returns 32*(n0+n1+n2+n3).
 template <bool PROBE>
-__device__ __forceinline__ float simplex_cell(uint32_t lane4, int ci, int cj, int ck,
+__device__ __forceinline__ float simplex_cell(uint32_t lane4, uint32_t I7, uint32_t J7, uint32_t K7,
                                               float fu, float fv, float fw, Lattice *lat) {
     const float G3 = 1.0f / 6.0f;
     float t = fmaf(fu + fv + fw, G3, 0.5f);      // fu,fv,fw carry a +1 bias: (sum-3)/6 + 1
@@ -160,7 +164,6 @@ __device__ __forceinline__ float simplex_cell(uint32_t lane4, int ci, int cj, in
 
     // hash walk: perm[ii+oi+perm[jj+oj+perm[kk+ok]]], offsets pre-scaled by 128. An address is the wrapped index
     // of the corner WITHOUT its +1 offsets; the offsets pick the entry at the address or the one after it.
-    const uint32_t K7 = (uint32_t)ck << 7, J7 = (uint32_t)cj << 7, I7 = (uint32_t)ci << 7;
     const uint32_t aK = addr_of(lane4, K7);
     const uint32_t A0 = ld0(aK), A1 = ld1(aK);
     const uint32_t aJ0 = addr_of(lane4, A0 + J7), aJ1 = addr_of(lane4, A1 + J7);
@@ -188,9 +191,9 @@ __device__ __forceinline__ float simplex_cell(uint32_t lane4, int ci, int cj, in
     if (PROBE) {
         lat->c1 = (int)i1 + 2 * (int)j1 + 4 * (int)k1;
         lat->c2 = (int)i2 + 2 * (int)j2 + 4 * (int)k2;
-        lat->g0 = (C0 >> 16) & 15; lat->g1 = (C1 >> 16) & 15; lat->g2 = (C2 >> 16) & 15; lat->g3 = (C3 >> 16) & 15;
+        lat->g0 = (C0 >> 20) & 15; lat->g1 = (C1 >> 20) & 15; lat->g2 = (C2 >> 20) & 15; lat->g3 = (C3 >> 20) & 15;
     }
-    return 32.0f * n;
+    return n;        // 1/32 of the raw value: callers fold the factor into their own scale
 }
 
 // skewed coordinates of the point (x,y,z) (doubles), reference operation order (simplexnoise.cpp:247-251)
@@ -206,7 +209,7 @@ __device__ __forceinline__ void skew(double x, double y, double z, Skewed &su, S
 // (almost never needed) variant that checks for the reference's fastfloor behaviour at exact integers.
 template <bool QUIRK>
 __device__ __forceinline__ float octave(uint32_t lane4, const Skewed &su, const Skewed &sv, const Skewed &sw, int k) {
-    int ci, cj, ck;
+    uint32_t ci, cj, ck;
     float fu, fv, fw;
     cell_of<QUIRK>(su, k, ci, fu);
     cell_of<QUIRK>(sv, k, cj, fv);
@@ -253,7 +256,7 @@ __device__ __forceinline__ float fbm(uint32_t lane4, float px, float py, float p
     float total;
     if (maybe_integer(su, sv, sw, octaves - 1)) total = fbm_quirk(lane4, x, y, z, octaves, pers);
     else total = fbm_sum<false>(lane4, su, sv, sw, octaves, pers);
-    return total * inv_maxamp;
+    return total * (32.0f * inv_maxamp);
 }
 
 // Noise::getRidgedMf (noise.cpp:81-128). v is the float QVector3D (already r*scale); it is scaled by
@@ -268,7 +271,7 @@ __device__ __forceinline__ float ridged(uint32_t lane4, float vx, float vy, floa
         float signal;
         if (maybe_integer(su, sv, sw, 0)) signal = octave_quirk(lane4, vx, vy, vz);
         else signal = octave<false>(lane4, su, sv, sw, 0);
-        signal = offset - fabsf(signal);
+        signal = offset - fabsf(32.0f * signal);
         signal *= signal;
         signal *= weight;
         weight = fminf(fmaxf(signal * gain, 0.0f), 1.0f);
