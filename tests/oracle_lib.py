@@ -93,12 +93,27 @@ class Oracle:
         return np.array(out[:], dtype=np.float32)
 
 
-def build(target="all"):
-    subprocess.run(["make", "-C", ODIR, target], check=True, stdout=subprocess.DEVNULL)
+def build(target="all", force=False):
+    subprocess.run(["make", "-C", ODIR] + (["-B"] if force else []) + [target], check=True, stdout=subprocess.DEVNULL)
+
+
+_fast_built = False
 
 
 def load(fast=False):
-    path = FAST if fast else STRICT
-    if not os.path.exists(path):
-        build("native" if fast else "all")
-    return Oracle(path)
+    """strict: the parity oracle (-O2, IEEE). fast: the timed CPU baseline with the reference's flags
+    (-Ofast -march=native): always rebuilt once per process ON THE MACHINE THAT TIMES IT — a library that
+    travelled from another box has the wrong -march=native and possibly an older source."""
+    global _fast_built
+    if fast:
+        if not _fast_built:
+            build("native", force=True)
+            _fast_built = True
+        return Oracle(FAST)
+    if not os.path.exists(STRICT):
+        build("all")
+    try:
+        return Oracle(STRICT)
+    except AttributeError:          # stale build from an older source: rebuild once
+        build("all", force=True)
+        return Oracle(STRICT)
