@@ -6,8 +6,12 @@
 // PARITY UNPINNED: the reference ships no golden vectors, known-answer tests or baseline images
 // for this path (its two harnesses need Gamer.exe + PySide6/slangpy, absent here),
 // and the reference itself cannot be built here (every file on the path includes Qt headers; Qt is
-// not installed).  What pins this file: (1) its simplex core is checked bit-for-bit against the
-// reference's own source/noise/simplexnoise.cpp compiled in place into oracle/_ref (see Makefile);
+// not installed).  What pins this file: (1) its noise layer — raw simplex, fBm (octave_noise_3d) and
+// the ridged multifractal (getRidgedMf) — is checked bit-for-bit against the reference's own
+// source/noise/{simplexnoise,noise,simplex}.cpp compiled in place into oracle/_ref (see Makefile; the
+// two class files against the minimal Qt stand-ins of oracle/qtshim) and against the golden vectors
+// those libraries produced (tests/golden/simplex_ref.npz, noise_class_ref.npz); everything ABOVE the
+// noise layer (march, components, camera, post-process) remains unpinned;
 // (2) it follows the reference line by line, each function citing what it restates; (3) Qt's float
 // value-class arithmetic is restated in qt5_math.h (Qt 5.15 semantics).
 //

@@ -6,6 +6,9 @@
   galaxies.json    the same files decoded by gamer_b200.gax (human-readable)
   simplex_ref.npz  raw_noise_3d / octave_noise_3d values produced by the reference's OWN
                    source/noise/simplexnoise.cpp compiled in place (oracle/_ref, `make -C oracle ref`)
+  noise_class_ref.npz  Noise::octave_noise_3d and Noise::getRidgedMf of the reference's OWN noise.cpp / simplex.cpp
+                   (class Simplex(1,1,1,1), as Rasterizer constructs it), compiled in place against oracle/qtshim,
+                   with the argument patterns of galaxycomponents.cpp (disk/dust/stars fBm, dust2 ridged)
 """
 import ctypes as C
 import glob
@@ -48,7 +51,34 @@ def main():
     cases = [(10, 1.0, 1.0), (9, -0.8, 0.5), (10, 1.0, 15.0), (4, -2.0, 0.2), (10, -0.5, 0.5)]
     octv = np.array([[ref.ref_octave_noise_3d(o, p, s, *q) for q in pts[:300]] for (o, p, s) in cases])
     np.savez_compressed(os.path.join(HERE, "simplex_ref.npz"), pts=pts, raw=raw, oct_cases=np.array(cases), oct=octv)
-    print("wrote", len(out), "galaxies,", len(pts), "noise points")
+    # the class-level entry points the components call (galaxycomponent.h:93-98, galaxycomponents.cpp:45,68,92-94,141)
+    cls = C.CDLL(os.path.join(ROOT, "oracle", "_ref", "libgamer_ref_noise_class.so"))
+    p = C.c_void_p
+    cls.ref_class_octave_noise_3d.argtypes = [p, C.c_int, C.c_double, C.c_double, C.c_double, p]
+    cls.ref_class_ridged.argtypes = [p, C.c_int, C.c_double, C.c_int, C.c_double, C.c_double, C.c_double, p]
+    cls.ref_class_raw_3d.argtypes = [p, C.c_int, p]
+    pf = np.ascontiguousarray(np.concatenate([rng.uniform(-1.2, 1.2, (700, 3)), rng.uniform(-30, 30, (200, 3)),
+                                              np.array([[0, 0, 0], [0.5, 0.25, -0.125], [-1, 0, 2], [3, 3, 3]])]), dtype=np.float32)
+    n = len(pf)
+    fbm_cases = [(10, 1.0, float(np.float32(10) * np.float32(0.1))), (10, 1.0, float(np.float32(1) * np.float32(0.1))),
+                 (9, -0.8, float(np.float32(4) * np.float32(0.1))), (10, -0.5, float(np.float32(5) * np.float32(0.1))),
+                 (10, 1.0, float(np.float32(0.01) * np.float32(6) * 100)), (4, -2.0, 2.0 * float(np.float32(0.1)))]
+    fbm = np.empty((len(fbm_cases), n))
+    for k, (o, pe, sc) in enumerate(fbm_cases):
+        cls.ref_class_octave_noise_3d(pf.ctypes.data, n, o, pe, sc, fbm[k].ctypes.data)
+    # dust2: getRidgedMf(r * scale, ks, 9, 2.5, noiseOffset, noiseTilt); the point already carries the scale
+    rid_cases = [(1.0, 9, 2.5, 1.0, 1.5, 5.0), (1.0, 9, 2.5, 1.2, 1.5, 4.0), (1.0, 9, 2.5, 1.05, 1.5, 6.0), (-0.5, 9, 2.5, 1.1, 1.2, 8.0)]
+    rid = np.empty((len(rid_cases), n))
+    for k, (fr, o, lac, off, gain, scale) in enumerate(rid_cases):
+        q = np.ascontiguousarray(pf * np.float32(scale))
+        cls.ref_class_ridged(q.ctypes.data, n, fr, o, lac, off, gain, rid[k].ctypes.data)
+    raw2 = np.empty(len(pts))
+    pd = np.ascontiguousarray(pts)
+    cls.ref_class_raw_3d(pd.ctypes.data, len(pts), raw2.ctypes.data)
+    assert np.array_equal(raw2, raw)            # Simplex::raw_3d is raw_noise_3d
+    np.savez_compressed(os.path.join(HERE, "noise_class_ref.npz"), pts=pf, fbm_cases=np.array(fbm_cases), fbm=fbm,
+                        rid_cases=np.array(rid_cases), rid=rid)
+    print("wrote", len(out), "galaxies,", len(pts), "noise points,", n, "class-level noise points")
 
 
 if __name__ == "__main__":

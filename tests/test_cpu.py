@@ -198,3 +198,18 @@ def test_fits_export_roundtrip(tmp_path):
         # first stored value is the bottom-left pixel, big-endian double
         first = np.frombuffer(raw, dtype=">f8", count=1, offset=2880)[0]
         assert first == np.float64(rgb[-1, 0, no])
+
+
+# ---- oracle pinned by the reference's own Noise / Simplex CLASSES (noise.cpp, simplex.cpp in place) --------
+def test_oracle_fbm_and_ridged_equal_reference_class_golden(oracle):
+    """tests/golden/noise_class_ref.npz was produced by Noise::octave_noise_3d (noise.cpp:162-180) and
+    Noise::getRidgedMf (noise.cpp:81-128) of the reference itself, compiled in place against oracle/qtshim with
+    the argument patterns of galaxycomponents.cpp. The restated fBm and ridged multifractal must match bit for bit."""
+    g = np.load(os.path.join(ROOT, "tests", "golden", "noise_class_ref.npz"))
+    pts = g["pts"]
+    for (oc, pe, sc), ref in zip(g["fbm_cases"], g["fbm"]):
+        assert np.array_equal(oracle.fbm(pts, int(oc), float(pe), float(sc)), ref), (oc, pe, sc)
+    for (fr, oc, lac, off, gain, scale), ref in zip(g["rid_cases"], g["rid"]):
+        q = np.ascontiguousarray(pts * np.float32(scale))
+        # a negative frequency (ks < 0) makes pow(frequency, -0.05) NaN in the reference too: compared as equal NaNs
+        assert np.array_equal(oracle.ridged(q, float(fr), int(oc), float(lac), float(off), float(gain)), ref, equal_nan=True), (fr, off, gain, scale)
