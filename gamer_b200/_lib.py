@@ -11,7 +11,7 @@ LIB_PATH = os.environ.get("GAMER_B200_LIB") or os.path.join(_HERE, "lib", "libga
 
 CNT_RAYS, CNT_SAMPLES, CNT_GATES, CNT_COMP_EVALS, CNT_OCTAVES, CNT_N = 0, 1, 2, 3, 4, 8
 E_ARG, E_CUDA, E_ABORTED, E_STATE = -1, -2, -3, -4
-FRAME_CONTINUE, FRAME_PARTIAL = 1, 2
+FRAME_CONTINUE, FRAME_PARTIAL, FRAME_NO_RADIAL_GATE = 1, 2, 4
 MAX_GALAXIES, MAX_COMPONENTS = 8, 64
 
 CLASS_IDS = {          # factory strings of source/galaxy/galaxy.cpp:15-42

@@ -49,7 +49,7 @@ int gk_build_scene(const GamerFrame *f, const GamerGalaxy *gal, const GamerCompo
     if (f->n_galaxies < 0 || f->n_galaxies > DEV_MAX_GALAXIES) return fail("n_galaxies out of range (max 8 per frame)");
     if (f->n_components < 0) return fail("n_components negative");
     if ((f->n_galaxies && !gal) || (f->n_components && !comp)) return fail("null galaxy/component array");
-    if (f->flags & ~(GAMER_FRAME_CONTINUE | GAMER_FRAME_PARTIAL)) return fail("unknown frame flags");
+    if (f->flags & ~(GAMER_FRAME_CONTINUE | GAMER_FRAME_PARTIAL | GAMER_FRAME_NO_RADIAL_GATE)) return fail("unknown frame flags");
     if (f->band_rows < 0 || (f->band_rows > 0 && f->band_stride < f->band_rows)) return fail("bad band_rows/band_stride");
     if (!(f->ray_step > 0.0) || !(f->min_ray_step > 0.0) || f->min_ray_step > 0.01) return fail("ray_step/min_ray_step out of range");
 
@@ -137,12 +137,13 @@ int gk_build_scene(const GamerFrame *f, const GamerGalaxy *gal, const GamerCompo
             // radial gate (galaxycomponent.h:72-81, galaxycomponent.cpp:58-65)
             const float ax = g.axis[0];
             const double r0h = c.r0 * 0.5f;
+            const double radial_floor = (f->flags & GAMER_FRAME_NO_RADIAL_GATE) ? 0.0 : 0.001;
             auto radial = [&](float plen) {
                 float radius = plen / ax;
                 double r = std::exp(-double(radius) / r0h);
                 double in = ref_clamp(r - 0.01f, 0, 1);
                 if (in > 0.1) in = 0.1;
-                return in > 0.001;
+                return in > radial_floor;   // 0.001 as written; 0 when the test is compiled away (gamer_b200.h)
             };
             if (c.r0 > 0 && ax > 0) q.plen_thr = largest_passing(radial);
             else q.plen_thr = radial(1.0f) ? std::numeric_limits<float>::infinity() : -1.0f;

@@ -116,6 +116,7 @@ Scene RasterizerB200::Prepare() const {
     f.cam[0] = cam.x; f.cam[1] = cam.y; f.cam[2] = cam.z;
     f.ray_step = double(rp.rayStep());
     f.min_ray_step = m_isPreview ? 0.01 : 0.001;  // rasterizer.cpp:437-441
+    f.flags = m_noRadialGate ? GAMER_FRAME_NO_RADIAL_GATE : 0;
     f.n_galaxies = int32_t(sc.galaxies.size());
     f.n_components = int32_t(sc.components.size());
     return sc;
@@ -153,7 +154,8 @@ int RasterizerB200::RenderPixels() {
         GamerFrame f = sc.frame;
         f.n_galaxies = int32_t(gals.size());
         f.n_components = int32_t(comps.size());
-        f.flags = (first > 0 ? GAMER_FRAME_CONTINUE : 0) | (last < ng ? GAMER_FRAME_PARTIAL : 0);
+        f.flags = (sc.frame.flags & GAMER_FRAME_NO_RADIAL_GATE) | (first > 0 ? GAMER_FRAME_CONTINUE : 0) |
+                  (last < ng ? GAMER_FRAME_PARTIAL : 0);
         rc = gamer_b200_upload(m_ctx, &f, gals.empty() ? &no_gal : gals.data(), comps.empty() ? &no_comp : comps.data());
         if (rc != GAMER_OK) return rc;
         rc = last < ng ? gamer_b200_render_device(m_ctx) : gamer_b200_render(m_ctx, m_renderBuffer.data());

@@ -104,6 +104,9 @@ public:
     void Clear() { m_galaxies.clear(); }
     void CopyFrom(const RasterizerB200* from) { m_galaxies = from->m_galaxies; }
     void setNewSize(int s) { m_renderingParams->setSize(s); }
+    // gamer_b200.h GAMER_FRAME_NO_RADIAL_GATE: reproduce a g++/clang -O1+ build of the reference, in which the
+    // `intensity > 0.001` test of galaxycomponent.cpp:62 is compiled away (default: the test as written)
+    void setNoRadialGate(bool on) { m_noRadialGate = on; }
 
     // render (rasterizer.cpp:190-213, 283-313, 350-370)
     Scene Prepare() const;
@@ -141,6 +144,7 @@ private:
     std::atomic<int> m_status{0};
     bool m_isPreview = false;
     bool m_deviceStars = false;
+    bool m_noRadialGate = false;
     uint64_t m_starSeed = 0;
     int m_width = 0, m_height = 0;
     std::thread m_thread;

@@ -126,7 +126,7 @@ class Scene:
 
 
 def build_scene(rp: RenderingParams, instances: List[GalaxyInstance], preview: bool = False,
-                inv_vp: Optional[np.ndarray] = None) -> Scene:
+                inv_vp: Optional[np.ndarray] = None, no_radial_gate: bool = False) -> Scene:
     """Rasterizer::Prepare: sort far->near by |position - camera| (stable, like std::sort on the
     reference's small lists is in practice), build components with resolved spectra, camera matrix."""
     cam = np.array(rp.camera().m_camera, dtype=np.float32)
@@ -172,6 +172,7 @@ def build_scene(rp: RenderingParams, instances: List[GalaxyInstance], preview: b
     f.cam[:] = [float(v) for v in cam]
     f.ray_step = float(rp.rayStep())
     f.min_ray_step = 0.01 if preview else 0.001     # rasterizer.cpp:437-441
+    f.flags = _lib.FRAME_NO_RADIAL_GATE if no_radial_gate else 0   # gamer_b200.h: the test g++ -O1+ deletes
     f.n_galaxies, f.n_components = len(gals), len(comps)
     ga = (_lib.GamerGalaxy * max(1, len(gals)))(*gals)
     ca = (_lib.GamerComponent * max(1, len(comps)))(*comps)
@@ -210,6 +211,7 @@ def split_passes(scene: Scene) -> List[Scene]:
             gals.append(g)
         fr = _lib.GamerFrame.from_buffer_copy(f)
         fr.n_galaxies, fr.n_components = len(gals), len(comps)
-        fr.flags = (_lib.FRAME_CONTINUE if ci > 0 else 0) | (_lib.FRAME_PARTIAL if ci < len(chunks) - 1 else 0)
+        fr.flags = ((f.flags & _lib.FRAME_NO_RADIAL_GATE) | (_lib.FRAME_CONTINUE if ci > 0 else 0)
+                    | (_lib.FRAME_PARTIAL if ci < len(chunks) - 1 else 0))
         out.append(Scene(fr, (_lib.GamerGalaxy * max(1, len(gals)))(*gals), (_lib.GamerComponent * max(1, len(comps)))(*comps)))
     return out

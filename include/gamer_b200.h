@@ -90,6 +90,14 @@ typedef struct GamerGalaxy {
  * framebuffer between them, unscaled, so the result is bit-identical to a single pass. */
 #define GAMER_FRAME_CONTINUE 1   /* start every pixel from the unscaled I the previous pass left          */
 #define GAMER_FRAME_PARTIAL  2   /* leave the unscaled I (skip the final * 0.01 / rayStep): more to come  */
+/* GalaxyComponent::calculateIntensity (galaxycomponent.cpp:45-88) has no return statement on the path where
+ * `intensity > 0.001` (:62) fails. As written (and as the reference's tools/galaxy_repro.py:609 restates it)
+ * such a sample contributes nothing: that is the default here. g++ and clang at -O1 and above — the reference's
+ * own build uses -Ofast, gamer.pro:13 — treat the return-less path as unreachable and delete the test, so in
+ * those binaries every sample with intensity > 0 goes on to the `val * weight > 0.0005` test (:79). Set this
+ * flag to reproduce such a build. Both behaviours are pinned against the reference's own code compiled in
+ * place (oracle/Makefile, tests/test_ref_path.py). */
+#define GAMER_FRAME_NO_RADIAL_GATE 4
 
 /* One frame: camera + size + step (RenderingParams, GamerCamera). Galaxies must already be sorted
  * far -> near as Rasterizer::Prepare does (rasterizer.cpp:190-201). */

@@ -206,6 +206,7 @@ struct Ctx {            // what a GalaxyComponent sees
     V3 orient;
     Quat rotmat;
     Counters *cn;
+    bool radial_gate = true;   // false: GAMER_FRAME_NO_RADIAL_GATE (the test g++ -O1+ deletes, see gamer_b200.h)
 };
 
 inline double c_cosh(double x) { return (std::exp(x) + std::exp(-x)) / 2.0; }   // galaxycomponent.h:57-59
@@ -361,7 +362,7 @@ void calculate_intensity(const Ctx &c, Pixel &rp, V3 &p, double weight) {
     if (rp.z > 0.01) {
         double intensity = radial_intensity(c, rp.radius);
         if (intensity > 0.1) intensity = 0.1;
-        if (intensity > 0.001) {
+        if (intensity > 0.001 || !c.radial_gate) {
             double scale = std::pow(u_smoothstep(0, 1.0f * cp.inner, rp.radius), 4);
             if (cp.arm != 0) {
                 armVal = arm_value(c, rp.radius, rp.P);
@@ -394,6 +395,10 @@ V3 coord2ray(const GamerFrame &f, double x, double y, double width) {
     return q5::normalized(V3(o[0], o[1], o[2]));
 }
 
+// debug trace of one pixel's march (go_trace_pixel): (p.xyz, step, I.xyz) after every sample
+static float *g_trace = nullptr;
+static int g_trace_n = 0, g_trace_max = 0;
+
 // Rasterizer::getIntensity (rasterizer.cpp:422-483)
 void march(const Scene &sc, const GamerGalaxy &g, Pixel &rp, V3 isp1, V3 isp2, Counters &cn) {
     V3 origin = isp1;
@@ -411,6 +416,7 @@ void march(const Scene &sc, const GamerGalaxy &g, Pixel &rp, V3 isp1, V3 isp2, C
     c.orient = V3(g.orient[0], g.orient[1], g.orient[2]);
     c.rotmat = Quat(g.rotmat[0], g.rotmat[1], g.rotmat[2], g.rotmat[3]);
     c.cn = &cn;
+    c.radial_gate = !(sc.f.flags & GAMER_FRAME_NO_RADIAL_GATE);
     cn.c[GAMER_CNT_RAYS]++;
     while (q5::dot(p - origin, ll) < length + step) {
         step = u_clamp(std::pow(q5::length(p - camera), 1) * sc.f.ray_step, minRayStep, 0.01);
@@ -424,6 +430,11 @@ void march(const Scene &sc, const GamerGalaxy &g, Pixel &rp, V3 isp1, V3 isp2, C
                 calculate_intensity(c, rp, p, step * 200.0);
             }
         }
+        if (g_trace && g_trace_n < g_trace_max) {
+            float *o = g_trace + (size_t)g_trace_n * 7;
+            o[0] = p.x; o[1] = p.y; o[2] = p.z; o[3] = float(step); o[4] = rp.I.x; o[5] = rp.I.y; o[6] = rp.I.z;
+        }
+        if (g_trace) g_trace_n++;
         p = p - dir * float(step);
         cn.c[GAMER_CNT_SAMPLES]++;
         rp.I = u_floor(rp.I);
@@ -495,6 +506,21 @@ int go_max_threads(void) {
 // Rasterizer::RenderPixelsOMP (rasterizer.cpp:283-313). The shuffled render order and the DrawBox
 // progressive splat (buffer2d.cpp:52-63) do not change the final image (every pixel is eventually
 // rendered and written at its own location), so each pixel is rendered once and stored once.
+// Debug aid for tests: march pixel (i, j) single-threaded and record every sample. Returns the sample count.
+int go_trace_pixel(const GamerFrame *frame, const GamerGalaxy *gal, const GamerComponent *comp, int i, int j,
+                   int max_samples, float *out7) {
+    Scene sc;
+    sc.f = *frame;
+    sc.gal.assign(gal, gal + frame->n_galaxies);
+    sc.comp.assign(comp, comp + frame->n_components);
+    Counters cn;
+    g_trace = out7; g_trace_n = 0; g_trace_max = max_samples;
+    V3 dir = coord2ray(sc.f, i, j, frame->full_size);
+    render_pixel(sc, dir, cn);
+    g_trace = nullptr;
+    return g_trace_n;
+}
+
 int go_render(const GamerFrame *frame, const GamerGalaxy *gal, const GamerComponent *comp,
               float *rgb_out, uint64_t counters_out[GAMER_CNT_N], int n_threads) {
     if (!frame || !gal || !comp || !rgb_out) return GAMER_E_ARG;

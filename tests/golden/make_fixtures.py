@@ -9,6 +9,11 @@
   noise_class_ref.npz  Noise::octave_noise_3d and Noise::getRidgedMf of the reference's OWN noise.cpp / simplex.cpp
                    (class Simplex(1,1,1,1), as Rasterizer constructs it), compiled in place against oracle/qtshim,
                    with the argument patterns of galaxycomponents.cpp (disk/dust/stars fBm, dust2 ridged)
+  ref_path_frames.npz  whole frames rendered by the reference's OWN Rasterizer (Prepare, RenderPixels, renderPixel,
+                   getIntensity, the GalaxyComponent classes, GamerCamera, Buffer2D::ToColorBuffer ...) compiled in
+                   place against oracle/qtshim (oracle/ref_path_wrap.cpp), for the scenes of tests/ref_cases.py:
+                   "<case>|src" as the source reads, "<case>|o2" as g++ -O2 compiles it (see oracle/Makefile),
+                   plus "<case>|tm<k>|image/shadow" ARGB32 images of AssembleImage
 """
 import ctypes as C
 import glob
@@ -79,6 +84,27 @@ def main():
     np.savez_compressed(os.path.join(HERE, "noise_class_ref.npz"), pts=pf, fbm_cases=np.array(fbm_cases), fbm=fbm,
                         rid_cases=np.array(rid_cases), rid=rid)
     print("wrote", len(out), "galaxies,", len(pts), "noise points,", n, "class-level noise points")
+    ref_path_frames()
+
+
+def ref_path_frames():
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import ref_cases
+    import ref_path_lib
+    frames = {}
+    for name, case in ref_cases.cases().items():
+        rp, gis, preview = case
+        for kind in ("src", "o2"):
+            with ref_path_lib.RefRasterizer(rp, gis, kind) as r:
+                frames[name + "|" + kind] = r.render(preview)
+                if kind == "src" and name in ref_cases.TONEMAP_CASES:
+                    for k, (e, g, s) in enumerate(ref_cases.TONEMAPS):
+                        img, shadow = r.assemble(e, g, s)
+                        frames["%s|tm%d|image" % (name, k)] = img
+                        frames["%s|tm%d|shadow" % (name, k)] = shadow
+        print(name, float(frames[name + "|src"].max()), float(np.abs(frames[name + "|src"] - frames[name + "|o2"]).max()))
+    np.savez_compressed(os.path.join(HERE, "ref_path_frames.npz"), **frames)
+    print("wrote", len(frames), "reference frames/images")
 
 
 if __name__ == "__main__":

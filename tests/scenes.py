@@ -34,11 +34,11 @@ def rendering_params(size, view="cli", ray_step=RAY_STEP) -> RenderingParams:
 
 
 def single_galaxy_scene(name_or_galaxy, size, view="cli", ray_step=RAY_STEP, preview=False,
-                        position=(0, 0, 0), orientation=(0, 1, 0), iscale=1.0):
+                        position=(0, 0, 0), orientation=(0, 1, 0), iscale=1.0, no_radial_gate=False):
     g = load_galaxy(name_or_galaxy) if isinstance(name_or_galaxy, str) else name_or_galaxy
     rp = rendering_params(size, view, ray_step)
     gi = GalaxyInstance(g, g.galaxyParams.name, position, orientation, iscale, 0.0)
-    return build_scene(rp, [gi], preview=preview)
+    return build_scene(rp, [gi], preview=preview, no_radial_gate=no_radial_gate)
 
 
 def multi_galaxy_scene(size, view="outside", ray_step=RAY_STEP):

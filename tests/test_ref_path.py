@@ -1,0 +1,108 @@
+"""The oracle against frames rendered by the reference's OWN render path compiled in place
+(tests/golden/ref_path_frames.npz, made by tests/golden/make_fixtures.py from oracle/_ref/libgamer_ref_path*.so).
+Bit-for-bit: every float of every frame, both readings of galaxycomponent.cpp:62 (gamer_b200.h,
+GAMER_FRAME_NO_RADIAL_GATE), and every ARGB32 pixel of AssembleImage.  The -m gpu tests hold the CUDA path
+to the same frames within the linear-intensity tolerance."""
+import os
+
+import numpy as np
+import pytest
+
+import ref_cases
+import ref_path_lib
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref_path_frames.npz")
+CASES = ref_cases.cases()
+KINDS = {"src": False, "o2": True}       # fixture suffix -> no_radial_gate
+
+
+@pytest.fixture(scope="module")
+def golden():
+    return np.load(GOLDEN)
+
+
+def test_golden_covers_every_case(golden):
+    for name in CASES:
+        for kind in KINDS:
+            assert name + "|" + kind in golden.files
+    # the two readings of the return-less path do differ on the shipped galaxies
+    assert any(not np.array_equal(golden[n + "|src"], golden[n + "|o2"]) for n in CASES)
+
+
+@pytest.mark.parametrize("kind", sorted(KINDS))
+@pytest.mark.parametrize("name", sorted(CASES))
+def test_oracle_equals_reference_frame(golden, oracle, name, kind):
+    sc = ref_cases.scene_of(CASES[name], no_radial_gate=KINDS[kind])
+    rgb, cnt = oracle.render(sc)
+    ref = golden[name + "|" + kind]
+    assert rgb.shape == ref.shape
+    assert ref.max() > 1.0                                   # a real picture, not an empty frame
+    assert np.array_equal(rgb.view(np.uint32), ref.view(np.uint32)), \
+        "oracle differs from the reference's own code: max |d| = %g" % float(np.abs(rgb - ref).max())
+
+
+@pytest.mark.parametrize("name", ref_cases.TONEMAP_CASES)
+def test_oracle_tonemap_equals_reference_assemble(golden, oracle, name):
+    rgb = golden[name + "|src"]
+    for k, (e, g, s) in enumerate(ref_cases.TONEMAPS):
+        img, shadow = oracle.tonemap(rgb, e, g, s)
+        assert np.array_equal(np.asarray(img).reshape(rgb.shape[:2]), golden["%s|tm%d|image" % (name, k)])
+        assert np.array_equal(np.asarray(shadow).reshape(rgb.shape[:2]), golden["%s|tm%d|shadow" % (name, k)])
+
+
+@pytest.mark.skipif(not (ref_path_lib.available("src") and ref_path_lib.available("o2")),
+                    reason="oracle/_ref/libgamer_ref_path*.so are built only where the reference checkout exists")
+def test_fixture_is_what_the_reference_library_renders_now(golden):
+    """The committed frames are reproducible from the compiled reference (where it is present)."""
+    for name in ("Spiral/cli", "three/outside"):
+        rp, gis, preview = CASES[name]
+        for kind in KINDS:
+            with ref_path_lib.RefRasterizer(rp, gis, kind) as r:
+                assert np.array_equal(r.render(preview), golden[name + "|" + kind])
+
+
+@pytest.mark.skipif(not ref_path_lib.available("src"), reason="needs oracle/_ref/libgamer_ref_path.so")
+def test_rays_equal_reference_camera(oracle):
+    """GamerCamera::setupViewmatrix + coord2ray (gamercamera.cpp:185-217) through the reference's own code."""
+    import ctypes as C
+    for name in ("Spiral/cli", "Spiral/tilted", "eleven/outside"):
+        rp, gis, preview = CASES[name]
+        sc = ref_cases.scene_of(CASES[name])
+        n = rp.size()
+        with ref_path_lib.RefRasterizer(rp, gis) as r:
+            r.render(preview)                               # Prepare() sets the camera matrices up
+            for idx in list(range(0, n * n, 37)) + [n * n - 1]:
+                d = np.zeros(3, np.float32)
+                oracle.lib.go_coord2ray(C.addressof(sc.frame), idx % n, idx // n, d.ctypes.data)
+                assert np.array_equal(d, r.ray(idx))
+
+
+# ---- the CUDA path against the same frames -------------------------------------------------------------------
+REL, ABS = 1e-3, 1e-5      # |gpu - ref| <= REL * |ref| + ABS on linear intensity (BASELINE.json north_star)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("kind", sorted(KINDS))
+def test_gpu_equals_reference_frames(golden, gpu_ctx, kind):
+    for name in sorted(CASES):
+        sc = ref_cases.scene_of(CASES[name], no_radial_gate=KINDS[kind])
+        rgb = gpu_ctx.render_passes(sc)
+        ref = golden[name + "|" + kind]
+        err = np.abs(rgb.reshape(ref.shape) - ref) - (REL * np.abs(ref) + ABS)
+        assert err.max() <= 0, "%s|%s: exceeds tolerance by %g" % (name, kind, float(err.max()))
+
+
+@pytest.mark.gpu
+def test_gpu_tonemap_equals_reference_assemble(golden, gpu_ctx):
+    """K2 on the reference's own frames: an empty scene renders zeros, the frame enters as the added layer
+    (0 + v == v exactly), so every ARGB32 pixel has to equal Buffer2D::ToColorBuffer's."""
+    import scenes
+    from gamer_b200.model import build_scene
+    for name in ref_cases.TONEMAP_CASES:
+        rgb = golden[name + "|src"]
+        gpu_ctx.upload(build_scene(scenes.rendering_params(rgb.shape[0], "cli"), []))
+        assert not gpu_ctx.render().any()
+        for k, (e, g, s) in enumerate(ref_cases.TONEMAPS):
+            img, shadow = gpu_ctx.tonemap(e, g, s, rgb)
+            assert np.array_equal(img, golden["%s|tm%d|image" % (name, k)])
+            assert np.array_equal(shadow, golden["%s|tm%d|shadow" % (name, k)])
