@@ -117,22 +117,64 @@ def cpu_sample_scene(workload: str, row_stride: int):
     return sc.tile(0, 0, n, n // row_stride, band_rows=1, band_stride=row_stride)
 
 
-def time_cpu(workload: str, row_stride: int, repeats: int = 1):
-    """Times the CPU oracle built with the reference's own flags (-Ofast -march=native -fopenmp,
-    gamer.pro:13,20,23) on all host threads. Returns (samples/s, cores, sample description, seconds)."""
-    import oracle_lib
-    o = oracle_lib.load(fast=True)
-    sc = cpu_sample_scene(workload, row_stride)
-    best, samples = None, 0
-    for _ in range(repeats):
+class CpuArm:
+    """The CPU side of the comparison on a bounded sample (every row_stride-th row of frame 0 of the workload).
+    kind "reference": the reference's OWN render path (rasterizer.cpp, galaxycomponent*.cpp, noise/*.cpp ...)
+    compiled in place with its own flags by oracle/Makefile into oracle/_ref/libgamer_ref_path_fast.so
+    (-Ofast -fopenmp, OpenMP over pixels like RenderPixelsOMP) — used whenever that library travelled here and
+    the host has AVX2. kind "port": the oracle restatement built on this machine with -Ofast -march=native
+    -fopenmp. Ray samples are counted by the oracle on the same rows (its march is bit-identical to the
+    reference's, tests/test_ref_path.py); the count is outside the timed region."""
+
+    def __init__(self, workload: str, row_stride: int, threads: int = 0, force_port: bool = False):
+        import oracle_lib
+        import ref_path_lib
+        import scenes
+        from gamer_b200.model import GalaxyInstance
+        self.workload, self.row_stride = workload, row_stride
+        self.scene = cpu_sample_scene(workload, row_stride)
+        self.oracle = oracle_lib.load(fast=True)
+        self.rows, self.size = self.scene.frame.height, self.scene.frame.full_size
+        self.ref = None
+        self.threads = threads
+        if ref_path_lib.available("fast") and not force_port:
+            name, size, view = WORKLOADS[workload]
+            view = orbit_view(0) if view is None else view
+            rp = scenes.rendering_params(size, view)
+            gi = GalaxyInstance(scenes.load_galaxy(name), name, (0, 0, 0), (0, 1, 0), 1.0, 0.0)
+            self.ref = ref_path_lib.RefRasterizer(rp, [gi], "fast")
+            self.ref.render_rows(0, row_stride, 0, 1, prepare=True)      # Rasterizer::Prepare, once, untimed
+        self.kind = "reference" if self.ref else "port"
+        _, cnt = self.oracle.render(self.scene)
+        self.samples = cnt["samples"]
+        self.cores = threads or self.oracle.max_threads()
+
+    def step(self) -> float:
         t0 = time.perf_counter()
-        _, cnt = o.render(sc)
-        dt = time.perf_counter() - t0
-        samples = cnt["samples"]
-        best = dt if best is None else min(best, dt)
-    desc = (f"frame 0 of {workload}, every {row_stride}th row ({sc.frame.height} of {sc.frame.full_size} rows, "
-            f"{samples} ray samples), pixel loop only, best of {repeats}")
-    return samples / best, o.max_threads(), desc, best
+        if self.ref:
+            _, self.cores = self.ref.render_rows(0, self.row_stride, self.rows, self.threads, prepare=False)
+        else:
+            self.oracle.render(self.scene, self.threads)
+        return time.perf_counter() - t0
+
+    def describe(self) -> str:
+        what = ("the reference's own code (oracle/_ref/libgamer_ref_path_fast.so: -Ofast -march=x86-64-v3 -fopenmp)"
+                if self.ref else "oracle port (-Ofast -march=native -fopenmp)")
+        return (f"frame 0 of {self.workload}, every {self.row_stride}th row ({self.rows} of {self.size} rows, "
+                f"{self.samples} ray samples), pixel loop only, {what}")
+
+    def close(self):
+        if self.ref:
+            self.ref.close()
+
+
+def time_cpu(workload: str, row_stride: int, repeats: int = 1):
+    """cpu_baseline leg. Returns (samples/s, cores, sample description, seconds, kind)."""
+    arm = CpuArm(workload, row_stride)
+    best = min(arm.step() for _ in range(repeats))
+    out = (arm.samples / best, arm.cores, arm.describe() + f", best of {repeats}", best, arm.kind)
+    arm.close()
+    return out
 
 
 # dram__bytes_read.sum + dram__bytes_write.sum of one k1_march launch, from the `ncu --set full` capture
@@ -333,8 +375,8 @@ def run_ours(args):
             "clocks": clk,
         }
         if world == 1 and not args.no_cpu:
-            v, cores, desc, secs = time_cpu(wl, args.cpu_row_stride)
-            out["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": desc, "seconds": secs}
+            v, cores, desc, secs, kind = time_cpu(wl, args.cpu_row_stride)
+            out["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": kind, "sample": desc, "seconds": secs}
         print(json.dumps(out), flush=True)
     # torch tensors that were used on the context's stream must be released while that stream still exists
     gathered[:] = [None, None]
@@ -353,37 +395,32 @@ def ctx_scene_bytes(scene) -> int:
 
 
 def run_reference(args):
-    """Reference arm: the reference's CPU implementation of the path on the host cores. The reference
-    itself cannot be built here (Qt headers absent), so this times the oracle port
-    compiled with the reference's own flags, all host threads, on a bounded sample of the same workload."""
+    """Reference arm: the reference's CPU implementation of the path on the host cores (class CpuArm: the
+    reference's own sources compiled in place when oracle/_ref travelled here, else the oracle port), all host
+    threads, each step a bounded sample of the same workload."""
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     if rank != 0:
         return
-    import oracle_lib
-    o = oracle_lib.load(fast=True)
     wl = args.workload
-    sc = cpu_sample_scene(wl, args.ref_row_stride)
-    times, samples = [], 0
+    arm = CpuArm(wl, args.ref_row_stride)
+    sc, samples = arm.scene, arm.samples
+    times = []
     for i in range(args.warmup + args.steps):
-        t0 = time.perf_counter()
-        _, cnt = o.render(sc)
-        dt = time.perf_counter() - t0
-        samples = cnt["samples"]
+        dt = arm.step()
         if i >= args.warmup:
             times.append(dt)
     total = sum(times)
     value = samples * len(times) / total
     size = WORKLOADS[wl][1]
     frac = sc.frame.height / sc.frame.full_size
-    desc = (f"each step = every {args.ref_row_stride}th row of frame 0 of {wl} ({sc.frame.height} of {size} rows, {samples} "
-            f"ray samples); a whole frame is ~{1 / frac:.0f}x that")
+    desc = f"each step = {arm.describe()}; a whole frame is ~{1 / frac:.0f}x that"
     out = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
            "warmup": args.warmup, "ms_per_step": 1e3 * total / len(times), "higher_is_better": True, "scaling": "weak",
            "vs_baseline": None, "dtype": "f64/f32 (reference mix)", "data": "synthetic",
            "config": {"workload": wl, "galaxy": WORKLOADS[wl][0] + ".gax (tests/golden/gax)", "size": size, "ray_step": "0.025f",
                       "sample": desc, "est_ms_per_full_frame": 1e3 * total / len(times) / frac},
-           "cpu_baseline": {"value": value, "unit": UNIT, "cores": o.max_threads(), "kind": "port", "sample": desc},
+           "cpu_baseline": {"value": value, "unit": UNIT, "cores": arm.cores, "kind": arm.kind, "sample": desc},
            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
            "gpu_launches": 0}
     print(json.dumps(out), flush=True)

@@ -3,17 +3,30 @@
 // Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may
 // load this library, and only as the checker or the timed CPU baseline — never as a product path.
 //
-// PARITY UNPINNED: the reference ships no golden vectors, known-answer tests or baseline images
-// for this path (its two harnesses need Gamer.exe + PySide6/slangpy, absent here),
-// and the reference itself cannot be built here (every file on the path includes Qt headers; Qt is
-// not installed).  What pins this file: (1) its noise layer — raw simplex, fBm (octave_noise_3d) and
-// the ridged multifractal (getRidgedMf) — is checked bit-for-bit against the reference's own
-// source/noise/{simplexnoise,noise,simplex}.cpp compiled in place into oracle/_ref (see Makefile; the
-// two class files against the minimal Qt stand-ins of oracle/qtshim) and against the golden vectors
-// those libraries produced (tests/golden/simplex_ref.npz, noise_class_ref.npz); everything ABOVE the
-// noise layer (march, components, camera, post-process) remains unpinned;
-// (2) it follows the reference line by line, each function citing what it restates; (3) Qt's float
-// value-class arithmetic is restated in qt5_math.h (Qt 5.15 semantics).
+// PARITY PINNED — against the reference's own code, compiled in place and run in the build container.
+//   * whole path (rasterizer.cpp Prepare/RenderPixels/renderPixel/getIntensity, galaxycomponent.h/.cpp,
+//     galaxycomponents.cpp, galaxy.cpp SetupComponents + .gax reader, galaxyinstance.cpp, gamercamera.cpp,
+//     buffer2d.cpp ToColorBuffer/PostProcess, util.h IntersectSphere/clamp/smoothstep/floor, noise/*.cpp):
+//     `make -C oracle ref` compiles those UNMODIFIED sources where they lie under /root/reference into
+//     oracle/_ref/libgamer_ref_path*.so (door: oracle/ref_path_wrap.cpp). tests/golden/ref_path_frames.npz
+//     holds 26 scenes rendered by it — all nine shipped galaxies, five views, preview mode, tilted / flipped /
+//     displaced instances, synthetic galaxies covering the classes and branches no shipped file uses, 3- and
+//     11-galaxy scenes — and tests/test_ref_path.py requires this oracle to reproduce EVERY FLOAT of every
+//     frame bit-for-bit, every ARGB32 pixel of AssembleImage at four exposure/gamma/saturation settings,
+//     and the camera rays. It does, in both readings of the return-less path of
+//     GalaxyComponent::calculateIntensity (galaxycomponent.cpp:62-88; GAMER_FRAME_NO_RADIAL_GATE in
+//     gamer_b200.h explains the two).
+//   * what is NOT the reference's code in that build: Qt. Its headers are absent here, so the QVector3D /
+//     QQuaternion / QMatrix4x4 arithmetic is oracle/qt5_math.h's restatement of Qt 5.15 (shared by this
+//     oracle and by the stand-in classes of oracle/qtshim/qtshim.h the reference sources compile against),
+//     QThread::start runs synchronously and OpenMP is off. The pin is therefore "modulo Qt value-class
+//     arithmetic": control flow, formulas, evaluation order, casts and libm calls are the reference's own.
+//   * noise layer: additionally pinned on its own (tests/golden/simplex_ref.npz, noise_class_ref.npz): 1009
+//     raw values + fBm / ridged cases from the reference's simplexnoise.cpp / noise.cpp / simplex.cpp.
+//   * "stars small" (galaxycomponents.cpp:159-170) draws from libc rand() per sample and is not
+//     reproducible; it is dropped here, in the product and in the reference's tools/galaxy_repro.py:734-737.
+//   * the star layer's random draws (buffer2d.cpp:128-165, libc rand()) are likewise not reproducible; only
+//     the stamping arithmetic is restated (go_stamp_stars).
 //
 // Precision follows the reference exactly: scalars are double, vectors are float32 Qt value
 // classes, `double * QVector3D` narrows the scalar to float first, M_PI is 3.14159265 in the

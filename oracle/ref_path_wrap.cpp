@@ -8,6 +8,9 @@
 // Only tests/golden/make_fixtures.py and tests/ load this library; it exists where /root/reference exists.
 #include <cstdint>
 #include <cstring>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
 
 #include "source/galaxy/rasterizer.h"
 #include "source/galaxy/galaxycomponent.h"
@@ -58,6 +61,36 @@ int refpath_render(void *hp, int preview, float *rgb_out) {
             o[0] = v.x(); o[1] = v.y(); o[2] = v.z();
         }
     return 0;
+}
+
+// Timing door (bench.py --impl reference, cpu_baseline): rows row0, row0+stride, ... (n_rows of them) of the
+// frame through the reference's own per-pixel code — Rasterizer::Prepare once, then setupCamera + renderPixel per
+// pixel, OpenMP over pixels like RenderPixelsOMP (rasterizer.cpp:283-313) when built with -fopenmp.
+// prepare != 0 runs Prepare() (+ one warm-up pixel) first; a caller timing the pixel loop passes it once, untimed.
+// out = n_rows * size * 3 floats. Returns the number of threads used.
+int refpath_render_rows(void *hp, int row0, int stride, int n_rows, int threads, int prepare, float *out) {
+    RefPath *h = static_cast<RefPath *>(hp);
+    const int n = h->rp.size();
+    if (prepare) {
+        h->ras->Prepare();
+        // one pixel on this thread first: the reference allocates some tables lazily (noise.cpp:88-89)
+        RasterPixel warm = h->ras->renderPixel(h->ras->setupCamera((n / 2) * n + n / 2), h->ras->getGalaxies());
+        (void)warm;
+    }
+    int used = 1;
+#ifdef _OPENMP
+    if (threads <= 0) threads = omp_get_max_threads();
+    used = threads;
+#pragma omp parallel for schedule(dynamic, 16) num_threads(threads)
+#endif
+    for (int k = 0; k < n_rows * n; k++) {
+        const int j = row0 + (k / n) * stride, i = k % n;
+        RasterPixel p = h->ras->renderPixel(h->ras->setupCamera(i + j * n), h->ras->getGalaxies());
+        out[size_t(k) * 3 + 0] = p.I().x();
+        out[size_t(k) * 3 + 1] = p.I().y();
+        out[size_t(k) * 3 + 2] = p.I().z();
+    }
+    return used;
 }
 
 // One ray through Rasterizer::setupCamera + renderPixel (after a render has run Prepare()).

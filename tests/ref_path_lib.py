@@ -13,12 +13,22 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIBS = {"src": os.path.join(ROOT, "oracle", "_ref", "libgamer_ref_path.so"),
-        "o2": os.path.join(ROOT, "oracle", "_ref", "libgamer_ref_path_o2.so")}
+        "o2": os.path.join(ROOT, "oracle", "_ref", "libgamer_ref_path_o2.so"),
+        # the timing build: -Ofast -fopenmp -march=x86-64-v3 (bench.py --impl reference / cpu_baseline)
+        "fast": os.path.join(ROOT, "oracle", "_ref", "libgamer_ref_path_fast.so")}
 _loaded = {}
 
 
 def available(kind="src"):
-    return os.path.exists(LIBS[kind])
+    if not os.path.exists(LIBS[kind]):
+        return False
+    if kind == "fast":          # built for x86-64-v3: needs AVX2/FMA/BMI2 on the machine it runs on
+        try:
+            flags = next(l for l in open("/proc/cpuinfo") if l.startswith("flags")).split()
+        except (OSError, StopIteration):
+            return False
+        return all(f in flags for f in ("avx2", "fma", "bmi2", "movbe", "f16c"))
+    return True
 
 
 def _lib(kind):
@@ -29,6 +39,7 @@ def _lib(kind):
         L.refpath_create.argtypes = [C.c_int, C.c_double, p, p, p, C.c_double]
         L.refpath_add_galaxy.argtypes = [p, C.c_char_p, p, p, C.c_double, C.c_double]
         L.refpath_render.argtypes = [p, C.c_int, p]
+        L.refpath_render_rows.argtypes = [p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, p]
         L.refpath_pixel.argtypes = [p, C.c_int, p]
         L.refpath_ray.argtypes = [p, C.c_int, p]
         L.refpath_trace.argtypes = [p, C.c_int, C.c_int, C.c_int, p]
@@ -68,6 +79,14 @@ class RefRasterizer:
         out = np.zeros((self.size, self.size, 3), np.float32)
         assert self.L.refpath_render(self.h, int(bool(preview)), out.ctypes.data) == 0
         return out
+
+    def render_rows(self, row0, stride, n_rows, threads=0, prepare=True):
+        """Rows row0, row0+stride, ... through (Prepare +) setupCamera + renderPixel, OpenMP over pixels in the
+        "fast" build. Returns (rgb [n_rows, size, 3], threads used)."""
+        out = np.zeros((n_rows, self.size, 3), np.float32)
+        used = self.L.refpath_render_rows(self.h, int(row0), int(stride), int(n_rows), int(threads), int(bool(prepare)),
+                                          out.ctypes.data)
+        return out, used
 
     def ray(self, idx):
         d = np.zeros(3, np.float32)

@@ -62,6 +62,16 @@ def test_fixture_is_what_the_reference_library_renders_now(golden):
 
 
 @pytest.mark.skipif(not ref_path_lib.available("src"), reason="needs oracle/_ref/libgamer_ref_path.so")
+def test_timing_door_renders_the_same_rows(golden):
+    """bench.py's CPU arm goes through refpath_render_rows (Prepare + setupCamera + renderPixel per pixel):
+    it has to produce the rows Rasterizer::Render produced."""
+    rp, gis, preview = CASES["three/outside"]
+    with ref_path_lib.RefRasterizer(rp, gis, "src") as r:
+        rows, used = r.render_rows(1, 5, 9)
+    assert np.array_equal(rows, golden["three/outside|src"][1:1 + 5 * 9:5])
+
+
+@pytest.mark.skipif(not ref_path_lib.available("src"), reason="needs oracle/_ref/libgamer_ref_path.so")
 def test_rays_equal_reference_camera(oracle):
     """GamerCamera::setupViewmatrix + coord2ray (gamercamera.cpp:185-217) through the reference's own code."""
     import ctypes as C
