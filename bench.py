@@ -172,9 +172,21 @@ def time_cpu(workload: str, row_stride: int, repeats: int = 1):
     """cpu_baseline leg. Returns (samples/s, cores, sample description, seconds, kind)."""
     arm = CpuArm(workload, row_stride)
     best = min(arm.step() for _ in range(repeats))
-    out = (arm.samples / best, arm.cores, arm.describe() + f", best of {repeats}", best, arm.kind)
+    out = (arm.samples / best, arm.cores, arm.describe() + f", best of {repeats}", best, arm.kind, port_value(arm))
     arm.close()
     return out
+
+
+def port_value(arm: "CpuArm"):
+    """When the timed arm is the reference's own code, also time the oracle port on the same sample: the port
+    scales linearly with threads, the reference does not (every calculateIntensity call stores m_currentGI into
+    component objects all threads share, galaxycomponent.cpp:48 — profiles/r01_cpu_scaling.jsonl), so the port is
+    the STRONGER CPU baseline and is reported beside the reference."""
+    if arm.kind != "reference":
+        return None
+    port = CpuArm(arm.workload, arm.row_stride, force_port=True)
+    dt = min(port.step() for _ in range(2))
+    return {"value": port.samples / dt, "unit": UNIT, "cores": port.cores, "kind": "port"}
 
 
 # dram__bytes_read.sum + dram__bytes_write.sum of one k1_march launch, from the `ncu --set full` capture
@@ -375,8 +387,10 @@ def run_ours(args):
             "clocks": clk,
         }
         if world == 1 and not args.no_cpu:
-            v, cores, desc, secs, kind = time_cpu(wl, args.cpu_row_stride)
+            v, cores, desc, secs, kind, port = time_cpu(wl, args.cpu_row_stride)
             out["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": kind, "sample": desc, "seconds": secs}
+            if port:
+                out["cpu_baseline"]["oracle_port"] = port
         print(json.dumps(out), flush=True)
     # torch tensors that were used on the context's stream must be released while that stream still exists
     gathered[:] = [None, None]
@@ -420,7 +434,8 @@ def run_reference(args):
            "vs_baseline": None, "dtype": "f64/f32 (reference mix)", "data": "synthetic",
            "config": {"workload": wl, "galaxy": WORKLOADS[wl][0] + ".gax (tests/golden/gax)", "size": size, "ray_step": "0.025f",
                       "sample": desc, "est_ms_per_full_frame": 1e3 * total / len(times) / frac},
-           "cpu_baseline": {"value": value, "unit": UNIT, "cores": arm.cores, "kind": arm.kind, "sample": desc},
+           "cpu_baseline": {"value": value, "unit": UNIT, "cores": arm.cores, "kind": arm.kind, "sample": desc,
+                            **({"oracle_port": port_value(arm)} if arm.kind == "reference" else {})},
            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
            "gpu_launches": 0}
     print(json.dumps(out), flush=True)
