@@ -251,6 +251,9 @@ __device__ __forceinline__ void march(const DScene &sc, const DGalaxy &g, f3 isp
             bulge_add(bk0 * weight, br0, bs0r, bs0g, bs0b, plen3, Ir, Ig, Ib);
             if (g.n_bulge > 1) bulge_add(bk1 * weight, br1, bs1r, bs1g, bs1b, plen3, Ir, Ig, Ib);
             if (COUNT) cn.evals += g.n_bulge;
+            if (COUNT) { cn.samples++; cn.gates += g.comp_count + g.noop_count; }
+            p = v_sub(p, v_mul(dir, stepf));
+            continue;                 // I only grew: the floor below is the identity (scene_build.cpp, fast_ok)
         } else {
             Shared1 s;
             s.p = p;

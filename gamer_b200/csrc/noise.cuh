@@ -12,10 +12,11 @@
 //  * In-cell offsets are the fractional parts (fu,fv,fw) in [0,1); the unskewed corner vectors
 //    follow from x0 = fu - (fu+fv+fw)/6, all FP32 on small numbers, so FP32 loses nothing even at
 //    coordinates ~1e5 where a float product would have no fractional bits left.
-//  * The permutation table lives in shared memory replicated once per bank (256 entries x 32
+//  * The permutation table lives in shared memory replicated once per bank (257 entries x 32
 //    lanes x 4 B = 32 KB): lane l only ever reads bank l, so the data-dependent hash walk is
-//    bank-conflict free.  An entry is (perm[e] << 7) | gradient code of (perm[e] % 12), i.e. the
-//    value is already the byte offset of the next lookup: one IADD + one LOP3 + one LDS per level.
+//    bank-conflict free.  An entry is perm[e] << 7, i.e. the value is already the byte offset of the
+//    next lookup: one IADD + one LOP3 + one LDS per level.  The last level reads a second 32 KB table
+//    whose rows hold the gradient vector itself (one conflict-free 128-bit load per corner).
 //  * The reference's fastfloor quirk (simplexnoise.h:130: exact non-positive integers floor one
 //    too low) is reproduced on a rare path.
 #pragma once
@@ -67,43 +68,74 @@ __host__ __device__ inline uint32_t grad_code(uint32_t g) {
 #define GN_TABLE_ENTRIES 257
 #define GN_TABLE_WORDS (GN_TABLE_ENTRIES * 32)
 #define GN_ADDR_MASK 0x7F80u
-// The replicated table must sit at a 32 KB-aligned address of the CTA's shared window so that a lookup
-// address is ONE LOP3: (off & 0x7F80) | (0x8000 | lane*4), followed by one LDS. Static shared memory
-// starts at window offset 0x400 (the first KB is reserved), so kernels that use the noise code take
-// GN_DYN_SMEM bytes of dynamic shared memory (and no static shared memory): the table occupies window
-// addresses 0x8000..0x1007F. table_init() verifies the base and traps if the layout ever differs.
-#define GN_TABLE_ADDR 0x8000u
+// Two tables in dynamic shared memory, both with a 128-byte row per entry so that one masked index serves both:
+//   hash table      row e = 32 x u32, one per lane (lane l reads bank l only: conflict free), value perm[e] << 7
+//                   (| the gradient code above, used by the probe) — the first two levels of the hash walk;
+//   gradient table  row e = 8 x float4 (gx, gy, gz, g as bits) of grad3[perm[e] % 12], one per lane of a
+//                   quarter warp (a 128-bit shared load is served one quarter warp at a time, and its 8 lanes
+//                   read 8 different 16-byte slots: conflict free) — the last level: ONE 128-bit load returns the
+//                   gradient itself, so the dot product is three FMA-pipe instructions instead of bit tests,
+//                   selects and sign logic on the ALU pipe (the kernel is issue/ALU bound, the LSU is not).
+// Static shared memory starts at window offset 0x400 (the first KB is reserved); kernels that use the noise code
+// take GN_DYN_SMEM bytes of dynamic shared memory and no static shared memory, so the tables sit at fixed
+// window addresses and the base is an immediate of the load. table_init() verifies the base and traps otherwise.
 #define GN_DYN_BASE 0x400u
-#define GN_DYN_SMEM (GN_TABLE_ADDR - GN_DYN_BASE + GN_TABLE_WORDS * 4u)
+#define GN_HASH_ADDR GN_DYN_BASE
+#define GN_GRAD_ADDR (GN_DYN_BASE + GN_TABLE_WORDS * 4u)
+#define GN_DYN_SMEM (2u * GN_TABLE_WORDS * 4u)
+// the same two addresses as plain decimal literals for the inline PTX (checked below)
+#define GN_HASH_IMM 1024
+#define GN_GRAD_IMM 33920
+#define GN_STR2(x) #x
+#define GN_STR(x) GN_STR2(x)
+static_assert(GN_HASH_IMM == GN_HASH_ADDR && GN_GRAD_IMM == GN_GRAD_ADDR, "PTX immediates out of step with the table layout");
 
 extern __shared__ __align__(16) unsigned char gn_dyn_smem[];
 
-// Fill the replicated table; call from all threads of the block, then __syncthreads().
+// grad3 of simplexnoise.h:142-146
+__host__ __device__ inline void grad3_of(uint32_t g, float &gx, float &gy, float &gz) {
+    const float sa = (g & 1u) ? -1.0f : 1.0f, sb = (g & 2u) ? -1.0f : 1.0f;
+    if (g < 4) { gx = sa; gy = sb; gz = 0.0f; }
+    else if (g < 8) { gx = sa; gy = 0.0f; gz = sb; }
+    else { gx = 0.0f; gy = sa; gz = sb; }
+}
+
+// Fill both tables; call from all threads of the block, then __syncthreads().
 __device__ __forceinline__ void table_init() {
     if ((uint32_t)__cvta_generic_to_shared(gn_dyn_smem) != GN_DYN_BASE) __trap();
-    uint32_t *tbl = reinterpret_cast<uint32_t *>(gn_dyn_smem + (GN_TABLE_ADDR - GN_DYN_BASE));
+    uint32_t *tbl = reinterpret_cast<uint32_t *>(gn_dyn_smem);
+    uint32_t *grd = tbl + GN_TABLE_WORDS;
     for (uint32_t w = threadIdx.x + threadIdx.y * blockDim.x; w < GN_TABLE_WORDS; w += blockDim.x * blockDim.y) {
-        uint32_t e = (w >> 5) & 255u;
-        uint32_t p = c_perm[e];
-        tbl[w] = (p << 7) | grad_code(p % 12u);
+        const uint32_t p = c_perm[(w >> 5) & 255u], g = p % 12u;
+        tbl[w] = (p << 7) | grad_code(g);
+        float gx, gy, gz;
+        grad3_of(g, gx, gy, gz);
+        const uint32_t c = w & 3u;
+        grd[w] = c == 0 ? __float_as_uint(gx) : c == 1 ? __float_as_uint(gy) : c == 2 ? __float_as_uint(gz) : g;
     }
 }
-// per-lane constant of the lookup address
-__device__ __forceinline__ uint32_t lane_const() { return GN_TABLE_ADDR | ((threadIdx.x & 31u) << 2); }
+// per-lane constant of the lookup address: the lane's bank in a hash-table row
+__device__ __forceinline__ uint32_t lane_const() { return (threadIdx.x & 31u) << 2; }
 
-// one level of the hash walk: shared-window address of entry ((off7 >> 7) & 255) of this lane's bank ...
+// one level of the hash walk: row offset of entry ((off7 >> 7) & 255) plus this lane's slot in the row ...
 __device__ __forceinline__ uint32_t addr_of(uint32_t lane4, uint32_t off7) { return (off7 & GN_ADDR_MASK) | lane4; }
-// ... and the entry at that address, or the one after it
-__device__ __forceinline__ uint32_t ld0(uint32_t a) { uint32_t v; asm("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a)); return v; }
-__device__ __forceinline__ uint32_t ld1(uint32_t a) { uint32_t v; asm("ld.shared.u32 %0, [%1+128];" : "=r"(v) : "r"(a)); return v; }
-
-// ±a ± b from a table entry
-__device__ __forceinline__ float grad_dot(uint32_t e, float x, float y, float z) {
-    float a = (e & 0x20000u) ? y : x;
-    float b = (e & 0x40000u) ? y : z;
-    b = __uint_as_float(__float_as_uint(b) ^ (e & 0x80000000u));
-    const float w = a + b;
-    return (e & 0x80000u) ? -w : w;
+// ... and the hash entry at that address, or the one after it
+__device__ __forceinline__ uint32_t ld0(uint32_t a) {
+    uint32_t v; asm("ld.shared.u32 %0, [%1+" GN_STR(GN_HASH_IMM) "];" : "=r"(v) : "r"(a)); return v;
+}
+__device__ __forceinline__ uint32_t ld1(uint32_t a) {
+    uint32_t v; asm("ld.shared.u32 %0, [%1+" GN_STR(GN_HASH_IMM) "+128];" : "=r"(v) : "r"(a)); return v;
+}
+// ... or the gradient at that address / the one after it (address built with the lane's 16-byte slot)
+struct Grad { float x, y, z; uint32_t g; };
+__device__ __forceinline__ Grad gd0(uint32_t a) {
+    Grad v; asm("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4+" GN_STR(GN_GRAD_IMM) "];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=r"(v.g) : "r"(a)); return v;
+}
+__device__ __forceinline__ Grad gd1(uint32_t a) {
+    Grad v; asm("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4+" GN_STR(GN_GRAD_IMM) "+128];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=r"(v.g) : "r"(a)); return v;
+}
+__device__ __forceinline__ float grad_dot(const Grad &e, float x, float y, float z) {
+    return fmaf(e.z, z, fmaf(e.y, y, e.x * x));
 }
 
 struct Lattice {   // filled only by the probe path
@@ -172,11 +204,12 @@ __device__ __forceinline__ float simplex_cell(uint32_t lane4, uint32_t I7, uint3
     const uint32_t B1 = j1 ? ld1(aB1) : ld0(aB1);
     const uint32_t B2 = j2 ? ld1(aB2) : ld0(aB2);
     const uint32_t B3 = ld1(aJ1);
-    const uint32_t aC1 = addr_of(lane4, B1 + I7), aC2 = addr_of(lane4, B2 + I7);
-    const uint32_t C0 = ld0(addr_of(lane4, B0 + I7));
-    const uint32_t C1 = i1 ? ld1(aC1) : ld0(aC1);
-    const uint32_t C2 = i2 ? ld1(aC2) : ld0(aC2);
-    const uint32_t C3 = ld1(addr_of(lane4, B3 + I7));
+    const uint32_t lane16 = (lane4 << 2) & 0x70u;      // (lane % 8) * 16: this lane's slot in a gradient row
+    const uint32_t aC1 = addr_of(lane16, B1 + I7), aC2 = addr_of(lane16, B2 + I7);
+    const Grad C0 = gd0(addr_of(lane16, B0 + I7));
+    const Grad C1 = i1 ? gd1(aC1) : gd0(aC1);
+    const Grad C2 = i2 ? gd1(aC2) : gd0(aC2);
+    const Grad C3 = gd1(addr_of(lane16, B3 + I7));
 
     float t0 = fmaxf(0.6f - x0 * x0 - y0 * y0 - z0 * z0, 0.0f);
     float t1 = fmaxf(0.6f - x1 * x1 - y1 * y1 - z1 * z1, 0.0f);
@@ -191,7 +224,7 @@ __device__ __forceinline__ float simplex_cell(uint32_t lane4, uint32_t I7, uint3
     if (PROBE) {
         lat->c1 = (int)i1 + 2 * (int)j1 + 4 * (int)k1;
         lat->c2 = (int)i2 + 2 * (int)j2 + 4 * (int)k2;
-        lat->g0 = (C0 >> 20) & 15; lat->g1 = (C1 >> 20) & 15; lat->g2 = (C2 >> 20) & 15; lat->g3 = (C3 >> 20) & 15;
+        lat->g0 = (int)C0.g; lat->g1 = (int)C1.g; lat->g2 = (int)C2.g; lat->g3 = (int)C3.g;
     }
     return n;        // 1/32 of the raw value: callers fold the factor into their own scale
 }

@@ -170,6 +170,11 @@ int gk_build_scene(const GamerFrame *f, const GamerGalaxy *gal, const GamerCompo
         }
         d.comp_count = nc - d.comp_begin;
         d.fast_ok = d.n_bulge <= 2;
+        // the bulge-only path also skips Util::floor (util.h:62-64): a bulge adds max(k v, 0) * spectrum, which
+        // cannot take a non-negative I below zero unless a spectrum component is negative (or NaN)
+        for (int b = 0; b < d.n_bulge && b < 2; b++)
+            for (int ch = 0; ch < 3; ch++)
+                if (!(s.comp[d.bulge_idx[b]].spec[ch] >= 0.0f)) d.fast_ok = 0;
     }
     return GAMER_OK;
 }
