@@ -1,0 +1,201 @@
+// dmath.cuh — call-free FP64 elementary functions for the control arithmetic of K1 (sm_100a).
+//
+// The reference evaluates getWinding (galaxycomponent.h:156-165: exp, atan) and the twirl quaternion
+// (galaxycomponent.h:86-90 via QQuaternion::fromAxisAndAngle: sin, cos) with the host libm. Their results are narrowed to
+// float right away (the winding angle, the quaternion), so what has to agree is the float, and an FP64 value within
+// ~1 ulp gives the same float except when it lands within 2^-52 of a rounding boundary (probability ~2^-29 per call) -
+// the same guarantee CUDA's own exp/atan/sincos gave. What CUDA's versions also bring is out-of-line slow paths
+// (Payne-Hanek reduction with a local array, division special cases): CALL sites that pin registers and made the
+// allocator spill the march state. These are straight-line: Cody-Waite reduction + fdlibm's minimax kernels
+// (e_exp.c, s_atan.c, k_sin.c, k_cos.c - Sun Microsystems' freely redistributable coefficients), arguments assumed
+// finite and of moderate size (|x| < 700 for exp, |a| < 1e5 rad for sincos), which the callers guarantee.
+// Compiles for the host as well (tests/ compare it with libm there).
+#pragma once
+#include <math.h>
+#include <stdint.h>
+#include <string.h>
+
+#if defined(__CUDA_ARCH__)
+#define DM_FN __device__ __forceinline__
+#define DM_FMA(a, b, c) __fma_rn((a), (b), (c))
+#define DM_MUL(a, b) __dmul_rn((a), (b))
+#define DM_ADD(a, b) __dadd_rn((a), (b))
+#elif defined(__CUDACC__)
+#define DM_FN __host__ __device__ inline
+#define DM_FMA(a, b, c) fma((a), (b), (c))
+#define DM_MUL(a, b) ((a) * (b))
+#define DM_ADD(a, b) ((a) + (b))
+#else
+#define DM_FN inline
+#define DM_FMA(a, b, c) fma((a), (b), (c))
+#define DM_MUL(a, b) ((a) * (b))
+#define DM_ADD(a, b) ((a) + (b))
+#endif
+
+namespace dmath {
+
+// a / b, correctly rounded for normal operands, without the library's slow-path subroutine
+DM_FN double div_nc(double a, double b) {
+#if defined(__CUDA_ARCH__)
+    double y;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(b));             // ~2^-20
+    double e = __fma_rn(-b, y, 1.0);
+    e = __fma_rn(e, e, e);
+    y = __fma_rn(y, e, y);                                             // ~2^-40
+    e = __fma_rn(-b, y, 1.0);
+    y = __fma_rn(y, e, y);                                             // full precision
+    const double q = __dmul_rn(a, y);
+    return __fma_rn(__fma_rn(-b, q, a), y, q);
+#else
+    return a / b;
+#endif
+}
+// sqrt(x), correctly rounded, x > 0 and normal
+DM_FN double sqrt_nc(double x) {
+#if defined(__CUDA_ARCH__)
+    double y;
+    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));           // ~2^-20
+    const double e = __fma_rn(-x, __dmul_rn(y, y), 1.0);               // 1 - x y^2
+    y = __fma_rn(__fma_rn(e, 0.375, 0.5), __dmul_rn(y, e), y);         // third-order step: ~2^-58
+    const double g = __dmul_rn(x, y), h = __dmul_rn(0.5, y);
+    return __fma_rn(__fma_rn(-g, g, x), h, g);
+#else
+    return sqrt(x);
+#endif
+}
+
+DM_FN double from_bits(uint64_t u) {
+#if defined(__CUDA_ARCH__)
+    return __longlong_as_double((long long)u);
+#else
+    double d; memcpy(&d, &u, 8); return d;
+#endif
+}
+DM_FN uint64_t to_bits(double d) {
+#if defined(__CUDA_ARCH__)
+    return (uint64_t)__double_as_longlong(d);
+#else
+    uint64_t u; memcpy(&u, &d, 8); return u;
+#endif
+}
+
+// nearest integer of a moderate-size double as (double, int) through the 1.5 * 2^52 shifter
+DM_FN double round_int(double v, int &k) {
+    const double shifter = 6755399441055744.0;
+    const double t = DM_ADD(v, shifter);
+    k = (int)(uint32_t)to_bits(t);
+    return DM_ADD(t, -shifter);
+}
+
+// exp(x), |x| < 700: x = k ln2 + r, |r| <= ln2/2; exp(r) by the degree-13 Taylor polynomial (remainder < 4e-18)
+DM_FN double exp_nc(double x) {
+    int k;
+    const double kd = round_int(DM_MUL(x, 1.4426950408889634074), k);
+    double r = DM_FMA(kd, -6.93147180369123816490e-01, x);            // ln2 hi (fdlibm e_exp.c)
+    r = DM_FMA(kd, -1.90821492927058770002e-10, r);                   // ln2 lo
+    double p = 1.0 / 6227020800.0;
+    p = DM_FMA(p, r, 1.0 / 479001600.0);
+    p = DM_FMA(p, r, 1.0 / 39916800.0);
+    p = DM_FMA(p, r, 1.0 / 3628800.0);
+    p = DM_FMA(p, r, 1.0 / 362880.0);
+    p = DM_FMA(p, r, 1.0 / 40320.0);
+    p = DM_FMA(p, r, 1.0 / 5040.0);
+    p = DM_FMA(p, r, 1.0 / 720.0);
+    p = DM_FMA(p, r, 1.0 / 120.0);
+    p = DM_FMA(p, r, 1.0 / 24.0);
+    p = DM_FMA(p, r, 1.0 / 6.0);
+    p = DM_FMA(p, r, 0.5);
+    p = DM_MUL(p, DM_MUL(r, r));
+    p = DM_ADD(DM_ADD(p, r), 1.0);                                     // 1 + r + r^2 (...)
+    return from_bits(to_bits(p) + ((uint64_t)(int64_t)k << 52));        // * 2^k (results stay normal for |x| < 700)
+}
+
+// atan(x) after fdlibm s_atan.c, branch-free: one division picks the reduced argument for all five intervals
+DM_FN double atan_nc(double x) {
+    const double ax = fabs(x);
+    double num, den, hi, lo;
+    if (ax < 0.4375)      { num = ax; den = 1.0; hi = 0.0; lo = 0.0; }
+    else if (ax < 0.6875) { num = DM_FMA(2.0, ax, -1.0); den = DM_ADD(2.0, ax); hi = 4.63647609000806093515e-01; lo = 2.26987774529616870924e-17; }
+    else if (ax < 1.1875) { num = DM_ADD(ax, -1.0); den = DM_ADD(ax, 1.0); hi = 7.85398163397448278999e-01; lo = 3.06161699786838301793e-17; }
+    else if (ax < 2.4375) { num = DM_ADD(ax, -1.5); den = DM_FMA(1.5, ax, 1.0); hi = 9.82793723247329054082e-01; lo = 1.39033110312309984516e-17; }
+    else                  { num = -1.0; den = ax; hi = 1.57079632679489655800e+00; lo = 6.12323399573676603587e-17; }
+    const double t = (ax < 0.4375) ? ax : div_nc(num, den);
+    const double z = DM_MUL(t, t), w = DM_MUL(z, z);
+    double s1 = 1.62858201153657823623e-02;                             // aT[10]
+    s1 = DM_FMA(s1, w, 4.97687799461593236017e-02);                     // aT[8]
+    s1 = DM_FMA(s1, w, 6.66107313738753120669e-02);                     // aT[6]
+    s1 = DM_FMA(s1, w, 9.09088713343650656196e-02);                     // aT[4]
+    s1 = DM_FMA(s1, w, 1.42857142725034663711e-01);                     // aT[2]
+    s1 = DM_FMA(s1, w, 3.33333333333329318027e-01);                     // aT[0]
+    s1 = DM_MUL(s1, z);
+    double s2 = -3.65315727442169155270e-02;                            // aT[9]
+    s2 = DM_FMA(s2, w, -5.83357013379057348645e-02);                    // aT[7]
+    s2 = DM_FMA(s2, w, -7.69187620504482999495e-02);                    // aT[5]
+    s2 = DM_FMA(s2, w, -1.11111104054623557880e-01);                    // aT[3]
+    s2 = DM_FMA(s2, w, -1.99999999998764832476e-01);                    // aT[1]
+    s2 = DM_MUL(s2, w);
+    const double corr = DM_MUL(t, DM_ADD(s1, s2));
+    const double r = DM_ADD(hi, -DM_ADD(DM_ADD(corr, -lo), -t));        // hi - ((t (s1+s2) - lo) - t); hi = lo = 0 below 7/16
+    return x < 0.0 ? -r : r;
+}
+
+// sin and cos of a (|a| < 1e5): a = k pi/2 + r by a three-term Cody-Waite reduction, fdlibm's k_sin / k_cos kernels
+DM_FN void sincos_nc(double a, double &s, double &c) {
+    int k;
+    const double kd = round_int(DM_MUL(a, 6.36619772367581382433e-01), k);
+    double r = DM_FMA(kd, -1.57079632673412561417e+00, a);            // pio2_1  (33 bits)
+    r = DM_FMA(kd, -6.07710050630396597660e-11, r);                   // pio2_2  (33 bits)
+    r = DM_FMA(kd, -2.02226624871116645580e-21, r);                   // pio2_3  (33 bits): residual k * 8e-32
+    const double z = DM_MUL(r, r);
+    double ps = 1.58969099521155010221e-10;                           // S6
+    ps = DM_FMA(ps, z, -2.50507602534068634195e-08);                  // S5
+    ps = DM_FMA(ps, z, 2.75573137070700676789e-06);                   // S4
+    ps = DM_FMA(ps, z, -1.98412698298579493134e-04);                  // S3
+    ps = DM_FMA(ps, z, 8.33333333332248946124e-03);                   // S2
+    ps = DM_FMA(ps, z, -1.66666666666666324348e-01);                  // S1
+    const double sn = DM_FMA(DM_MUL(z, r), ps, r);                     // r + r^3 (S1 + ...)
+    double pc = -1.13596475577881948265e-11;                          // C6
+    pc = DM_FMA(pc, z, 2.08757232129817482790e-09);                   // C5
+    pc = DM_FMA(pc, z, -2.75573143513906633035e-07);                  // C4
+    pc = DM_FMA(pc, z, 2.48015872894767294178e-05);                   // C3
+    pc = DM_FMA(pc, z, -1.38888888888741095749e-03);                  // C2
+    pc = DM_FMA(pc, z, 4.16666666666666019037e-02);                   // C1
+    const double cs = DM_FMA(DM_MUL(z, z), pc, DM_FMA(-0.5, z, 1.0));  // 1 - z/2 + z^2 (C1 + ...)
+    const bool swap = (k & 1) != 0;
+    const double ss = swap ? cs : sn, cc = swap ? sn : cs;
+    s = (k & 2) ? -ss : ss;
+    c = ((k + 1) & 2) ? -cc : cc;
+}
+
+// atan2f(y, x) in float to ~1e-7 absolute (value arithmetic: the arm phase): quotient by reciprocal, one more
+// reciprocal for the (a-1)/(a+1) reduction above tan(pi/8), degree-9 odd minimax polynomial (error < 1e-9)
+DM_FN float atan2f_fast(float y, float x) {
+    const float ax = fabsf(x), ay = fabsf(y);
+    const float mx = fmaxf(ax, ay), mn = fminf(ax, ay);
+#if defined(__CUDA_ARCH__)
+    float r0, r1;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r0) : "f"(mx));
+    float a = mn * r0;
+    if (!(mx > 0.0f)) a = 0.0f;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r1) : "f"(a + 1.0f));
+    const bool red = a > 0.41421356f;
+    const float t = red ? (a - 1.0f) * r1 : a;
+#else
+    float a = mx > 0.0f ? mn / mx : 0.0f;
+    const bool red = a > 0.41421356f;
+    const float t = red ? (a - 1.0f) / (a + 1.0f) : a;
+#endif
+    const float u = t * t;
+    float p = -0.06451928160230586f;
+    p = fmaf(p, u, 0.1074373147094983f);
+    p = fmaf(p, u, -0.14263955595196748f);
+    p = fmaf(p, u, 0.19999540483500192f);
+    p = fmaf(p, u, -0.33333331761166285f);
+    float r = fmaf(t * u, p, t);
+    if (red) r += 0.78539816339744831f;
+    if (ay > ax) r = 1.57079632679489662f - r;
+    if (x < 0.0f) r = 3.14159265358979324f - r;
+    return y < 0.0f ? -r : r;
+}
+
+}  // namespace dmath

@@ -7,9 +7,19 @@ using namespace gmarch;
 
 namespace {
 
-#define K1_THREADS 256   // 8 warps: 4 x 2 tiles of 8 x 4 pixels = a 32 x 8 pixel block
-#define K1_BW 32
-#define K1_BH 8
+// A CTA is K1_WX x K1_WY warps, each an 8 x 4 pixel tile. 5 x 2 warps (a 40 x 8 pixel block, 320 threads) with two
+// CTAs per SM gives every thread 96 registers (65536 / 640): the octave loop keeps all four gradient loads in flight
+// and the march state stays in registers. (256 threads x 3 CTAs = 80 registers spilled the march state into the
+// per-sample loop.)
+#ifndef K1_WX
+#define K1_WX 4
+#endif
+#ifndef K1_WY
+#define K1_WY 2
+#endif
+#define K1_THREADS (32 * K1_WX * K1_WY)
+#define K1_BW (8 * K1_WX)
+#define K1_BH (4 * K1_WY)
 #ifndef K1_MINBLOCKS
 #define K1_MINBLOCKS 3
 #endif
@@ -36,13 +46,13 @@ __device__ __forceinline__ void arm_base(const DGalaxy &g, Shared1 &s) {
     if (s.have_arm) return;
     // radius exactly as getRadius returns it: float |P| (double sqrt) / float axis.x, then the
     // reference's double expression atan(exp(-0.25/(0.5*r))/windingB)*2*windingN
-    const float radius = __fdiv_rn(v_length(s.P), g.axis_x);
+    const float radius = fdiv_nc(v_length(s.P), g.axis_x, frcp_nc(g.axis_x));
     const double r = __dadd_rn((double)radius, 0.05);
-    const double e = exp(__ddiv_rn(-0.25, __dmul_rn(0.5, r)));
-    s.Wd = __dmul_rn(__dmul_rn(atan(__ddiv_rn(e, g.winding_b)), 2.0), g.winding_n);
+    const double e = dmath::exp_nc(dmath::div_nc(-0.25, __dmul_rn(0.5, r)));
+    s.Wd = __dmul_rn(__dmul_rn(dmath::atan_nc(dmath::div_nc(e, g.winding_b)), 2.0), g.winding_n);
     s.W = (float)s.Wd;
     f3 q = g.rot_identity ? s.P : q_rotate(g.rot, s.P);
-    s.theta0 = atan2f(q.x, q.z);
+    s.theta0 = dmath::atan2f_fast(q.x, q.z);
     s.have_arm = true;
 }
 
@@ -104,8 +114,8 @@ __device__ __forceinline__ void eval_component(const DScene &sc, const DGalaxy &
     float ad = fabsf(s.dott);
     if (!(ad <= c.h_gate)) return;
     float e = fexp(ad * c.inv_z0);
-    float ch = 0.5f * (e + __frcp_rn(e));
-    float z = __frcp_rn(ch * ch);
+    float ch = 0.5f * (e + rcpa(e));
+    float z = rcpa(ch * ch);
     if (!(z > 0.01f)) return;
     // ---- radial gate: intensity > 0.001 (galaxycomponent.cpp:62-65), exact -----------------------
     bool pass;
@@ -143,7 +153,7 @@ __device__ __forceinline__ void eval_component(const DScene &sc, const DGalaxy &
     float n;
     if (is_ridged) {                    // getRidgedMf(r * scale, ks, 9, 2.5, noiseOffset, noiseTilt)
         n = gnoise::ridged(nz.lane4, __fmul_rn(r.x, c.rscale), __fmul_rn(r.y, c.rscale), __fmul_rn(r.z, c.rscale),
-                           DEV_RIDGED_OCTAVES, 2.5f, c.noise_offset, c.noise_tilt, c.rw);
+                           DEV_RIDGED_OCTAVES, 2.5f, c.noise_offset, c.noise_tilt, c.rw[0], c.rwq);
         if (COUNT) cn.octaves += DEV_RIDGED_OCTAVES;
     } else {                            // getPerlinCloudNoise / octave_noise_3d
         n = gnoise::fbm(nz.lane4, r.x, r.y, r.z, c.nscale, c.octaves, c.pers, c.inv_maxamp);
@@ -204,73 +214,115 @@ __device__ __forceinline__ void eval_component(const DScene &sc, const DGalaxy &
 template <bool COUNT>
 __device__ __forceinline__ void march(const DScene &sc, const DGalaxy &g, f3 isp1, f3 isp2, f3 camrel,
                                       const NoiseCtx &nz, float &Ir, float &Ig, float &Ib, Counts &cn) {
-    const f3 origin = isp1;
-    const f3 dseg = v_sub(isp1, isp2);
-    const double length = (double)v_length(dseg);
-    const f3 dir = v_normalized(dseg);
-    // ll = normalized(isp2 - origin) of the reference is -dir bit for bit (negation commutes with every
-    // rounding involved), so the loop test dot(p - origin, ll) < thr is evaluated as -dot(p - origin, dir) < thr.
-    const f3 orient = {g.orient[0], g.orient[1], g.orient[2]};
-    // the two clamped step states (rasterizer.cpp:449): step = 0.01 and step = minRayStep
-    const float thr_hi = __double2float_ru(__dadd_rn(length, 0.01));
-    const float thr_lo = __double2float_ru(__dadd_rn(length, sc.min_ray_step));
-    const float s_hi = __double2float_rn(0.01), s_lo = __double2float_rn(sc.min_ray_step);
-    const float w_hi = (float)(0.01 * 200.0), w_lo = (float)(sc.min_ray_step * 200.0);
-    float thr = __double2float_ru(__dadd_rn(length, sc.ray_step));     // the first test uses step = rayStep
-    // bulges of this galaxy in registers (fast path)
-    const bool fast_ok = g.fast_ok != 0;
-    float bk0 = 0.f, br0 = 0.f, bs0r = 0.f, bs0g = 0.f, bs0b = 0.f, bk1 = 0.f, br1 = 0.f, bs1r = 0.f, bs1g = 0.f, bs1b = 0.f;
-    if (g.n_bulge > 0) {
-        const DComp &c = sc.comp[g.bulge_idx[0]];
-        bk0 = c.strength * c.iscale * sc.ray_step_f; br0 = c.r0; bs0r = c.spec[0]; bs0g = c.spec[1]; bs0b = c.spec[2];
+    // The march has two kinds of samples with very different needs: off-slab samples (nine in ten in an exterior view)
+    // take ~60 instructions and want the ray geometry in registers; an in-slab sample runs the components and their noise
+    // octaves - thousands of instructions that need every register a thread has (80 at 3 CTAs/SM). ptxas does not split
+    // live ranges: a value that is live across the in-slab work and does not fit is kept in local memory for its whole
+    // life and reloaded in the per-sample loop. So the split is made by hand: the ray geometry lives in a small
+    // per-thread record; the off-slab run loop loads it when it starts, the in-slab section reads back the few
+    // values it needs, and nothing but the accumulated intensity is carried in registers between the two.
+    volatile float rec[16];
+    {
+        const f3 origin = isp1;
+        const f3 dseg = v_sub(isp1, isp2);
+        const float length_f = v_length(dseg);      // the reference's `length` is this float, widened
+        const f3 dir = v_normalized(dseg);
+        rec[0] = origin.x; rec[1] = origin.y; rec[2] = origin.z;      // p starts at origin
+        rec[3] = dir.x; rec[4] = dir.y; rec[5] = dir.z;
+        rec[6] = origin.x; rec[7] = origin.y; rec[8] = origin.z;
+        rec[9] = camrel.x; rec[10] = camrel.y; rec[11] = camrel.z;
+        rec[12] = length_f;
+        rec[13] = __double2float_ru(__dadd_rn((double)length_f, sc.ray_step));   // the first test uses step = rayStep
     }
-    if (g.n_bulge > 1) {
-        const DComp &c = sc.comp[g.bulge_idx[1]];
-        bk1 = c.strength * c.iscale * sc.ray_step_f; br1 = c.r0; bs1r = c.spec[0]; bs1g = c.spec[1]; bs1b = c.spec[2];
-    }
-    f3 p = origin;
     if (COUNT) cn.rays++;
-    while (-v_dot(v_sub(p, origin), dir) < thr) {
-        // step = clamp(|p - camera| * rayStep, minRayStep, 0.01)
-        const f3 dc = v_sub(p, camrel);
-        const float e2 = fmaf(dc.z, dc.z, fmaf(dc.y, dc.y, dc.x * dc.x));
-        float stepf, weight;
-        if (e2 > sc.est2_hi) { stepf = s_hi; weight = w_hi; thr = thr_hi; }
-        else if (e2 < sc.est2_lo) { stepf = s_lo; weight = w_lo; thr = thr_lo; }
-        else {
-            double v = __dmul_rn((double)v_length(dc), sc.ray_step);
-            v = (v < 0.01) ? v : 0.01;
-            const double step = (sc.min_ray_step < v) ? v : sc.min_ray_step;
-            stepf = __double2float_rn(step);
-            weight = (float)(step * 200.0);
-            thr = __double2float_ru(__dadd_rn(length, step));
+    const bool fast_ok = g.fast_ok != 0;
+    // The lanes that march this galaxy together stay in lockstep, one sample per iteration: the run loop is left as soon
+    // as ANY of them reaches an in-slab sample (a lane that ran ahead alone would execute its off-slab samples at a
+    // fraction of the warp's width), and a lane whose ray has ended idles until the last one is done.
+    const unsigned lanes = __activemask();
+    bool done = false;
+    for (;;) {
+        float stepf = 0.f, weight = 0.f, dott = 0.f, plen3 = 0.f;
+        bool need = false;
+        {   // ---- run of off-slab samples ---------------------------------------------------------------------
+            f3 p = {rec[0], rec[1], rec[2]};
+            const f3 dir = {rec[3], rec[4], rec[5]};
+            const f3 origin = {rec[6], rec[7], rec[8]};
+            const f3 camrel_ = {rec[9], rec[10], rec[11]};
+            const float length_f = rec[12];
+            float thr = rec[13];
+            // ll = normalized(isp2 - origin) of the reference is -dir bit for bit (negation commutes with every
+            // rounding involved), so the loop test dot(p - origin, ll) < thr is evaluated as -dot(p - origin, dir) < thr.
+            const f3 orient = {g.orient[0], g.orient[1], g.orient[2]};
+            // the two clamped step states (rasterizer.cpp:449): step = 0.01 and step = minRayStep
+            const float thr_hi = __double2float_ru(__dadd_rn((double)length_f, 0.01));
+            const float thr_lo = __double2float_ru(__dadd_rn((double)length_f, sc.min_ray_step));
+            const float s_hi = __double2float_rn(0.01), s_lo = __double2float_rn(sc.min_ray_step);
+            const float w_hi = (float)(0.01 * 200.0), w_lo = (float)(sc.min_ray_step * 200.0);
+            // bulges of this galaxy in registers
+            float bk0 = 0.f, br0 = 0.f, bs0r = 0.f, bs0g = 0.f, bs0b = 0.f, bk1 = 0.f, br1 = 0.f, bs1r = 0.f, bs1g = 0.f, bs1b = 0.f;
+            if (g.n_bulge > 0) {
+                const DComp &c = sc.comp[g.bulge_idx[0]];
+                bk0 = c.strength * c.iscale * sc.ray_step_f; br0 = c.r0; bs0r = c.spec[0]; bs0g = c.spec[1]; bs0b = c.spec[2];
+            }
+            if (g.n_bulge > 1) {
+                const DComp &c = sc.comp[g.bulge_idx[1]];
+                bk1 = c.strength * c.iscale * sc.ray_step_f; br1 = c.r0; bs1r = c.spec[0]; bs1g = c.spec[1]; bs1b = c.spec[2];
+            }
+            for (;;) {
+                if (!done) done = !(-v_dot(v_sub(p, origin), dir) < thr);
+                if (!done) {
+                    // step = clamp(|p - camera| * rayStep, minRayStep, 0.01)
+                    const f3 dc = v_sub(p, camrel_);
+                    const float e2 = fmaf(dc.z, dc.z, fmaf(dc.y, dc.y, dc.x * dc.x));
+                    if (e2 > sc.est2_hi) { stepf = s_hi; weight = w_hi; thr = thr_hi; }
+                    else if (e2 < sc.est2_lo) { stepf = s_lo; weight = w_lo; thr = thr_lo; }
+                    else {
+                        double v = __dmul_rn((double)v_length(dc), sc.ray_step);
+                        v = (v < 0.01) ? v : 0.01;
+                        const double step = (sc.min_ray_step < v) ? v : sc.min_ray_step;
+                        stepf = __double2float_rn(step);
+                        weight = (float)(step * 200.0);
+                        thr = __double2float_ru(__dadd_rn((double)length_f, step));
+                    }
+                    dott = v_dot(p, orient);                         // getRadius (galaxycomponent.h:72-76)
+                    plen3 = sqrta(fmaf(p.z, p.z, fmaf(p.y, p.y, p.x * p.x)));
+                    need = !(fast_ok && !(fabsf(dott) <= g.slab_gate));           // an in-slab sample at p
+                    if (!need) {
+                        bulge_add(bk0 * weight, br0, bs0r, bs0g, bs0b, plen3, Ir, Ig, Ib);
+                        if (g.n_bulge > 1) bulge_add(bk1 * weight, br1, bs1r, bs1g, bs1b, plen3, Ir, Ig, Ib);
+                        if (COUNT) { cn.evals += g.n_bulge; cn.samples++; cn.gates += g.comp_count + g.noop_count; }
+                        p = v_sub(p, v_mul(dir, stepf));
+                        // I only grew: the floor of the general path is the identity here (scene_build.cpp, fast_ok)
+                    }
+                }
+                if (__any_sync(lanes, need) || !__any_sync(lanes, !done)) break;
+            }
+            rec[0] = p.x; rec[1] = p.y; rec[2] = p.z;
+            rec[13] = thr;
         }
-        const float dott = v_dot(p, orient);                         // getRadius (galaxycomponent.h:72-76)
-        const float plen3 = sqrta(fmaf(p.z, p.z, fmaf(p.y, p.y, p.x * p.x)));
-        if (fast_ok && !(fabsf(dott) <= g.slab_gate)) {
-            bulge_add(bk0 * weight, br0, bs0r, bs0g, bs0b, plen3, Ir, Ig, Ib);
-            if (g.n_bulge > 1) bulge_add(bk1 * weight, br1, bs1r, bs1g, bs1b, plen3, Ir, Ig, Ib);
-            if (COUNT) cn.evals += g.n_bulge;
-            if (COUNT) { cn.samples++; cn.gates += g.comp_count + g.noop_count; }
-            p = v_sub(p, v_mul(dir, stepf));
-            continue;                 // I only grew: the floor below is the identity (scene_build.cpp, fast_ok)
-        } else {
+        if (!__any_sync(lanes, !done)) break;
+        if (need) {   // ---- one in-slab sample ------------------------------------------------------------------
+            const f3 orient = {g.orient[0], g.orient[1], g.orient[2]};
             Shared1 s;
-            s.p = p;
+            s.p = {rec[0], rec[1], rec[2]};
             s.dott = dott;
-            s.P = v_sub(p, v_mul(orient, dott));
+            s.P = v_sub(s.p, v_mul(orient, dott));
             s.Plen = sqrta(fmaf(s.P.z, s.P.z, fmaf(s.P.y, s.P.y, s.P.x * s.P.x)));
             s.plen3 = plen3;
             s.weight = weight;
             s.have_arm = false;
+            rec[14] = stepf;
 #pragma unroll 1
             for (int k = 0; k < g.comp_count; k++)
                 eval_component<COUNT>(sc, g, sc.comp[g.comp_begin + k], s, nz, Ir, Ig, Ib, cn);
+            if (COUNT) { cn.samples++; cn.gates += g.comp_count + g.noop_count; }
+            const f3 dir = {rec[3], rec[4], rec[5]};
+            const f3 p0 = {rec[0], rec[1], rec[2]};
+            const f3 pn = v_sub(p0, v_mul(dir, rec[14]));
+            rec[0] = pn.x; rec[1] = pn.y; rec[2] = pn.z;
+            Ir = fmaxf(0.0f, Ir); Ig = fmaxf(0.0f, Ig); Ib = fmaxf(0.0f, Ib);   // Util::floor (util.h:62-64)
         }
-        if (COUNT) { cn.samples++; cn.gates += g.comp_count + g.noop_count; }
-        p = v_sub(p, v_mul(dir, stepf));
-        Ir = fmaxf(0.0f, Ir); Ig = fmaxf(0.0f, Ig); Ib = fmaxf(0.0f, Ib);   // Util::floor (util.h:62-64)
-
     }
 }
 
@@ -279,7 +331,10 @@ __device__ __forceinline__ int image_row(const DScene &sc, int L) {
     return sc.y0 + L;
 }
 
-template <bool COUNT>
+// SINGLE: the frame holds one galaxy (the reference's CLI, the benchmarks, every shipped scene file): its index is a
+// compile-time 0, so every galaxy field is a constant-bank operand of the instruction that uses it - no load, no
+// register. The general kernel indexes the galaxy array at run time.
+template <bool COUNT, bool SINGLE>
 __global__ void __launch_bounds__(K1_THREADS, K1_MINBLOCKS)
 k1_march(const __grid_constant__ DScene sc, float *__restrict__ out, unsigned long long *__restrict__ counters,
          const volatile int *abort_flag, unsigned int *progress) {
@@ -288,8 +343,8 @@ k1_march(const __grid_constant__ DScene sc, float *__restrict__ out, unsigned lo
     if (*abort_flag) return;            // rasterizer.cpp:296-297: skipped pixels keep their old value
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int lx = blockIdx.x * K1_BW + (warp & 3) * 8 + (lane & 7);
-    const int ly = blockIdx.y * K1_BH + (warp >> 2) * 4 + (lane >> 3);
+    const int lx = blockIdx.x * K1_BW + (warp % K1_WX) * 8 + (lane & 7);
+    const int ly = blockIdx.y * K1_BH + (warp / K1_WX) * 4 + (lane >> 3);
     NoiseCtx nz;
     nz.lane4 = gnoise::lane_const();
     Counts cn = {0, 0, 0, 0, 0};
@@ -298,8 +353,8 @@ k1_march(const __grid_constant__ DScene sc, float *__restrict__ out, unsigned lo
         // ---- GamerCamera::coord2ray (gamercamera.cpp:210-217) --------------------------------
         const int i = sc.x0 + lx, j = image_row(sc, ly);
         const double half = __dmul_rn((double)sc.full_size, 0.5);
-        const float v0 = __double2float_rn(__dsub_rn(__ddiv_rn((double)i, half), 1.0));
-        const float v1 = __double2float_rn(-__dsub_rn(__ddiv_rn((double)j, half), 1.0));
+        const float v0 = __double2float_rn(__dsub_rn(dmath::div_nc((double)i, half), 1.0));
+        const float v1 = __double2float_rn(-__dsub_rn(dmath::div_nc((double)j, half), 1.0));
         f3 w;
         {
             const float *m = sc.inv_vp;
@@ -312,8 +367,8 @@ k1_march(const __grid_constant__ DScene sc, float *__restrict__ out, unsigned lo
         float Ir = 0.f, Ig = 0.f, Ib = 0.f;
         if (sc.flags & GAMER_FRAME_CONTINUE) { Ir = dst[0]; Ig = dst[1]; Ib = dst[2]; }   // unscaled I of the farther galaxies
         // ---- Rasterizer::renderPixel (rasterizer.cpp:379-416) --------------------------------
-        for (int gi = 0; gi < sc.n_galaxies; gi++) {
-            const DGalaxy &g = sc.gal[gi];
+        for (int gi = 0; gi < (SINGLE ? 1 : sc.n_galaxies); gi++) {
+            const DGalaxy &g = sc.gal[SINGLE ? 0 : gi];
             const f3 o = v_sub({sc.cam[0], sc.cam[1], sc.cam[2]}, {g.pos[0], g.pos[1], g.pos[2]});
             // Util::IntersectSphere (util.h:66-98)
             const f3 rD = {__fmul_rn(d.x, g.inv_axis2[0]), __fmul_rn(d.y, g.inv_axis2[1]), __fmul_rn(d.z, g.inv_axis2[2])};
@@ -323,9 +378,9 @@ k1_march(const __grid_constant__ DScene sc, float *__restrict__ out, unsigned lo
             const double C = __dsub_rn((double)v_dot(o, rO), 1.0);
             const double S = __dsub_rn(__dmul_rn(B, B), __dmul_rn(__dmul_rn(4.0, A), C));
             if (S <= 0.0) continue;
-            const double sq = __dsqrt_rn(S), twoA = __dmul_rn(2.0, A);
-            const double t0 = __ddiv_rn(__dsub_rn(-B, sq), twoA);
-            const double t1 = __ddiv_rn(__dadd_rn(-B, sq), twoA);
+            const double sq = dmath::sqrt_nc(S), twoA = __dmul_rn(2.0, A);
+            const double t0 = dmath::div_nc(__dsub_rn(-B, sq), twoA);
+            const double t1 = dmath::div_nc(__dadd_rn(-B, sq), twoA);
             f3 isp1 = v_add(o, v_mul(d, __double2float_rn(t0)));
             f3 isp2 = v_add(o, v_mul(d, __double2float_rn(t1)));
             if (t1 > 0.0) isp2 = o;
@@ -335,9 +390,10 @@ k1_march(const __grid_constant__ DScene sc, float *__restrict__ out, unsigned lo
         // rp.I * 0.01 / rayStep  (rasterizer.cpp:409): QVector3D*float then QVector3D/float
         if (sc.flags & GAMER_FRAME_PARTIAL) { dst[0] = Ir; dst[1] = Ig; dst[2] = Ib; }
         else {
-            dst[0] = __fdiv_rn(__fmul_rn(Ir, sc.final_mul), sc.ray_step_f);
-            dst[1] = __fdiv_rn(__fmul_rn(Ig, sc.final_mul), sc.ray_step_f);
-            dst[2] = __fdiv_rn(__fmul_rn(Ib, sc.final_mul), sc.ray_step_f);
+            const float rrs = frcp_nc(sc.ray_step_f);
+            dst[0] = fdiv_nc(__fmul_rn(Ir, sc.final_mul), sc.ray_step_f, rrs);
+            dst[1] = fdiv_nc(__fmul_rn(Ig, sc.final_mul), sc.ray_step_f, rrs);
+            dst[2] = fdiv_nc(__fmul_rn(Ib, sc.final_mul), sc.ray_step_f, rrs);
         }
     }
     if (COUNT) {
@@ -483,7 +539,7 @@ kp_simplex(const float *__restrict__ xyz, int n, double frequency, int32_t *__re
     L.i = su.hi - (int)((__funnelshift_l(su.lo, (uint32_t)su.hi, 7) - i7) >> 7);
     L.j = sv.hi - (int)((__funnelshift_l(sv.lo, (uint32_t)sv.hi, 7) - j7) >> 7);
     L.k = sw.hi - (int)((__funnelshift_l(sw.lo, (uint32_t)sw.hi, 7) - k7) >> 7);
-    float v = 32.0f * gnoise::simplex_cell<true>(lane4, i7, j7, k7, fu, fv, fw, &L);
+    float v = 32.0f * gnoise::simplex_cell<true>(lane4, gnoise::lane16_of(lane4), i7, j7, k7, fu, fv, fw, &L);
     if (val_out) val_out[q] = v;
     if (lat_out) {
         int32_t *o = lat_out + 10 * (size_t)q;
@@ -511,7 +567,7 @@ kp_ridged(const float *__restrict__ xyz, int n, int octaves, float lac, float of
     int q = blockIdx.x * blockDim.x + threadIdx.x;
     if (q >= n) return;
     out[q] = gnoise::ridged(gnoise::lane_const(), xyz[3 * q], xyz[3 * q + 1],
-                            xyz[3 * q + 2], octaves, lac, offset, gain, rw.w);
+                            xyz[3 * q + 2], octaves, lac, offset, gain, rw.w[0], rw.w[1] / rw.w[0]);
 }
 
 }  // namespace
@@ -521,8 +577,10 @@ namespace gk {
 
 // kernels that use the noise table need > 48 KB of dynamic shared memory: opt in once per device
 cudaError_t prepare_device() {
-    cudaError_t e = cudaFuncSetAttribute(k1_march<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GN_DYN_SMEM);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(k1_march<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GN_DYN_SMEM);
+    cudaError_t e = cudaFuncSetAttribute(k1_march<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GN_DYN_SMEM);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k1_march<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GN_DYN_SMEM);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k1_march<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GN_DYN_SMEM);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k1_march<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GN_DYN_SMEM);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(kp_simplex, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GN_DYN_SMEM);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(kp_fbm, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GN_DYN_SMEM);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(kp_ridged, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GN_DYN_SMEM);
@@ -533,8 +591,11 @@ cudaError_t launch_k1(const DScene &sc, float *out_dev, unsigned long long *coun
                       unsigned int *progress_dev, bool counted, cudaStream_t st, unsigned int *n_blocks) {
     dim3 grid((sc.width + K1_BW - 1) / K1_BW, (sc.height + K1_BH - 1) / K1_BH);
     if (n_blocks) *n_blocks = grid.x * grid.y;
-    if (counted) k1_march<true><<<grid, K1_THREADS, GN_DYN_SMEM, st>>>(sc, out_dev, counters_dev, abort_dev, progress_dev);
-    else         k1_march<false><<<grid, K1_THREADS, GN_DYN_SMEM, st>>>(sc, out_dev, counters_dev, abort_dev, progress_dev);
+    const bool single = sc.n_galaxies == 1;
+    if (counted && single)       k1_march<true, true><<<grid, K1_THREADS, GN_DYN_SMEM, st>>>(sc, out_dev, counters_dev, abort_dev, progress_dev);
+    else if (counted)            k1_march<true, false><<<grid, K1_THREADS, GN_DYN_SMEM, st>>>(sc, out_dev, counters_dev, abort_dev, progress_dev);
+    else if (single)             k1_march<false, true><<<grid, K1_THREADS, GN_DYN_SMEM, st>>>(sc, out_dev, counters_dev, abort_dev, progress_dev);
+    else                         k1_march<false, false><<<grid, K1_THREADS, GN_DYN_SMEM, st>>>(sc, out_dev, counters_dev, abort_dev, progress_dev);
     return cudaGetLastError();
 }
 

@@ -25,6 +25,9 @@
 #ifndef FBM_UNROLL
 #define FBM_UNROLL 1
 #endif
+#ifndef GN_NOISE_LINKAGE
+#define GN_NOISE_LINKAGE __noinline__
+#endif
 #define GN_PRAGMA(x) _Pragma(#x)
 #define GN_UNROLL(n) GN_PRAGMA(unroll n)
 
@@ -116,6 +119,8 @@ __device__ __forceinline__ void table_init() {
 }
 // per-lane constant of the lookup address: the lane's bank in a hash-table row
 __device__ __forceinline__ uint32_t lane_const() { return (threadIdx.x & 31u) << 2; }
+// (lane % 8) * 16: the lane's 16-byte slot in a gradient-table row
+__device__ __forceinline__ uint32_t lane16_of(uint32_t lane4) { return (lane4 << 2) & 0x70u; }
 
 // one level of the hash walk: row offset of entry ((off7 >> 7) & 255) plus this lane's slot in the row ...
 __device__ __forceinline__ uint32_t addr_of(uint32_t lane4, uint32_t off7) { return (off7 & GN_ADDR_MASK) | lane4; }
@@ -176,57 +181,120 @@ __device__ __forceinline__ void cell_of(const Skewed &s, int k, uint32_t &cell7,
     }
 }
 
-// One raw simplex value from cells (ci,cj,ck) and fractions (fu,fv,fw).  Returns 32*(n0+n1+n2+n3).
+// packed FP32 pairs (FFMA2 / FMUL2 of sm_100a): one issue slot for two lanes' worth of work. ptxas allocates the two
+// halves in adjacent registers and folds negations and immediates, so packing and unpacking cost nothing.
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pk2(float a, float b) { f32x2 r; asm("mov.b64 %0, {%1,%2};" : "=l"(r) : "f"(a), "f"(b)); return r; }
+__device__ __forceinline__ void upk2(f32x2 v, float &a, float &b) { asm("mov.b64 {%0,%1}, %2;" : "=f"(a), "=f"(b) : "l"(v)); }
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) { f32x2 r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c)); return r; }
+__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) { f32x2 r; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+
+// One raw simplex value from cells (ci,cj,ck) and fractions (fu,fv,fw).  Returns (n0+n1+n2+n3), i.e. 1/32 of the
+// reference's value. The kernel is bound by instruction issue and, inside this function, by the half-rate ALU pipe
+// (compare / select / logic / min-max: 2 cycles per warp instruction), so the code is arranged to keep work OFF it:
+//   * the six orderings of simplexnoise.cpp:267-276 are eight compare instructions whose boolean combination rides
+//     on the compare itself; the corner offsets are then PREDICATED ADDS with immediates (FMA pipe) — no selects;
+//   * the hash walk loads all four (j,k) combinations unconditionally and picks corner 1 / corner 2 by three
+//     predicated 128-bit gradient loads each (exactly one of them executes) — no address selects;
+//   * max(t, 0) is the saturation modifier of the last FMA of t (t <= 0.6 < 1, so the upper clamp never acts);
+//   * corners are processed as pairs (0,3) and (1,2) with packed FFMA2 / FMUL2.
 template <bool PROBE>
-__device__ __forceinline__ float simplex_cell(uint32_t lane4, uint32_t I7, uint32_t J7, uint32_t K7,
+__device__ __forceinline__ float simplex_cell(uint32_t lane4, uint32_t lane16, uint32_t I7, uint32_t J7, uint32_t K7,
                                               float fu, float fv, float fw, Lattice *lat) {
-    const float G3 = 1.0f / 6.0f;
-    float t = fmaf(fu + fv + fw, G3, 0.5f);      // fu,fv,fw carry a +1 bias: (sum-3)/6 + 1
+    // fu,fv,fw carry a +1 bias: t = (sum-3)/6 + 1. Multiply and add with immediates (an FMA would need 1/6 in a
+    // register, i.e. one more instruction on the ALU pipe or one more live register)
+    float t = __fadd_rn(__fmul_rn(fu + fv + fw, 1.0f / 6.0f), 0.5f);
     float x0 = fu - t, y0 = fv - t, z0 = fw - t;
-
-    // the six orderings of simplexnoise.cpp:267-276 as three comparisons
-    bool a = x0 >= y0, b = y0 >= z0, c = x0 >= z0;
-    bool i1 = a && c, j1 = !a && b, k1 = !b && !c;
-    bool i2 = a || c, j2 = !a || b, k2 = !(b && c);
-
-    const float G3m = G3 - 1.0f, G6 = 2.0f * G3, G6m = 2.0f * G3 - 1.0f;
-    float x1 = x0 + (i1 ? G3m : G3), y1 = y0 + (j1 ? G3m : G3), z1 = z0 + (k1 ? G3m : G3);
-    float x2 = x0 + (i2 ? G6m : G6), y2 = y0 + (j2 ? G6m : G6), z2 = z0 + (k2 ? G6m : G6);
-    float x3 = x0 - 0.5f, y3 = y0 - 0.5f, z3 = z0 - 0.5f;
-
+    float x1, y1, z1, x2, y2, z2;
+    Grad C0, C1, C2, C3;
     // hash walk: perm[ii+oi+perm[jj+oj+perm[kk+ok]]], offsets pre-scaled by 128. An address is the wrapped index
     // of the corner WITHOUT its +1 offsets; the offsets pick the entry at the address or the one after it.
-    const uint32_t aK = addr_of(lane4, K7);
-    const uint32_t A0 = ld0(aK), A1 = ld1(aK);
-    const uint32_t aJ0 = addr_of(lane4, A0 + J7), aJ1 = addr_of(lane4, A1 + J7);
-    const uint32_t aB1 = k1 ? aJ1 : aJ0, aB2 = k2 ? aJ1 : aJ0;
-    const uint32_t B0 = ld0(aJ0);
-    const uint32_t B1 = j1 ? ld1(aB1) : ld0(aB1);
-    const uint32_t B2 = j2 ? ld1(aB2) : ld0(aB2);
-    const uint32_t B3 = ld1(aJ1);
-    const uint32_t lane16 = (lane4 << 2) & 0x70u;      // (lane % 8) * 16: this lane's slot in a gradient row
-    const uint32_t aC1 = addr_of(lane16, B1 + I7), aC2 = addr_of(lane16, B2 + I7);
-    const Grad C0 = gd0(addr_of(lane16, B0 + I7));
-    const Grad C1 = i1 ? gd1(aC1) : gd0(aC1);
-    const Grad C2 = i2 ? gd1(aC2) : gd0(aC2);
-    const Grad C3 = gd1(addr_of(lane16, B3 + I7));
+    asm("{\n\t"
+        ".reg .pred pb, pc, i1, i2, j1, j2, k1, k2;\n\t"
+        ".reg .b32 aK, A0, A1, aJ0, aJ1, B00, B01, B10, B11, c00, c01, c10, c11;\n\t"
+        "setp.ge.f32 pc, %0, %2;\n\t"
+        "setp.ge.f32 pb, %1, %2;\n\t"
+        "setp.ge.and.f32 i1, %0, %1, pc;\n\t"
+        "setp.ge.or.f32  i2, %0, %1, pc;\n\t"
+        "setp.lt.and.f32 j1, %0, %1, pb;\n\t"
+        "setp.lt.or.f32  j2, %0, %1, pb;\n\t"
+        "setp.lt.and.f32 k1, %1, %2, !pc;\n\t"
+        "setp.lt.or.f32  k2, %1, %2, !pc;\n\t"
+        // corner offsets (simplexnoise.cpp:283-291): +G3 (-1 along the largest axis), +2*G3 (-1 along the two largest)
+        "add.f32 %3, %0, 0f3E2AAAAB;\n\t"
+        "add.f32 %4, %1, 0f3E2AAAAB;\n\t"
+        "add.f32 %5, %2, 0f3E2AAAAB;\n\t"
+        "@i1 add.f32 %3, %0, 0fBF555555;\n\t"
+        "@j1 add.f32 %4, %1, 0fBF555555;\n\t"
+        "@k1 add.f32 %5, %2, 0fBF555555;\n\t"
+        "add.f32 %6, %0, 0f3EAAAAAB;\n\t"
+        "add.f32 %7, %1, 0f3EAAAAAB;\n\t"
+        "add.f32 %8, %2, 0f3EAAAAAB;\n\t"
+        "@i2 add.f32 %6, %0, 0fBF2AAAAA;\n\t"
+        "@j2 add.f32 %7, %1, 0fBF2AAAAA;\n\t"
+        "@k2 add.f32 %8, %2, 0fBF2AAAAA;\n\t"
+        // level k
+        "lop3.b32 aK, %27, 0x7F80, %25, 0xEA;\n\t"
+        "ld.shared.u32 A0, [aK+" GN_STR(GN_HASH_IMM) "];\n\t"
+        "ld.shared.u32 A1, [aK+" GN_STR(GN_HASH_IMM) "+128];\n\t"
+        // level j: all four (j, k) offset combinations
+        "add.u32 A0, A0, %28;\n\t"
+        "add.u32 A1, A1, %28;\n\t"
+        "lop3.b32 aJ0, A0, 0x7F80, %25, 0xEA;\n\t"
+        "lop3.b32 aJ1, A1, 0x7F80, %25, 0xEA;\n\t"
+        "ld.shared.u32 B00, [aJ0+" GN_STR(GN_HASH_IMM) "];\n\t"
+        "ld.shared.u32 B10, [aJ0+" GN_STR(GN_HASH_IMM) "+128];\n\t"
+        "ld.shared.u32 B01, [aJ1+" GN_STR(GN_HASH_IMM) "];\n\t"
+        "ld.shared.u32 B11, [aJ1+" GN_STR(GN_HASH_IMM) "+128];\n\t"
+        // level i: gradient rows
+        "add.u32 B00, B00, %29;\n\t"
+        "add.u32 B10, B10, %29;\n\t"
+        "add.u32 B01, B01, %29;\n\t"
+        "add.u32 B11, B11, %29;\n\t"
+        "lop3.b32 c00, B00, 0x7F80, %26, 0xEA;\n\t"
+        "lop3.b32 c10, B10, 0x7F80, %26, 0xEA;\n\t"
+        "lop3.b32 c01, B01, 0x7F80, %26, 0xEA;\n\t"
+        "lop3.b32 c11, B11, 0x7F80, %26, 0xEA;\n\t"
+        "ld.shared.v4.b32 {%9,%10,%11,%12}, [c00+" GN_STR(GN_GRAD_IMM) "];\n\t"
+        "ld.shared.v4.b32 {%21,%22,%23,%24}, [c11+" GN_STR(GN_GRAD_IMM) "+128];\n\t"
+        "@i1 ld.shared.v4.b32 {%13,%14,%15,%16}, [c00+" GN_STR(GN_GRAD_IMM) "+128];\n\t"
+        "@j1 ld.shared.v4.b32 {%13,%14,%15,%16}, [c10+" GN_STR(GN_GRAD_IMM) "];\n\t"
+        "@k1 ld.shared.v4.b32 {%13,%14,%15,%16}, [c01+" GN_STR(GN_GRAD_IMM) "];\n\t"
+        "@!i2 ld.shared.v4.b32 {%17,%18,%19,%20}, [c11+" GN_STR(GN_GRAD_IMM) "];\n\t"
+        "@!j2 ld.shared.v4.b32 {%17,%18,%19,%20}, [c01+" GN_STR(GN_GRAD_IMM) "+128];\n\t"
+        "@!k2 ld.shared.v4.b32 {%17,%18,%19,%20}, [c10+" GN_STR(GN_GRAD_IMM) "+128];\n\t"
+        "}"
+        : "+f"(x0), "+f"(y0), "+f"(z0), "=f"(x1), "=f"(y1), "=f"(z1), "=f"(x2), "=f"(y2), "=f"(z2),
+          "=f"(C0.x), "=f"(C0.y), "=f"(C0.z), "=r"(C0.g), "=f"(C1.x), "=f"(C1.y), "=f"(C1.z), "=r"(C1.g),
+          "=f"(C2.x), "=f"(C2.y), "=f"(C2.z), "=r"(C2.g), "=f"(C3.x), "=f"(C3.y), "=f"(C3.z), "=r"(C3.g)
+        : "r"(lane4), "r"(lane16), "r"(K7), "r"(J7), "r"(I7));
+    const float x3 = x0 - 0.5f, y3 = y0 - 0.5f, z3 = z0 - 0.5f;
 
-    float t0 = fmaxf(0.6f - x0 * x0 - y0 * y0 - z0 * z0, 0.0f);
-    float t1 = fmaxf(0.6f - x1 * x1 - y1 * y1 - z1 * z1, 0.0f);
-    float t2 = fmaxf(0.6f - x2 * x2 - y2 * y2 - z2 * z2, 0.0f);
-    float t3 = fmaxf(0.6f - x3 * x3 - y3 * y3 - z3 * z3, 0.0f);
-    t0 *= t0; t1 *= t1; t2 *= t2; t3 *= t3;
-    float n = t0 * t0 * grad_dot(C0, x0, y0, z0);
-    n = fmaf(t1 * t1, grad_dot(C1, x1, y1, z1), n);
-    n = fmaf(t2 * t2, grad_dot(C2, x2, y2, z2), n);
-    n = fmaf(t3 * t3, grad_dot(C3, x3, y3, z3), n);
+    // t_c = max(0.6 - |x_c|^2, 0) for the corner pairs (0,3) and (1,2), then t^4
+    const f32x2 c06 = pk2(0.6f, 0.6f);
+    f32x2 ta = fma2(pk2(-x0, -x3), pk2(x0, x3), c06), tb = fma2(pk2(-x1, -x2), pk2(x1, x2), c06);
+    ta = fma2(pk2(-y0, -y3), pk2(y0, y3), ta);
+    tb = fma2(pk2(-y1, -y2), pk2(y1, y2), tb);
+    float t0, t1, t2, t3;
+    upk2(ta, t0, t3);
+    upk2(tb, t1, t2);
+    t0 = __saturatef(fmaf(-z0, z0, t0)); t3 = __saturatef(fmaf(-z3, z3, t3));
+    t1 = __saturatef(fmaf(-z1, z1, t1)); t2 = __saturatef(fmaf(-z2, z2, t2));
+    ta = pk2(t0, t3); tb = pk2(t1, t2);
+    ta = mul2(ta, ta); tb = mul2(tb, tb);
+    ta = mul2(ta, ta); tb = mul2(tb, tb);
+    f32x2 nn = mul2(ta, pk2(grad_dot(C0, x0, y0, z0), grad_dot(C3, x3, y3, z3)));
+    nn = fma2(tb, pk2(grad_dot(C1, x1, y1, z1), grad_dot(C2, x2, y2, z2)), nn);
+    float na, nb;
+    upk2(nn, na, nb);
 
     if (PROBE) {
-        lat->c1 = (int)i1 + 2 * (int)j1 + 4 * (int)k1;
-        lat->c2 = (int)i2 + 2 * (int)j2 + 4 * (int)k2;
+        const bool a = x0 >= y0, b = y0 >= z0, c = x0 >= z0;
+        lat->c1 = (int)(a && c) + 2 * (int)(!a && b) + 4 * (int)(!b && !c);
+        lat->c2 = (int)(a || c) + 2 * (int)(!a || b) + 4 * (int)(!(b && c));
         lat->g0 = (int)C0.g; lat->g1 = (int)C1.g; lat->g2 = (int)C2.g; lat->g3 = (int)C3.g;
     }
-    return n;        // 1/32 of the raw value: callers fold the factor into their own scale
+    return na + nb;        // 1/32 of the raw value: callers fold the factor into their own scale
 }
 
 // skewed coordinates of the point (x,y,z) (doubles), reference operation order (simplexnoise.cpp:247-251)
@@ -241,13 +309,13 @@ __device__ __forceinline__ void skew(double x, double y, double z, Skewed &su, S
 // one octave: cells/fractions of (2^k u, 2^k v, 2^k w) and the raw simplex value. QUIRK selects the
 // (almost never needed) variant that checks for the reference's fastfloor behaviour at exact integers.
 template <bool QUIRK>
-__device__ __forceinline__ float octave(uint32_t lane4, const Skewed &su, const Skewed &sv, const Skewed &sw, int k) {
+__device__ __forceinline__ float octave(uint32_t lane4, uint32_t lane16, const Skewed &su, const Skewed &sv, const Skewed &sw, int k) {
     uint32_t ci, cj, ck;
     float fu, fv, fw;
     cell_of<QUIRK>(su, k, ci, fu);
     cell_of<QUIRK>(sv, k, cj, fv);
     cell_of<QUIRK>(sw, k, ck, fw);
-    return simplex_cell<false>(lane4, ci, cj, ck, fu, fv, fw, nullptr);
+    return simplex_cell<false>(lane4, lane16, ci, cj, ck, fu, fv, fw, nullptr);
 }
 
 // can an octave k <= kmax of this point hit an exact integer in fixed point? (needs the low 32-kmax bits zero)
@@ -260,9 +328,10 @@ template <bool QUIRK>
 __device__ __forceinline__ float fbm_sum(uint32_t lane4, const Skewed &su, const Skewed &sv, const Skewed &sw,
                                          int octaves, float pers) {
     float total = 0.0f, amp = 1.0f;
+    const uint32_t lane16 = lane16_of(lane4);
 GN_UNROLL(FBM_UNROLL)
     for (int k = 0; k < octaves; k++) {
-        total = fmaf(octave<QUIRK>(lane4, su, sv, sw, k), amp, total);
+        total = fmaf(octave<QUIRK>(lane4, lane16, su, sv, sw, k), amp, total);
         amp *= pers;
     }
     return total;
@@ -276,12 +345,16 @@ __device__ __noinline__ float fbm_quirk(uint32_t lane4, double x, double y, doub
 __device__ __noinline__ float octave_quirk(uint32_t lane4, float vx, float vy, float vz) {
     Skewed su, sv, sw;
     skew((double)vx, (double)vy, (double)vz, su, sv, sw);
-    return octave<true>(lane4, su, sv, sw, 0);
+    return octave<true>(lane4, lane16_of(lane4), su, sv, sw, 0);
 }
 
 // Noise::octave_noise_3d (noise.cpp:162-180): sum_k raw(x f_k) a_k / sum a_k, f_k = scale 2^k, a_k = pers^k.
 // (px,py,pz) are the float coordinates the reference widens to double; scale is the double frequency.
-__device__ __forceinline__ float fbm(uint32_t lane4, float px, float py, float pz, double scale,
+// NOT inlined, on purpose: the call is where the register allocator splits live ranges. The octave loop wants ~45
+// registers and the march around it ~60 of the 80 a thread has (3 CTAs/SM); inlined, ptxas keeps the march state
+// in local memory for its whole life and reloads it in the per-sample loop. Out of line, what does not fit is
+// saved and restored around the call - once per noise evaluation (> 1000 instructions), never per sample.
+__device__ GN_NOISE_LINKAGE float fbm(uint32_t lane4, float px, float py, float pz, double scale,
                                      int octaves, float pers, float inv_maxamp) {
     const double x = __dmul_rn((double)px, scale), y = __dmul_rn((double)py, scale), z = __dmul_rn((double)pz, scale);
     Skewed su, sv, sw;
@@ -294,21 +367,25 @@ __device__ __forceinline__ float fbm(uint32_t lane4, float px, float py, float p
 
 // Noise::getRidgedMf (noise.cpp:81-128). v is the float QVector3D (already r*scale); it is scaled by
 // float(lacunarity) per octave exactly like `vt = vt * lacunarity`. rw[o] = pow(frequency_o, -0.05f).
-__device__ __forceinline__ float ridged(uint32_t lane4, float vx, float vy, float vz, int octaves,
-                                        float lac, float offset, float gain, const float *rw) {
-    float value = 0.0f, weight = 1.0f;
+// The spectral weights pow(frequency_o, -0.05f), frequency_o = ks * lac^o, are rw0 * (lac^-0.05)^o: a running product
+// (value arithmetic; a negative ks gives NaN either way, like the reference's pow).
+__device__ GN_NOISE_LINKAGE float ridged(uint32_t lane4, float vx, float vy, float vz, int octaves,
+                                        float lac, float offset, float gain, float rw0, float rwq) {
+    float value = 0.0f, weight = 1.0f, rw = rw0;
+    const uint32_t lane16 = lane16_of(lane4);
 #pragma unroll 1
     for (int o = 0; o < octaves; o++) {
         Skewed su, sv, sw;
         skew((double)vx, (double)vy, (double)vz, su, sv, sw);
         float signal;
         if (maybe_integer(su, sv, sw, 0)) signal = octave_quirk(lane4, vx, vy, vz);
-        else signal = octave<false>(lane4, su, sv, sw, 0);
+        else signal = octave<false>(lane4, lane16, su, sv, sw, 0);
         signal = offset - fabsf(32.0f * signal);
         signal *= signal;
         signal *= weight;
         weight = fminf(fmaxf(signal * gain, 0.0f), 1.0f);
-        value = fmaf(signal, rw[o], value);
+        value = fmaf(signal, rw, value);
+        rw *= rwq;
         vx = __fmul_rn(vx, lac); vy = __fmul_rn(vy, lac); vz = __fmul_rn(vz, lac);
     }
     return fmaf(value, 1.25f, -1.0f);

@@ -167,6 +167,7 @@ int gk_build_scene(const GamerFrame *f, const GamerGalaxy *gal, const GamerCompo
             double freq = c.ks;                                                        // noise.cpp:119-124
             const double w = -0.05f;
             for (int o = 0; o < DEV_RIDGED_OCTAVES; o++) { q.rw[o] = float(std::pow(freq, w)); freq *= 2.5; }
+            q.rwq = float(std::pow(2.5, w));
         }
         d.comp_count = nc - d.comp_begin;
         d.fast_ok = d.n_bulge <= 2;

@@ -44,7 +44,8 @@ struct DComp {
     float   rscale;          // float(cp.scale): getRidgedMf input scale (QVector3D * double)
     float   r0;
     float   spec[3];
-    float   rw[DEV_RIDGED_OCTAVES];   // pow(ks * 2.5^o, -0.05f)  (noise.cpp:119)
+    float   rw[DEV_RIDGED_OCTAVES];   // pow(ks * 2.5^o, -0.05f)  (noise.cpp:119); the kernel uses rw[0] and the ratio below
+    float   rwq;                      // pow(2.5, -0.05f): rw[o] = rw[0] * rwq^o
     int32_t octaves;         // fBm octave count of the class (10 disk/stars, 9 dust; 0 otherwise)
     double  nscale;          // fBm start frequency, as a double the way the reference forms it
     double  winding_d;       // cp.winding as the double the reference multiplies getWinding() with
