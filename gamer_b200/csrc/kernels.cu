@@ -205,14 +205,13 @@ __device__ __forceinline__ void eval_component(const DScene &sc, const DGalaxy &
     else { Ir = fmaf(k, c.spec[0], Ir); Ig = fmaf(k, c.spec[1], Ig); Ib = fmaf(k, c.spec[2], Ib); }
 }
 
-// Rasterizer::getIntensity (rasterizer.cpp:422-483) for one galaxy.
-// Control arithmetic is exact (see march.cuh). The loop test `dot(p-origin,ll) < length + step`
-// compares a float with a double; for a float d and double L, d < L  <=>  d < round_up_to_float(L),
-// so the bound is kept as a float that is refreshed only when the step length changes. Samples
-// outside every component's slab (|dott| > max h_gate: ~90 % of an exterior view) take a short path
-// that evaluates only the bulges, whose parameters sit in registers.
+// Rasterizer::getIntensity (rasterizer.cpp:422-483) for one galaxy, entered by ALL 32 lanes of the warp (`active` is
+// false for a lane outside the image or whose ray misses the ellipsoid: its ray ends before the first sample).
+// Control arithmetic is exact (see march.cuh). The loop test `dot(p-origin, ll) < length + step` compares a float with
+// a double; for a float d and double L, d < L  <=>  d < round_up_to_float(L), so the bound is kept as a float that is
+// refreshed only when the step length changes.
 template <bool COUNT>
-__device__ __forceinline__ void march(const DScene &sc, const DGalaxy &g, f3 isp1, f3 isp2, f3 camrel,
+__device__ __forceinline__ void march(const DScene &sc, const DGalaxy &g, bool active, f3 isp1, f3 isp2, f3 camrel,
                                       const NoiseCtx &nz, float &Ir, float &Ig, float &Ib, Counts &cn) {
     // The march has two kinds of samples with very different needs: off-slab samples (nine in ten in an exterior view)
     // take ~60 instructions and want the ray geometry in registers; an in-slab sample runs the components and their noise
@@ -232,18 +231,17 @@ __device__ __forceinline__ void march(const DScene &sc, const DGalaxy &g, f3 isp
         rec[6] = origin.x; rec[7] = origin.y; rec[8] = origin.z;
         rec[9] = camrel.x; rec[10] = camrel.y; rec[11] = camrel.z;
         rec[12] = length_f;
-        rec[13] = __double2float_ru(__dadd_rn((double)length_f, sc.ray_step));   // the first test uses step = rayStep
+        // the first test uses step = rayStep; a ray that is not marched has no bound at all
+        rec[13] = active ? __double2float_ru(__dadd_rn((double)length_f, sc.ray_step)) : -INFINITY;
     }
-    if (COUNT) cn.rays++;
+    if (COUNT && active) cn.rays++;
     const bool fast_ok = g.fast_ok != 0;
-    // The lanes that march this galaxy together stay in lockstep, one sample per iteration: the run loop is left as soon
-    // as ANY of them reaches an in-slab sample (a lane that ran ahead alone would execute its off-slab samples at a
-    // fraction of the warp's width), and a lane whose ray has ended idles until the last one is done.
-    const unsigned lanes = __activemask();
-    bool done = false;
+    // The 32 rays stay in lockstep, one sample per iteration: the run loop is left as soon as ANY of them reaches an
+    // in-slab sample (a lane that ran ahead alone would execute its off-slab samples at a fraction of the warp's width),
+    // and a lane whose ray has ended - its loop test stays false, p no longer moves - idles until the last one is done.
+    const unsigned FULL = 0xffffffffu;
     for (;;) {
-        float stepf = 0.f, weight = 0.f, dott = 0.f, plen3 = 0.f;
-        bool need = false;
+        bool need = false, any_alive;
         {   // ---- run of off-slab samples ---------------------------------------------------------------------
             f3 p = {rec[0], rec[1], rec[2]};
             const f3 dir = {rec[3], rec[4], rec[5]};
@@ -251,6 +249,7 @@ __device__ __forceinline__ void march(const DScene &sc, const DGalaxy &g, f3 isp
             const f3 camrel_ = {rec[9], rec[10], rec[11]};
             const float length_f = rec[12];
             float thr = rec[13];
+            float stepf = 0.f, weight = 0.f;
             // ll = normalized(isp2 - origin) of the reference is -dir bit for bit (negation commutes with every
             // rounding involved), so the loop test dot(p - origin, ll) < thr is evaluated as -dot(p - origin, dir) < thr.
             const f3 orient = {g.orient[0], g.orient[1], g.orient[2]};
@@ -270,8 +269,8 @@ __device__ __forceinline__ void march(const DScene &sc, const DGalaxy &g, f3 isp
                 bk1 = c.strength * c.iscale * sc.ray_step_f; br1 = c.r0; bs1r = c.spec[0]; bs1g = c.spec[1]; bs1b = c.spec[2];
             }
             for (;;) {
-                if (!done) done = !(-v_dot(v_sub(p, origin), dir) < thr);
-                if (!done) {
+                const bool alive = -v_dot(v_sub(p, origin), dir) < thr;
+                if (alive) {
                     // step = clamp(|p - camera| * rayStep, minRayStep, 0.01)
                     const f3 dc = v_sub(p, camrel_);
                     const float e2 = fmaf(dc.z, dc.z, fmaf(dc.y, dc.y, dc.x * dc.x));
@@ -285,10 +284,10 @@ __device__ __forceinline__ void march(const DScene &sc, const DGalaxy &g, f3 isp
                         weight = (float)(step * 200.0);
                         thr = __double2float_ru(__dadd_rn((double)length_f, step));
                     }
-                    dott = v_dot(p, orient);                         // getRadius (galaxycomponent.h:72-76)
-                    plen3 = sqrta(fmaf(p.z, p.z, fmaf(p.y, p.y, p.x * p.x)));
+                    const float dott = v_dot(p, orient);                         // getRadius (galaxycomponent.h:72-76)
                     need = !(fast_ok && !(fabsf(dott) <= g.slab_gate));           // an in-slab sample at p
                     if (!need) {
+                        const float plen3 = sqrta(fmaf(p.z, p.z, fmaf(p.y, p.y, p.x * p.x)));
                         bulge_add(bk0 * weight, br0, bs0r, bs0g, bs0b, plen3, Ir, Ig, Ib);
                         if (g.n_bulge > 1) bulge_add(bk1 * weight, br1, bs1r, bs1g, bs1b, plen3, Ir, Ig, Ib);
                         if (COUNT) { cn.evals += g.n_bulge; cn.samples++; cn.gates += g.comp_count + g.noop_count; }
@@ -296,23 +295,23 @@ __device__ __forceinline__ void march(const DScene &sc, const DGalaxy &g, f3 isp
                         // I only grew: the floor of the general path is the identity here (scene_build.cpp, fast_ok)
                     }
                 }
-                if (__any_sync(lanes, need) || !__any_sync(lanes, !done)) break;
+                any_alive = __any_sync(FULL, alive);
+                if (__any_sync(FULL, need) || !any_alive) break;
             }
             rec[0] = p.x; rec[1] = p.y; rec[2] = p.z;
-            rec[13] = thr;
+            rec[13] = thr; rec[14] = stepf; rec[15] = weight;
         }
-        if (!__any_sync(lanes, !done)) break;
+        if (!any_alive) break;
         if (need) {   // ---- one in-slab sample ------------------------------------------------------------------
             const f3 orient = {g.orient[0], g.orient[1], g.orient[2]};
             Shared1 s;
             s.p = {rec[0], rec[1], rec[2]};
-            s.dott = dott;
-            s.P = v_sub(s.p, v_mul(orient, dott));
+            s.dott = v_dot(s.p, orient);
+            s.P = v_sub(s.p, v_mul(orient, s.dott));
             s.Plen = sqrta(fmaf(s.P.z, s.P.z, fmaf(s.P.y, s.P.y, s.P.x * s.P.x)));
-            s.plen3 = plen3;
-            s.weight = weight;
+            s.plen3 = sqrta(fmaf(s.p.z, s.p.z, fmaf(s.p.y, s.p.y, s.p.x * s.p.x)));
+            s.weight = rec[15];
             s.have_arm = false;
-            rec[14] = stepf;
 #pragma unroll 1
             for (int k = 0; k < g.comp_count; k++)
                 eval_component<COUNT>(sc, g, sc.comp[g.comp_begin + k], s, nz, Ir, Ig, Ib, cn);
@@ -349,9 +348,13 @@ k1_march(const __grid_constant__ DScene sc, float *__restrict__ out, unsigned lo
     nz.lane4 = gnoise::lane_const();
     Counts cn = {0, 0, 0, 0, 0};
 
-    if (lx < sc.width && ly < sc.height) {
+    // Every lane of the warp walks the same control flow (the march keeps the 32 rays in lockstep with warp votes);
+    // a lane outside the image computes the ray of the nearest pixel inside it and marches nothing.
+    const bool inimg = lx < sc.width && ly < sc.height;
+    {
+        const int cx = min(lx, sc.width - 1), cy = min(ly, sc.height - 1);
         // ---- GamerCamera::coord2ray (gamercamera.cpp:210-217) --------------------------------
-        const int i = sc.x0 + lx, j = image_row(sc, ly);
+        const int i = sc.x0 + cx, j = image_row(sc, cy);
         const double half = __dmul_rn((double)sc.full_size, 0.5);
         const float v0 = __double2float_rn(__dsub_rn(dmath::div_nc((double)i, half), 1.0));
         const float v1 = __double2float_rn(-__dsub_rn(dmath::div_nc((double)j, half), 1.0));
@@ -363,7 +366,7 @@ k1_march(const __grid_constant__ DScene sc, float *__restrict__ out, unsigned lo
             w.z = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(v0, m[8]), __fmul_rn(v1, m[9])), m[10]), m[11]);
         }
         const f3 d = v_normalized(w);
-        float *dst = out + 3 * ((size_t)ly * sc.width + lx);
+        float *dst = out + 3 * ((size_t)cy * sc.width + cx);
         float Ir = 0.f, Ig = 0.f, Ib = 0.f;
         if (sc.flags & GAMER_FRAME_CONTINUE) { Ir = dst[0]; Ig = dst[1]; Ib = dst[2]; }   // unscaled I of the farther galaxies
         // ---- Rasterizer::renderPixel (rasterizer.cpp:379-416) --------------------------------
@@ -377,18 +380,19 @@ k1_march(const __grid_constant__ DScene sc, float *__restrict__ out, unsigned lo
             const double B = __dmul_rn(2.0, (double)v_dot(d, rO));
             const double C = __dsub_rn((double)v_dot(o, rO), 1.0);
             const double S = __dsub_rn(__dmul_rn(B, B), __dmul_rn(__dmul_rn(4.0, A), C));
-            if (S <= 0.0) continue;
-            const double sq = dmath::sqrt_nc(S), twoA = __dmul_rn(2.0, A);
+            bool hit = inimg && S > 0.0;
+            const double sq = dmath::sqrt_nc(hit ? S : 1.0), twoA = __dmul_rn(2.0, A);
             const double t0 = dmath::div_nc(__dsub_rn(-B, sq), twoA);
             const double t1 = dmath::div_nc(__dadd_rn(-B, sq), twoA);
             f3 isp1 = v_add(o, v_mul(d, __double2float_rn(t0)));
             f3 isp2 = v_add(o, v_mul(d, __double2float_rn(t1)));
             if (t1 > 0.0) isp2 = o;
-            if (t0 > 0.0 && t1 > 0.0) continue;
-            march<COUNT>(sc, g, isp1, isp2, o, nz, Ir, Ig, Ib, cn);
+            if (t0 > 0.0 && t1 > 0.0) hit = false;
+            march<COUNT>(sc, g, hit, isp1, isp2, o, nz, Ir, Ig, Ib, cn);
         }
         // rp.I * 0.01 / rayStep  (rasterizer.cpp:409): QVector3D*float then QVector3D/float
-        if (sc.flags & GAMER_FRAME_PARTIAL) { dst[0] = Ir; dst[1] = Ig; dst[2] = Ib; }
+        if (!inimg) { }
+        else if (sc.flags & GAMER_FRAME_PARTIAL) { dst[0] = Ir; dst[1] = Ig; dst[2] = Ib; }
         else {
             const float rrs = frcp_nc(sc.ray_step_f);
             dst[0] = fdiv_nc(__fmul_rn(Ir, sc.final_mul), sc.ray_step_f, rrs);
