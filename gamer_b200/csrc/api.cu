@@ -118,13 +118,13 @@ int launch_render(gamer_ctx *ctx, bool counted) {
     for (Dev &d : ctx->devs) {
         if (d.rows <= 0) continue;
         CK(cudaSetDevice(d.device));
-        CK(cudaMemsetAsync(d.progress, 0, sizeof(unsigned int), d.st));
+        CK(cudaMemsetAsync(d.progress, 0, 2 * sizeof(unsigned int), d.st));
         CK(cudaMemsetAsync(d.abort_flag, 0, sizeof(int), d.st));
         if (counted) CK(cudaMemsetAsync(d.counters, 0, GAMER_CNT_N * sizeof(unsigned long long), d.st));
         if (!(d.scene.flags & GAMER_FRAME_CONTINUE))
             CK(cudaMemsetAsync(d.rgb, 0, (size_t)d.rows * d.scene.width * 3 * sizeof(float), d.st));
         CK(cudaEventRecord(d.ev[0], d.st));
-        CK(gk::launch_k1(d.scene, d.rgb, d.counters, d.abort_flag, d.progress, counted, d.st, &d.n_blocks));
+        CK(gk::launch_k1(d.scene, d.rgb, d.counters, d.abort_flag, d.progress, counted, d.sm_count, d.st, &d.n_blocks));
         CK(cudaEventRecord(d.ev[1], d.st));
         ctx->launches += 1;
     }
@@ -242,10 +242,10 @@ int gamer_b200_create(gamer_ctx **out, const int32_t *device_ids, int32_t n_devi
         for (int k = 0; k < 4 && e == cudaSuccess; k++) e = cudaEventCreate(&d.ev[k]);
         if (e == cudaSuccess) e = cudaMalloc(&d.counters, GAMER_CNT_N * sizeof(unsigned long long));
         if (e == cudaSuccess) e = cudaMalloc(&d.abort_flag, sizeof(int));
-        if (e == cudaSuccess) e = cudaMalloc(&d.progress, sizeof(unsigned int));
+        if (e == cudaSuccess) e = cudaMalloc(&d.progress, 2 * sizeof(unsigned int));
         if (e == cudaSuccess) e = cudaHostAlloc(&d.progress_host, sizeof(unsigned int), cudaHostAllocDefault);
         if (e == cudaSuccess) e = cudaMemset(d.abort_flag, 0, sizeof(int));
-        if (e == cudaSuccess) e = cudaMemset(d.progress, 0, sizeof(unsigned int));
+        if (e == cudaSuccess) e = cudaMemset(d.progress, 0, 2 * sizeof(unsigned int));
         if (e != cudaSuccess) {
             gamer_b200_destroy(c);
             return cuda_fail(nullptr, e, "context creation");

@@ -7,26 +7,29 @@ using namespace gmarch;
 
 namespace {
 
-// A CTA is K1_WX x K1_WY warps, each an 8 x 4 pixel tile. 5 x 2 warps (a 40 x 8 pixel block, 320 threads) with two
-// CTAs per SM gives every thread 96 registers (65536 / 640): the octave loop keeps all four gradient loads in flight
-// and the march state stays in registers. (256 threads x 3 CTAs = 80 registers spilled the march state into the
-// per-sample loop.)
-#ifndef K1_WX
-#define K1_WX 4
+// ONE persistent CTA of K1_WARPS warps per SM (80 registers per thread); each warp draws 8 x 4 pixel tiles from a
+// ticket counter. The noise tables (2 x 64 KB) and the per-thread ray records (48 KB) then exist once per SM.
+// Measured: 24 x 1 = 12 x 2 warps; 10 x 2 (96 registers) and 8 x 3 are 2-3 % slower.
+#ifndef K1_WARPS
+#define K1_WARPS 24
 #endif
-#ifndef K1_WY
-#define K1_WY 2
-#endif
-#define K1_THREADS (32 * K1_WX * K1_WY)
-#define K1_BW (8 * K1_WX)
-#define K1_BH (4 * K1_WY)
+#define K1_THREADS (32 * K1_WARPS)
 #ifndef K1_MINBLOCKS
-#define K1_MINBLOCKS 3
+#define K1_MINBLOCKS 1
 #endif
 
 struct NoiseCtx {
     uint32_t lane4;
 };
+
+// The per-thread ray record of march(): K1_REC_WORDS floats per thread in shared memory behind the noise tables,
+// word k of thread t at [k][t] (conflict free). volatile: every access is a real load or store.
+#define K1_REC_WORDS 16
+struct Rec {
+    volatile float *base;
+    __device__ __forceinline__ volatile float &operator[](int k) const { return base[k * K1_THREADS]; }
+};
+#define K1_DYN_SMEM (GN_DYN_SMEM + K1_REC_WORDS * K1_THREADS * 4u)
 
 struct Shared1 {          // values of one sample shared by every component of a galaxy
     f3 p;                 // sample position (exact)
@@ -211,16 +214,16 @@ __device__ __forceinline__ void eval_component(const DScene &sc, const DGalaxy &
 // a double; for a float d and double L, d < L  <=>  d < round_up_to_float(L), so the bound is kept as a float that is
 // refreshed only when the step length changes.
 template <bool COUNT>
-__device__ __forceinline__ void march(const DScene &sc, const DGalaxy &g, bool active, f3 isp1, f3 isp2, f3 camrel,
-                                      const NoiseCtx &nz, float &Ir, float &Ig, float &Ib, Counts &cn) {
+__device__ __forceinline__ void march(const DScene &sc, const DGalaxy &g, const Rec rec, bool active, f3 isp1, f3 isp2,
+                                      f3 camrel, const NoiseCtx &nz, float &Ir, float &Ig, float &Ib, Counts &cn) {
     // The march has two kinds of samples with very different needs: off-slab samples (nine in ten in an exterior view)
     // take ~60 instructions and want the ray geometry in registers; an in-slab sample runs the components and their noise
     // octaves - thousands of instructions that need every register a thread has (80 at 3 CTAs/SM). ptxas does not split
     // live ranges: a value that is live across the in-slab work and does not fit is kept in local memory for its whole
     // life and reloaded in the per-sample loop. So the split is made by hand: the ray geometry lives in a small
-    // per-thread record; the off-slab run loop loads it when it starts, the in-slab section reads back the few
-    // values it needs, and nothing but the accumulated intensity is carried in registers between the two.
-    volatile float rec[16];
+    // per-thread record in shared memory (`rec`); the off-slab run loop loads it when it starts, the in-slab section
+    // reads back the few values it needs, and nothing but the accumulated intensity is carried in registers between
+    // the two.
     {
         const f3 origin = isp1;
         const f3 dseg = v_sub(isp1, isp2);
@@ -336,18 +339,29 @@ __device__ __forceinline__ int image_row(const DScene &sc, int L) {
 template <bool COUNT, bool SINGLE>
 __global__ void __launch_bounds__(K1_THREADS, K1_MINBLOCKS)
 k1_march(const __grid_constant__ DScene sc, float *__restrict__ out, unsigned long long *__restrict__ counters,
-         const volatile int *abort_flag, unsigned int *progress) {
+         const volatile int *abort_flag, unsigned int *progress, unsigned int n_tiles, unsigned int tiles_x) {
     gnoise::table_init();
     __syncthreads();
-    if (*abort_flag) return;            // rasterizer.cpp:296-297: skipped pixels keep their old value
 
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int lx = blockIdx.x * K1_BW + (warp % K1_WX) * 8 + (lane & 7);
-    const int ly = blockIdx.y * K1_BH + (warp / K1_WX) * 4 + (lane >> 3);
+    const int lane = threadIdx.x & 31;
     NoiseCtx nz;
     nz.lane4 = gnoise::lane_const();
     Counts cn = {0, 0, 0, 0, 0};
+    Rec rec;
+    rec.base = reinterpret_cast<volatile float *>(gnoise::gn_dyn_smem + GN_DYN_SMEM) + threadIdx.x;
 
+    // Persistent warps: the grid is one wave (K1_MINBLOCKS CTAs per SM, tables built once per CTA) and every warp draws
+    // 8 x 4 pixel tiles from a ticket counter until none is left. Tile cost varies by two orders of magnitude (sky
+    // versus the disk seen edge-on), so a fixed tile-to-CTA map left warps idle at a CTA's final barrier and SMs idle
+    // at the end of the frame. progress[0] counts finished tiles (Rasterizer::getPercentDone), progress[1] is the ticket.
+    for (;;) {
+        unsigned int tile = 0;
+        if (lane == 0) tile = atomicAdd(progress + 1, 1u);
+        tile = __shfl_sync(0xffffffffu, tile, 0);
+        if (tile >= n_tiles) break;
+        if (*abort_flag) break;             // rasterizer.cpp:296-297: skipped pixels keep their old value
+        const int lx = (int)(tile % tiles_x) * 8 + (lane & 7);
+        const int ly = (int)(tile / tiles_x) * 4 + (lane >> 3);
     // Every lane of the warp walks the same control flow (the march keeps the 32 rays in lockstep with warp votes);
     // a lane outside the image computes the ray of the nearest pixel inside it and marches nothing.
     const bool inimg = lx < sc.width && ly < sc.height;
@@ -388,7 +402,7 @@ k1_march(const __grid_constant__ DScene sc, float *__restrict__ out, unsigned lo
             f3 isp2 = v_add(o, v_mul(d, __double2float_rn(t1)));
             if (t1 > 0.0) isp2 = o;
             if (t0 > 0.0 && t1 > 0.0) hit = false;
-            march<COUNT>(sc, g, hit, isp1, isp2, o, nz, Ir, Ig, Ib, cn);
+            march<COUNT>(sc, g, rec, hit, isp1, isp2, o, nz, Ir, Ig, Ib, cn);
         }
         // rp.I * 0.01 / rayStep  (rasterizer.cpp:409): QVector3D*float then QVector3D/float
         if (!inimg) { }
@@ -400,6 +414,8 @@ k1_march(const __grid_constant__ DScene sc, float *__restrict__ out, unsigned lo
             dst[2] = fdiv_nc(__fmul_rn(Ib, sc.final_mul), sc.ray_step_f, rrs);
         }
     }
+        if (lane == 0) atomicAdd(progress, 1u);
+    }
     if (COUNT) {
         unsigned long long v[5] = {cn.rays, cn.samples, cn.gates, cn.evals, cn.octaves};
 #pragma unroll
@@ -409,8 +425,6 @@ k1_march(const __grid_constant__ DScene sc, float *__restrict__ out, unsigned lo
             if (lane == 0 && x) atomicAdd(&counters[q], x);
         }
     }
-    __syncthreads();
-    if (threadIdx.x == 0) atomicAdd(progress, 1u);
 }
 
 // ---- K2: Buffer2D::PostProcess + ToColorBuffer (buffer2d.cpp:65-85,106-126) -------------------------
@@ -581,10 +595,10 @@ namespace gk {
 
 // kernels that use the noise table need > 48 KB of dynamic shared memory: opt in once per device
 cudaError_t prepare_device() {
-    cudaError_t e = cudaFuncSetAttribute(k1_march<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GN_DYN_SMEM);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(k1_march<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GN_DYN_SMEM);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(k1_march<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GN_DYN_SMEM);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(k1_march<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GN_DYN_SMEM);
+    cudaError_t e = cudaFuncSetAttribute(k1_march<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)K1_DYN_SMEM);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k1_march<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)K1_DYN_SMEM);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k1_march<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)K1_DYN_SMEM);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k1_march<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)K1_DYN_SMEM);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(kp_simplex, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GN_DYN_SMEM);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(kp_fbm, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GN_DYN_SMEM);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(kp_ridged, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GN_DYN_SMEM);
@@ -592,14 +606,21 @@ cudaError_t prepare_device() {
 }
 
 cudaError_t launch_k1(const DScene &sc, float *out_dev, unsigned long long *counters_dev, const int *abort_dev,
-                      unsigned int *progress_dev, bool counted, cudaStream_t st, unsigned int *n_blocks) {
-    dim3 grid((sc.width + K1_BW - 1) / K1_BW, (sc.height + K1_BH - 1) / K1_BH);
-    if (n_blocks) *n_blocks = grid.x * grid.y;
+                      unsigned int *progress_dev, bool counted, int sm_count, cudaStream_t st, unsigned int *n_tiles_out) {
+    const unsigned int tiles_x = (sc.width + 7) / 8, tiles_y = (sc.height + 3) / 4, n_tiles = tiles_x * tiles_y;
+    if (n_tiles_out) *n_tiles_out = n_tiles;
+    const unsigned int warps_per_cta = K1_THREADS / 32;
+    unsigned int grid = (n_tiles + warps_per_cta - 1) / warps_per_cta;
+    const unsigned int wave = (unsigned int)sm_count * K1_MINBLOCKS;
+    if (grid > wave) grid = wave;
+    if (grid < 1) grid = 1;
     const bool single = sc.n_galaxies == 1;
-    if (counted && single)       k1_march<true, true><<<grid, K1_THREADS, GN_DYN_SMEM, st>>>(sc, out_dev, counters_dev, abort_dev, progress_dev);
-    else if (counted)            k1_march<true, false><<<grid, K1_THREADS, GN_DYN_SMEM, st>>>(sc, out_dev, counters_dev, abort_dev, progress_dev);
-    else if (single)             k1_march<false, true><<<grid, K1_THREADS, GN_DYN_SMEM, st>>>(sc, out_dev, counters_dev, abort_dev, progress_dev);
-    else                         k1_march<false, false><<<grid, K1_THREADS, GN_DYN_SMEM, st>>>(sc, out_dev, counters_dev, abort_dev, progress_dev);
+#define K1_LAUNCH(C, S) k1_march<C, S><<<grid, K1_THREADS, K1_DYN_SMEM, st>>>(sc, out_dev, counters_dev, abort_dev, progress_dev, n_tiles, tiles_x)
+    if (counted && single)       K1_LAUNCH(true, true);
+    else if (counted)            K1_LAUNCH(true, false);
+    else if (single)             K1_LAUNCH(false, true);
+    else                         K1_LAUNCH(false, false);
+#undef K1_LAUNCH
     return cudaGetLastError();
 }
 

@@ -8,7 +8,8 @@
 namespace gk {
 cudaError_t prepare_device();   // per device, before the first launch
 cudaError_t launch_k1(const DScene &sc, float *out_dev, unsigned long long *counters_dev, const int *abort_dev,
-                      unsigned int *progress_dev, bool counted, cudaStream_t st, unsigned int *n_blocks);
+                      unsigned int *progress_dev /* [0] tiles done, [1] ticket; both zeroed by the caller */, bool counted,
+                      int sm_count, cudaStream_t st, unsigned int *n_tiles);
 cudaError_t launch_k2(const float *rgb, const float *stars, uint32_t *argb, uint32_t *shadow, size_t n, double exposure,
                       double gamma, double saturation, int sm_count, cudaStream_t st);
 cudaError_t launch_k4(const GamerStar *stars, int n, float *layer, const DScene &sc, cudaStream_t st);

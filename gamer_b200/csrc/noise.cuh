@@ -12,10 +12,10 @@
 //  * In-cell offsets are the fractional parts (fu,fv,fw) in [0,1); the unskewed corner vectors
 //    follow from x0 = fu - (fu+fv+fw)/6, all FP32 on small numbers, so FP32 loses nothing even at
 //    coordinates ~1e5 where a float product would have no fractional bits left.
-//  * The permutation table lives in shared memory replicated once per bank (257 entries x 32
-//    lanes x 4 B = 32 KB): lane l only ever reads bank l, so the data-dependent hash walk is
-//    bank-conflict free.  An entry is perm[e] << 7, i.e. the value is already the byte offset of the
-//    next lookup: one IADD + one LOP3 + one LDS per level.  The last level reads a second 32 KB table
+//  * The permutation table lives in shared memory replicated once per bank (512 entries x 32
+//    lanes x 4 B = 64 KB): lane l only ever reads bank l, so the data-dependent hash walk is
+//    bank-conflict free.  An entry is perm[e & 255] << 7, i.e. the value is already the byte offset of
+//    the next lookup: one IADD + one LDS per level.  The last level reads a second 64 KB table
 //    whose rows hold the gradient vector itself (one conflict-free 128-bit load per corner).
 //  * The reference's fastfloor quirk (simplexnoise.h:130: exact non-positive integers floor one
 //    too low) is reproduced on a rare path.
@@ -49,36 +49,22 @@ __constant__ uint8_t c_perm[256] = {
     181, 199, 106, 157, 184, 84,  204, 176, 115, 121, 50,  45,  127, 4,   150, 254, 138, 236, 205, 93,
     222, 114, 67,  29,  24,  72,  243, 141, 128, 195, 78,  66,  215, 61,  156, 180};
 
-// Gradient code of g = perm % 12 for grad3 (simplexnoise.h:142-146): dot(grad3[g], (x,y,z)) = ±a ± b with
-//   g<4: (a,b)=(x,y)   4<=g<8: (x,z)   g>=8: (y,z);  sign(a) = g&1, sign(b) = (g>>1)&1.
-// ±a ± b = sa (a + (sa sb) b): bit 31 = sign(a) XOR sign(b) (flips b with one LOP3), bit 19 = sign(a) (applied to the
-// sum through a predicate), bit 17 = "a is y", bit 18 = "b is y"; bits 20..23 = g itself (probe only). The low
-// 7 bits of an entry stay ZERO: an index operand may then carry 7 garbage bits below the <<7 position (the
-// fraction bits a funnel shift brings along) without a carry into the index.
-__host__ __device__ inline uint32_t grad_code(uint32_t g) {
-    uint32_t code = (g << 20);
-    const uint32_t sa = g & 1u, sb = (g >> 1) & 1u;
-    if (sa ^ sb) code |= 0x80000000u;
-    if (sa) code |= 0x80000u;
-    if (g >= 8) code |= 0x20000u;
-    if (g < 4) code |= 0x40000u;
-    return code;
-}
-
-// 257 entries (entry 256 repeats entry 0, like perm[256] of the reference's doubled table): the "+1" of a
-// corner offset is then a +128-byte displacement AFTER the index has been wrapped, i.e. an immediate of the
-// load instead of index arithmetic.
-#define GN_TABLE_ENTRIES 257
+// 512 entries (entry e holds perm[e & 255], the reference's own doubled table, simplexnoise.h:160-185): an index
+// "cell + perm[...]" (< 511) then needs no wrap, so one level of the hash walk is ONE add - the masked cell offset
+// with the lane's slot already OR-ed in is prepared once per coordinate and octave - and a corner's "+1" is a
+// +128-byte immediate of the load.
+#define GN_TABLE_ENTRIES 512
 #define GN_TABLE_WORDS (GN_TABLE_ENTRIES * 32)
 #define GN_ADDR_MASK 0x7F80u
-// Two tables in dynamic shared memory, both with a 128-byte row per entry so that one masked index serves both:
-//   hash table      row e = 32 x u32, one per lane (lane l reads bank l only: conflict free), value perm[e] << 7
-//                   (| the gradient code above, used by the probe) — the first two levels of the hash walk;
-//   gradient table  row e = 8 x float4 (gx, gy, gz, g as bits) of grad3[perm[e] % 12], one per lane of a
+// Two tables in dynamic shared memory, both with a 128-byte row per entry:
+//   hash table      row e = 32 x u32, one per lane (lane l reads bank l only: conflict free), value perm[e & 255] << 7,
+//                   i.e. already the row offset of the next level - the first two levels of the hash walk;
+//   gradient table  row e = 8 x float4 (gx, gy, gz, g as bits) of grad3[perm[e & 255] % 12], one per lane of a
 //                   quarter warp (a 128-bit shared load is served one quarter warp at a time, and its 8 lanes
-//                   read 8 different 16-byte slots: conflict free) — the last level: ONE 128-bit load returns the
+//                   read 8 different 16-byte slots: conflict free) - the last level: ONE 128-bit load returns the
 //                   gradient itself, so the dot product is three FMA-pipe instructions instead of bit tests,
 //                   selects and sign logic on the ALU pipe (the kernel is issue/ALU bound, the LSU is not).
+// 2 x 64 KB: the ray-march kernel runs one persistent CTA of 24 warps per SM, so the tables exist once per SM.
 // Static shared memory starts at window offset 0x400 (the first KB is reserved); kernels that use the noise code
 // take GN_DYN_SMEM bytes of dynamic shared memory and no static shared memory, so the tables sit at fixed
 // window addresses and the base is an immediate of the load. table_init() verifies the base and traps otherwise.
@@ -88,7 +74,7 @@ __host__ __device__ inline uint32_t grad_code(uint32_t g) {
 #define GN_DYN_SMEM (2u * GN_TABLE_WORDS * 4u)
 // the same two addresses as plain decimal literals for the inline PTX (checked below)
 #define GN_HASH_IMM 1024
-#define GN_GRAD_IMM 33920
+#define GN_GRAD_IMM 66560
 #define GN_STR2(x) #x
 #define GN_STR(x) GN_STR2(x)
 static_assert(GN_HASH_IMM == GN_HASH_ADDR && GN_GRAD_IMM == GN_GRAD_ADDR, "PTX immediates out of step with the table layout");
@@ -110,7 +96,7 @@ __device__ __forceinline__ void table_init() {
     uint32_t *grd = tbl + GN_TABLE_WORDS;
     for (uint32_t w = threadIdx.x + threadIdx.y * blockDim.x; w < GN_TABLE_WORDS; w += blockDim.x * blockDim.y) {
         const uint32_t p = c_perm[(w >> 5) & 255u], g = p % 12u;
-        tbl[w] = (p << 7) | grad_code(g);
+        tbl[w] = p << 7;
         float gx, gy, gz;
         grad3_of(g, gx, gy, gz);
         const uint32_t c = w & 3u;
@@ -122,23 +108,8 @@ __device__ __forceinline__ uint32_t lane_const() { return (threadIdx.x & 31u) <<
 // (lane % 8) * 16: the lane's 16-byte slot in a gradient-table row
 __device__ __forceinline__ uint32_t lane16_of(uint32_t lane4) { return (lane4 << 2) & 0x70u; }
 
-// one level of the hash walk: row offset of entry ((off7 >> 7) & 255) plus this lane's slot in the row ...
-__device__ __forceinline__ uint32_t addr_of(uint32_t lane4, uint32_t off7) { return (off7 & GN_ADDR_MASK) | lane4; }
-// ... and the hash entry at that address, or the one after it
-__device__ __forceinline__ uint32_t ld0(uint32_t a) {
-    uint32_t v; asm("ld.shared.u32 %0, [%1+" GN_STR(GN_HASH_IMM) "];" : "=r"(v) : "r"(a)); return v;
-}
-__device__ __forceinline__ uint32_t ld1(uint32_t a) {
-    uint32_t v; asm("ld.shared.u32 %0, [%1+" GN_STR(GN_HASH_IMM) "+128];" : "=r"(v) : "r"(a)); return v;
-}
-// ... or the gradient at that address / the one after it (address built with the lane's 16-byte slot)
+// a gradient-table entry: grad3[perm % 12] and the index itself (read by the probes only)
 struct Grad { float x, y, z; uint32_t g; };
-__device__ __forceinline__ Grad gd0(uint32_t a) {
-    Grad v; asm("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4+" GN_STR(GN_GRAD_IMM) "];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=r"(v.g) : "r"(a)); return v;
-}
-__device__ __forceinline__ Grad gd1(uint32_t a) {
-    Grad v; asm("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4+" GN_STR(GN_GRAD_IMM) "+128];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=r"(v.g) : "r"(a)); return v;
-}
 __device__ __forceinline__ float grad_dot(const Grad &e, float x, float y, float z) {
     return fmaf(e.z, z, fmaf(e.y, y, e.x * x));
 }
@@ -237,24 +208,18 @@ __device__ __forceinline__ float simplex_cell(uint32_t lane4, uint32_t lane16, u
         "lop3.b32 aK, %27, 0x7F80, %25, 0xEA;\n\t"
         "ld.shared.u32 A0, [aK+" GN_STR(GN_HASH_IMM) "];\n\t"
         "ld.shared.u32 A1, [aK+" GN_STR(GN_HASH_IMM) "+128];\n\t"
-        // level j: all four (j, k) offset combinations
-        "add.u32 A0, A0, %28;\n\t"
-        "add.u32 A1, A1, %28;\n\t"
-        "lop3.b32 aJ0, A0, 0x7F80, %25, 0xEA;\n\t"
-        "lop3.b32 aJ1, A1, 0x7F80, %25, 0xEA;\n\t"
+        // level j: all four (j, k) offset combinations; %28 = masked j cell offset | lane slot
+        "add.u32 aJ0, A0, %28;\n\t"
+        "add.u32 aJ1, A1, %28;\n\t"
         "ld.shared.u32 B00, [aJ0+" GN_STR(GN_HASH_IMM) "];\n\t"
         "ld.shared.u32 B10, [aJ0+" GN_STR(GN_HASH_IMM) "+128];\n\t"
         "ld.shared.u32 B01, [aJ1+" GN_STR(GN_HASH_IMM) "];\n\t"
         "ld.shared.u32 B11, [aJ1+" GN_STR(GN_HASH_IMM) "+128];\n\t"
-        // level i: gradient rows
-        "add.u32 B00, B00, %29;\n\t"
-        "add.u32 B10, B10, %29;\n\t"
-        "add.u32 B01, B01, %29;\n\t"
-        "add.u32 B11, B11, %29;\n\t"
-        "lop3.b32 c00, B00, 0x7F80, %26, 0xEA;\n\t"
-        "lop3.b32 c10, B10, 0x7F80, %26, 0xEA;\n\t"
-        "lop3.b32 c01, B01, 0x7F80, %26, 0xEA;\n\t"
-        "lop3.b32 c11, B11, 0x7F80, %26, 0xEA;\n\t"
+        // level i: gradient rows; %29 = masked i cell offset | 16-byte lane slot
+        "add.u32 c00, B00, %29;\n\t"
+        "add.u32 c10, B10, %29;\n\t"
+        "add.u32 c01, B01, %29;\n\t"
+        "add.u32 c11, B11, %29;\n\t"
         "ld.shared.v4.b32 {%9,%10,%11,%12}, [c00+" GN_STR(GN_GRAD_IMM) "];\n\t"
         "ld.shared.v4.b32 {%21,%22,%23,%24}, [c11+" GN_STR(GN_GRAD_IMM) "+128];\n\t"
         "@i1 ld.shared.v4.b32 {%13,%14,%15,%16}, [c00+" GN_STR(GN_GRAD_IMM) "+128];\n\t"
@@ -267,7 +232,7 @@ __device__ __forceinline__ float simplex_cell(uint32_t lane4, uint32_t lane16, u
         : "+f"(x0), "+f"(y0), "+f"(z0), "=f"(x1), "=f"(y1), "=f"(z1), "=f"(x2), "=f"(y2), "=f"(z2),
           "=f"(C0.x), "=f"(C0.y), "=f"(C0.z), "=r"(C0.g), "=f"(C1.x), "=f"(C1.y), "=f"(C1.z), "=r"(C1.g),
           "=f"(C2.x), "=f"(C2.y), "=f"(C2.z), "=r"(C2.g), "=f"(C3.x), "=f"(C3.y), "=f"(C3.z), "=r"(C3.g)
-        : "r"(lane4), "r"(lane16), "r"(K7), "r"(J7), "r"(I7));
+        : "r"(lane4), "r"(lane16), "r"(K7), "r"((J7 & GN_ADDR_MASK) | lane4), "r"((I7 & GN_ADDR_MASK) | lane16));
     const float x3 = x0 - 0.5f, y3 = y0 - 0.5f, z3 = z0 - 0.5f;
 
     // t_c = max(0.6 - |x_c|^2, 0) for the corner pairs (0,3) and (1,2), then t^4
