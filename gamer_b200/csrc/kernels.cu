@@ -33,30 +33,25 @@ struct Rec {
 
 struct Shared1 {          // values of one sample shared by every component of a galaxy
     f3 p;                 // sample position (exact)
-    f3 P;                 // in-plane part (exact)
     float dott;           // height above the plane along the axis (exact)
     float Plen;           // |P| fast float
-    float plen3;          // |p| fast float
     float weight;         // step * 200
-    bool have_arm;        // lazily computed per sample
     float W;              // getWinding(radius), narrowed
     double Wd;            // getWinding(radius) in double: it feeds the twirl angle
     float theta0;         // atan2(q.x, q.z), q = rotmat * P
 };
 
 // getWinding (galaxycomponent.h:156-165) and the atan2 of getTheta (:150-153), once per sample
-__device__ __forceinline__ void arm_base(const DGalaxy &g, Shared1 &s) {
-    if (s.have_arm) return;
+__device__ __forceinline__ void arm_base(const DGalaxy &g, Shared1 &s, f3 P) {
     // radius exactly as getRadius returns it: float |P| (double sqrt) / float axis.x, then the
     // reference's double expression atan(exp(-0.25/(0.5*r))/windingB)*2*windingN
-    const float radius = fdiv_nc(v_length(s.P), g.axis_x, frcp_nc(g.axis_x));
+    const float radius = fdiv_nc(v_length(P), g.axis_x, frcp_nc(g.axis_x));
     const double r = __dadd_rn((double)radius, 0.05);
     const double e = dmath::exp_nc(dmath::div_nc(-0.25, __dmul_rn(0.5, r)));
     s.Wd = __dmul_rn(__dmul_rn(dmath::atan_nc(dmath::div_nc(e, g.winding_b)), 2.0), g.winding_n);
     s.W = (float)s.Wd;
-    f3 q = g.rot_identity ? s.P : q_rotate(g.rot, s.P);
+    f3 q = g.rot_identity ? P : q_rotate(g.rot, P);
     s.theta0 = dmath::atan2f_fast(q.x, q.z);
-    s.have_arm = true;
 }
 
 // findDifference (galaxycomponent.h:103-118) with M_PI = 3.14159265 (util.h:20)
@@ -109,7 +104,8 @@ __device__ __forceinline__ void eval_component(const DScene &sc, const DGalaxy &
                                                const NoiseCtx &nz, float &Ir, float &Ig, float &Ib, Counts &cn) {
     const float rs = sc.ray_step_f;
     if (c.cls == GAMER_CLASS_BULGE) {   // galaxycomponents.cpp:5-25 — evaluated at every sample, no gates
-        bulge_add(c.strength * c.iscale * rs * s.weight, c.r0, c.spec[0], c.spec[1], c.spec[2], s.plen3, Ir, Ig, Ib);
+        bulge_add(c.strength * c.iscale * rs * s.weight, c.r0, c.spec[0], c.spec[1], c.spec[2],
+                  sqrta(fmaf(s.p.z, s.p.z, fmaf(s.p.y, s.p.y, s.p.x * s.p.x))), Ir, Ig, Ib);
         if (COUNT) cn.evals++;
         return;
     }
@@ -124,7 +120,10 @@ __device__ __forceinline__ void eval_component(const DScene &sc, const DGalaxy &
     bool pass;
     if (s.Plen < c.plen_lo) pass = true;
     else if (s.Plen > c.plen_hi) pass = false;
-    else pass = v_length(s.P) <= c.plen_thr;
+    else {      // rare: inside the band where only the exact |P| decides; P = p - orient * dott like getRadius
+        const f3 orient = {g.orient[0], g.orient[1], g.orient[2]};
+        pass = v_length(v_sub(s.p, v_mul(orient, s.dott))) <= c.plen_thr;
+    }
     if (!pass) return;
     float intensity = fminf(fmaxf(ex2(s.Plen * c.k_radial) - 0.01f, 0.0f), 0.1f);
     float scale = 1.0f;
@@ -137,7 +136,6 @@ __device__ __forceinline__ void eval_component(const DScene &sc, const DGalaxy &
     float armv = 1.0f;
     double winding = 0.0;
     if (c.flags & DC_HAS_ARM) {
-        arm_base(g, s);
         armv = arm_value(g, c, s);
         if (c.flags & DC_HAS_WINDING) winding = __dmul_rn(s.Wd, c.winding_d);
     }
@@ -310,11 +308,12 @@ __device__ __forceinline__ void march(const DScene &sc, const DGalaxy &g, const 
             Shared1 s;
             s.p = {rec[0], rec[1], rec[2]};
             s.dott = v_dot(s.p, orient);
-            s.P = v_sub(s.p, v_mul(orient, s.dott));
-            s.Plen = sqrta(fmaf(s.P.z, s.P.z, fmaf(s.P.y, s.P.y, s.P.x * s.P.x)));
-            s.plen3 = sqrta(fmaf(s.p.z, s.p.z, fmaf(s.p.y, s.p.y, s.p.x * s.p.x)));
+            const f3 P = v_sub(s.p, v_mul(orient, s.dott));
+            s.Plen = sqrta(fmaf(P.z, P.z, fmaf(P.y, P.y, P.x * P.x)));
             s.weight = rec[15];
-            s.have_arm = false;
+            // getWinding / getTheta once per sample, up front: a lazily set flag would have to live (in local memory)
+            // across every noise call of the sample
+            if (g.any_arm) arm_base(g, s, P);
 #pragma unroll 1
             for (int k = 0; k < g.comp_count; k++)
                 eval_component<COUNT>(sc, g, sc.comp[g.comp_begin + k], s, nz, Ir, Ig, Ib, cn);

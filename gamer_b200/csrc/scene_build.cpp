@@ -94,6 +94,7 @@ int gk_build_scene(const GamerFrame *f, const GamerGalaxy *gal, const GamerCompo
         d.no_arms = (g.no_arms == 1) ? 1 : (g.no_arms == 2) ? 2 : (g.no_arms == 3) ? 3 : 4;
         d.comp_begin = nc;
         d.slab_gate = -1.0f;
+        d.any_arm = 0;
         d.n_bulge = 0;
         for (int k = 0; k < g.comp_count; k++) {
             const GamerComponent &c = comp[g.comp_begin + k];
@@ -104,7 +105,7 @@ int gk_build_scene(const GamerFrame *f, const GamerGalaxy *gal, const GamerCompo
             DComp &q = s.comp[nc++];
             q.cls = c.class_id;
             q.flags = 0;
-            if (c.arm != 0) q.flags |= DC_HAS_ARM;
+            if (c.arm != 0) { q.flags |= DC_HAS_ARM; d.any_arm = 1; }
             if (c.winding != 0) q.flags |= DC_HAS_WINDING;
             if (c.noise_offset != 0) q.flags |= DC_HAS_NOFF;
             const double inner = 1.0f * c.inner;

@@ -70,7 +70,7 @@ struct DGalaxy {
     int32_t fast_ok;                  // n_bulge <= 2: off-slab samples may take the bulge-only path
     float   slab_gate;                // max h_gate over the non-bulge components (-1 if none)
     int32_t noop_count;               // active "stars small" components: visited by the reference, no-op here
-    int32_t _pad;
+    int32_t any_arm;                  // some active component has arm != 0 (getWinding / getTheta are then needed)
     double  winding_b, winding_n;     // getWinding is evaluated in double (its result feeds the twirl angle)
 };
 
