@@ -213,3 +213,42 @@ def test_oracle_fbm_and_ridged_equal_reference_class_golden(oracle):
         q = np.ascontiguousarray(pts * np.float32(scale))
         # a negative frequency (ks < 0) makes pow(frequency, -0.05) NaN in the reference too: compared as equal NaNs
         assert np.array_equal(oracle.ridged(q, float(fr), int(oc), float(lac), float(off), float(gain)), ref, equal_nan=True), (fr, off, gain, scale)
+
+
+def test_dmath_host_build_matches_libm(tmp_path):
+    """csrc/dmath.cuh (the call-free FP64 exp / atan / sincos and the fast atan2f of K1) compiled for the host and
+    compared with libm over the argument ranges the kernel uses: <= 1 ulp in double, identical once narrowed to float
+    (which is all the reference consumes: the winding angle and the twirl quaternion)."""
+    import subprocess
+    src = tmp_path / "dm.cpp"
+    hdr = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "gamer_b200", "csrc", "dmath.cuh")
+    src.write_text(r'''
+#include "%s"
+#include <cstdio>
+#include <cstdlib>
+#include <cmath>
+static double ulps(double a, double b) { if (a == b) return 0; double u = std::fabs(std::nextafter(b, INFINITY) - b); return std::fabs(a - b) / u; }
+int main() {
+    srand(1);
+    double me = 0, ma = 0, ms = 0; float mf = 0; long mism = 0;
+    for (long i = 0; i < 1000000; i++) {
+        double u = rand() / (double)RAND_MAX;
+        double x = -12.0 * u, e = dmath::exp_nc(x), er = exp(x);
+        me = fmax(me, ulps(e, er)); mism += ((float)e != (float)er);
+        double y = 6.0 * u * u * (i & 1 ? 1 : -1), a = dmath::atan_nc(y), ar = atan(y);
+        ma = fmax(ma, ulps(a, ar)); mism += ((float)a != (float)ar);
+        double an = (float)(600.0 * (u - 0.5)), s, c; dmath::sincos_nc(an, s, c);
+        ms = fmax(ms, fmax(std::fabs(s - sin(an)), std::fabs(c - cos(an))));
+        mism += ((float)s != (float)sin(an)) + ((float)c != (float)cos(an));
+        float fy = (float)(2 * (rand() / (double)RAND_MAX) - 1), fx = (float)(2 * (rand() / (double)RAND_MAX) - 1);
+        mf = fmaxf(mf, fabsf(dmath::atan2f_fast(fy, fx) - (float)atan2((double)fy, (double)fx)));
+    }
+    printf("%%.4f %%.4f %%.3g %%.3g %%ld\n", me, ma, ms, (double)mf, mism);
+}
+''' % hdr)
+    exe = tmp_path / "dm"
+    subprocess.run(["g++", "-O2", "-ffp-contract=off", "-o", str(exe), str(src)], check=True)
+    me, ma, ms, mf, mism = subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.split()
+    assert float(me) <= 1.0 and float(ma) <= 1.0, (me, ma)
+    assert float(ms) <= 3e-16 and float(mf) <= 5e-7, (ms, mf)
+    assert int(mism) == 0
