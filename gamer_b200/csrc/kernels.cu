@@ -24,7 +24,7 @@ struct NoiseCtx {
 
 // The per-thread ray record of march(): K1_REC_WORDS floats per thread in shared memory behind the noise tables,
 // word k of thread t at [k][t] (conflict free). volatile: every access is a real load or store.
-#define K1_REC_WORDS 16
+#define K1_REC_WORDS 17
 struct Rec {
     volatile float *base;
     __device__ __forceinline__ volatile float &operator[](int k) const { return base[k * K1_THREADS]; }
@@ -232,6 +232,7 @@ __device__ __forceinline__ void march(const DScene &sc, const DGalaxy &g, const 
         rec[6] = origin.x; rec[7] = origin.y; rec[8] = origin.z;
         rec[9] = camrel.x; rec[10] = camrel.y; rec[11] = camrel.z;
         rec[12] = length_f;
+        rec[16] = active ? 0.0f : INFINITY;            // distance marched so far (estimate, see the run loop)
         // the first test uses step = rayStep; a ray that is not marched has no bound at all
         rec[13] = active ? __double2float_ru(__dadd_rn((double)length_f, sc.ray_step)) : -INFINITY;
     }
@@ -250,6 +251,11 @@ __device__ __forceinline__ void march(const DScene &sc, const DGalaxy &g, const 
             const f3 camrel_ = {rec[9], rec[10], rec[11]};
             const float length_f = rec[12];
             float thr = rec[13];
+            // The exact loop test costs ten instructions and decides only at the very end of a ray: d = -dot(p - origin,
+            // dir) differs from the running sum of the steps by rounding alone (bounded by sc.alive_margin, scene_build.cpp),
+            // so while that sum stays below length - margin the ray is certainly alive (the bound is length + step).
+            float marched = rec[16];
+            const float sure_below = length_f - sc.alive_margin;
             float stepf = 0.f, weight = 0.f;
             // ll = normalized(isp2 - origin) of the reference is -dir bit for bit (negation commutes with every
             // rounding involved), so the loop test dot(p - origin, ll) < thr is evaluated as -dot(p - origin, dir) < thr.
@@ -270,7 +276,7 @@ __device__ __forceinline__ void march(const DScene &sc, const DGalaxy &g, const 
                 bk1 = c.strength * c.iscale * sc.ray_step_f; br1 = c.r0; bs1r = c.spec[0]; bs1g = c.spec[1]; bs1b = c.spec[2];
             }
             for (;;) {
-                const bool alive = -v_dot(v_sub(p, origin), dir) < thr;
+                const bool alive = marched < sure_below || -v_dot(v_sub(p, origin), dir) < thr;
                 if (alive) {
                     // step = clamp(|p - camera| * rayStep, minRayStep, 0.01)
                     const f3 dc = v_sub(p, camrel_);
@@ -278,12 +284,16 @@ __device__ __forceinline__ void march(const DScene &sc, const DGalaxy &g, const 
                     if (e2 > sc.est2_hi) { stepf = s_hi; weight = w_hi; thr = thr_hi; }
                     else if (e2 < sc.est2_lo) { stepf = s_lo; weight = w_lo; thr = thr_lo; }
                     else {
-                        double v = __dmul_rn((double)v_length(dc), sc.ray_step);
-                        v = (v < 0.01) ? v : 0.01;
-                        const double step = (sc.min_ray_step < v) ? v : sc.min_ray_step;
-                        stepf = __double2float_rn(step);
-                        weight = (float)(step * 200.0);
-                        thr = __double2float_ru(__dadd_rn((double)length_f, step));
+                        // the clamps as exact float thresholds on the length (scene_build.cpp), FP64 only in between
+                        const float len_f = v_length(dc);
+                        if (len_f > sc.len_hi_thr) { stepf = s_hi; weight = w_hi; thr = thr_hi; }
+                        else if (len_f <= sc.len_lo_thr) { stepf = s_lo; weight = w_lo; thr = thr_lo; }
+                        else {
+                            const double step = __dmul_rn((double)len_f, sc.ray_step);
+                            stepf = __double2float_rn(step);
+                            weight = (float)__dmul_rn(step, 200.0);
+                            thr = __double2float_ru(__dadd_rn((double)length_f, step));
+                        }
                     }
                     const float dott = v_dot(p, orient);                         // getRadius (galaxycomponent.h:72-76)
                     need = !(fast_ok && !(fabsf(dott) <= g.slab_gate));           // an in-slab sample at p
@@ -293,6 +303,7 @@ __device__ __forceinline__ void march(const DScene &sc, const DGalaxy &g, const 
                         if (g.n_bulge > 1) bulge_add(bk1 * weight, br1, bs1r, bs1g, bs1b, plen3, Ir, Ig, Ib);
                         if (COUNT) { cn.evals += g.n_bulge; cn.samples++; cn.gates += g.comp_count + g.noop_count; }
                         p = v_sub(p, v_mul(dir, stepf));
+                        marched += stepf;
                         // I only grew: the floor of the general path is the identity here (scene_build.cpp, fast_ok)
                     }
                 }
@@ -300,7 +311,7 @@ __device__ __forceinline__ void march(const DScene &sc, const DGalaxy &g, const 
                 if (__any_sync(FULL, need) || !any_alive) break;
             }
             rec[0] = p.x; rec[1] = p.y; rec[2] = p.z;
-            rec[13] = thr; rec[14] = stepf; rec[15] = weight;
+            rec[13] = thr; rec[14] = stepf; rec[15] = weight; rec[16] = marched;
         }
         if (!any_alive) break;
         if (need) {   // ---- one in-slab sample ------------------------------------------------------------------
@@ -320,7 +331,9 @@ __device__ __forceinline__ void march(const DScene &sc, const DGalaxy &g, const 
             if (COUNT) { cn.samples++; cn.gates += g.comp_count + g.noop_count; }
             const f3 dir = {rec[3], rec[4], rec[5]};
             const f3 p0 = {rec[0], rec[1], rec[2]};
-            const f3 pn = v_sub(p0, v_mul(dir, rec[14]));
+            const float stepf = rec[14];
+            const f3 pn = v_sub(p0, v_mul(dir, stepf));
+            rec[16] = rec[16] + stepf;
             rec[0] = pn.x; rec[1] = pn.y; rec[2] = pn.z;
             Ir = fmaxf(0.0f, Ir); Ig = fmaxf(0.0f, Ig); Ib = fmaxf(0.0f, Ib);   // Util::floor (util.h:62-64)
         }

@@ -69,6 +69,24 @@ int gk_build_scene(const GamerFrame *f, const GamerGalaxy *gal, const GamerCompo
         double hi = 0.01 * (1.0 + 2e-5) / f->ray_step, lo = f->min_ray_step * (1.0 - 2e-5) / f->ray_step;
         s.est2_hi = float(hi * hi * (1.0 + 1e-6));
         s.est2_lo = float(lo * lo * (1.0 - 1e-6));
+        // the same decision made exactly, on the float length the reference multiplies (rasterizer.cpp:449)
+        const double rs = f->ray_step, mn = f->min_ray_step;
+        auto step_of = [&](float L) { return ref_clamp(double(L) * rs, mn, 0.01); };
+        const double step_hi = ref_clamp(0.01, mn, 0.01), step_lo = step_of(0.0f);
+        s.len_hi_thr = largest_passing([&](float L) { return step_of(L) < step_hi; });
+        s.len_lo_thr = largest_passing([&](float L) { return step_of(L) <= step_lo; });
+        // Rounding bound for the cheap "certainly alive" test of the run loop. A march inside the unit-scale scene
+        // (|p| < 4, length < 8) takes at most 8 / minRayStep samples; each adds at most 3 half-ulps of p's components
+        // (2.4e-7 each at |p| < 4) to the position and one half-ulp of the running sum (< 8: 4.8e-7) to the sum.
+        // 4e-6 / minRayStep covers both with a factor 2 to spare; 0.004 covers the normalisation of dir and the
+        // first step. Scenes outside that scale, or without a lower step bound, always take the exact test.
+        {
+            bool unit_scale = mn > 0;
+            for (int gi = 0; gi < f->n_galaxies; gi++)
+                for (int i = 0; i < 3; i++)
+                    if (!(std::fabs(gal[gi].axis[i]) <= 2.0f) || !(std::fabs(gal[gi].pos[i] - f->cam[i]) <= 2.0f)) unit_scale = false;
+            s.alive_margin = unit_scale ? float(0.004 + 4e-6 / mn) : std::numeric_limits<float>::infinity();
+        }
     }
 
     int nc = 0;

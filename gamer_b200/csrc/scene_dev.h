@@ -86,7 +86,9 @@ struct DScene {
     double  min_ray_step;
     float   final_mul;       // float(0.01)
     float   est2_hi, est2_lo; // |p-cam|^2 above / below which the step is certainly clamped to 0.01 / minRayStep
-    float   _pad;
+    float   len_hi_thr;      // exact: the step is the upper clamp iff |p-cam| (float, as QVector3D::length) > len_hi_thr
+    float   len_lo_thr;      // exact: ... the lower clamp iff |p-cam| <= len_lo_thr (tested second)
+    float   alive_margin;    // bound on |(-dot(p - origin, dir)) - sum of steps| over a whole march (+inf: always test exactly)
     DGalaxy gal[DEV_MAX_GALAXIES];
     DComp   comp[DEV_MAX_COMPONENTS];
 };
