@@ -191,8 +191,8 @@ def port_value(arm: "CpuArm"):
 
 # dram__bytes_read.sum + dram__bytes_write.sum of one k1_march launch, from the `ncu --set full` capture
 # summarised in profiles/r01_k1_ncu_summary.csv (the 50 MB framebuffer is still in the 126 MB L2 when the
-# kernel ends, so DRAM sees ~12 MB; the algorithmic bytes are 12 B/pixel = 50 MB)
-K1_DRAM_TRAFFIC = {"spiral_2048_oblique_orbit": 1660160 + 10038528}
+# kernel ends, so DRAM sees ~8 MB; the algorithmic bytes are 12 B/pixel = 50 MB)
+K1_DRAM_TRAFFIC = {"spiral_2048_oblique_orbit": 407040 + 7358976}
 
 
 def run_ours(args):

@@ -216,7 +216,7 @@ __device__ __forceinline__ void march(const DScene &sc, const DGalaxy &g, const 
                                       f3 camrel, const NoiseCtx &nz, float &Ir, float &Ig, float &Ib, Counts &cn) {
     // The march has two kinds of samples with very different needs: off-slab samples (nine in ten in an exterior view)
     // take ~60 instructions and want the ray geometry in registers; an in-slab sample runs the components and their noise
-    // octaves - thousands of instructions that need every register a thread has (80 at 3 CTAs/SM). ptxas does not split
+    // octaves - thousands of instructions that need every register a thread has (80 at 24 warps per SM). ptxas does not split
     // live ranges: a value that is live across the in-slab work and does not fit is kept in local memory for its whole
     // life and reloaded in the per-sample loop. So the split is made by hand: the ray geometry lives in a small
     // per-thread record in shared memory (`rec`); the off-slab run loop loads it when it starts, the in-slab section

@@ -316,7 +316,7 @@ __device__ __noinline__ float octave_quirk(uint32_t lane4, float vx, float vy, f
 // Noise::octave_noise_3d (noise.cpp:162-180): sum_k raw(x f_k) a_k / sum a_k, f_k = scale 2^k, a_k = pers^k.
 // (px,py,pz) are the float coordinates the reference widens to double; scale is the double frequency.
 // NOT inlined, on purpose: the call is where the register allocator splits live ranges. The octave loop wants ~45
-// registers and the march around it ~60 of the 80 a thread has (3 CTAs/SM); inlined, ptxas keeps the march state
+// registers and the march around it ~60 of the 80 a thread has (24 warps per SM); inlined, ptxas keeps the march state
 // in local memory for its whole life and reloads it in the per-sample loop. Out of line, what does not fit is
 // saved and restored around the call - once per noise evaluation (> 1000 instructions), never per sample.
 __device__ GN_NOISE_LINKAGE float fbm(uint32_t lane4, float px, float py, float pz, double scale,
