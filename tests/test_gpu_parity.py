@@ -356,3 +356,45 @@ def test_errors(gpu_ctx):
         c.upload(sc)
     assert e.value.code == _lib.E_ARG
     c.close()
+
+
+def test_progress_and_abort_from_another_thread():
+    """Rasterizer::getPercentDone / Abort (rasterizer.h:91-118) against the persistent kernel: progress counts finished
+    8x4 tiles and is monotone in [0, 1]; an abort makes the warps stop drawing tiles, the render call reports
+    GAMER_E_ABORTED and the skipped pixels keep their cleared value (rasterizer.cpp:296-297)."""
+    import threading
+    import time
+    from gamer_b200 import _lib
+    from gamer_b200.rasterizer import Context
+    ctx = Context([0])
+    try:
+        ctx.upload(scenes.single_galaxy_scene("Spiral", 2048, "cli"))      # ~90 ms of kernel time
+        box = {}
+
+        def work():
+            try:
+                box["img"] = ctx.render()
+            except _lib.GamerError as e:
+                box["err"] = e
+
+        t = threading.Thread(target=work)
+        t.start()
+        seen = []
+        deadline = time.time() + 20
+        while t.is_alive() and time.time() < deadline:
+            f = ctx.progress()
+            seen.append(f)
+            if 0.0 < f < 0.9:
+                ctx.abort()
+                break
+        t.join(30)
+        assert not t.is_alive()
+        assert all(0.0 <= f <= 1.0 for f in seen) and seen == sorted(seen)
+        if "err" in box:                       # the abort landed while the kernel was running
+            assert box["err"].code == _lib.E_ABORTED
+        else:                                  # the frame finished before the abort was seen: a complete image
+            assert np.isfinite(box["img"]).all()
+        full = ctx.render()                    # the context is usable again and renders the whole frame
+        assert ctx.progress() == 1.0 and (full > 0).any()
+    finally:
+        ctx.close()
