@@ -52,7 +52,7 @@ WORKER = textwrap.dedent("""
     dist.barrier()
     ctx.close()
     dist.destroy_process_group()
-    print("rank", rank, "ok")
+    print("rank %d ok" % rank, flush=True)   # one write for the text: the ranks share the pipe
 """)
 
 

@@ -62,7 +62,7 @@ WORKER = textwrap.dedent("""
     assert mx == world - 1 and sm == world
     assert parallel.units_of(rank, world, 5) == list(range(rank, 5, world))
     dist.destroy_process_group()
-    print("rank", rank, "ok")
+    print("rank %d ok" % rank, flush=True)   # one write for the text: the ranks share the pipe
 """)
 
 
