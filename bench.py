@@ -377,7 +377,7 @@ def run_ours(args):
                          "peak_source": f"{sm_count} SMs x 128 FP32 lanes x 2 flop x {sm_max:.0f} MHz (sm_max_mhz of "
                                         f"MEASURED_PEAKS.json, {peak_src}); the path is FP32/SFU-pipe bound, not HBM or tensor",
                          "algorithmic_flop_per_launch": my_flop / K, "launch_ms": k1_avg_ms},
-            "roofline_k2": {"kernel": "k2_tonemap", "bound": "hbm", "achieved": k2_bytes / (k2_best * 1e-3) / 1e9,
+            "roofline_k2": {"kernel": "k2_tonemap_v4", "bound": "hbm", "achieved": k2_bytes / (k2_best * 1e-3) / 1e9,
                             "peak": float(peaks.get("hbm_gbs", 6650.0)), "unit": "GB/s",
                             "frac": k2_bytes / (k2_best * 1e-3) / 1e9 / float(peaks.get("hbm_gbs", 6650.0)),
                             "traffic": None, "algorithmic_bytes_per_launch": k2_bytes, "launch_ms": k2_best,

@@ -462,7 +462,10 @@ __device__ __forceinline__ void tone_px(float x, float y, float z, float inv_exp
     x = (x < 255.0f) ? x : 255.0f; x = (0.0f < x) ? x : 0.0f;
     y = (y < 255.0f) ? y : 255.0f; y = (0.0f < y) ? y : 0.0f;
     z = (z < 255.0f) ? z : 255.0f; z = (0.0f < z) ? z : 0.0f;
-    uint32_t r = (uint32_t)(int)x, g = (uint32_t)(int)y, b = (uint32_t)(int)z;
+    // (int)v for v in [0, 255]: v + 2^23 rounded DOWN leaves floor(v) in the low significand bits — an FADD on the FMA
+    // pipe instead of a third kind of conversion on the XU pipe, the busiest unit of this kernel (ncu: 76 % while active)
+    uint32_t r = __float_as_uint(__fadd_rd(x, 8388608.0f)) & 0xFFu, g = __float_as_uint(__fadd_rd(y, 8388608.0f)) & 0xFFu,
+             b = __float_as_uint(__fadd_rd(z, 8388608.0f)) & 0xFFu;
     argb   = 0xFF000000u | (b << 16) | (g << 8) | r;
     shadow = 0xFF000000u | (r << 16) | (g << 8) | b;
 }
@@ -501,6 +504,44 @@ k2_tonemap(const float *__restrict__ rgb, const float *__restrict__ stars, uint3
         }
     }
     for (; k < n; k += nth) {
+        float x = rgb[3 * k], y = rgb[3 * k + 1], z = rgb[3 * k + 2];
+        if (stars) { x = __fadd_rn(x, stars[3 * k]); y = __fadd_rn(y, stars[3 * k + 1]); z = __fadd_rn(z, stars[3 * k + 2]); }
+        uint32_t o, h;
+        tone_px(x, y, z, inv_exposure, gamma, saturation, o, h);
+        if (argb)   argb[k] = o;
+        if (shadow) shadow[k] = h;
+    }
+}
+
+// K2 for 16-byte aligned buffers (the normal case; launch_k2 checks): four CONSECUTIVE pixels per thread — three 16-byte
+// loads (48 B of RGB), one 16-byte store per output image, a quarter of the memory instructions of the scalar kernel —
+// and no grid-stride loop: one group per thread, 1536 resident threads per SM, the block scheduler does the balancing.
+// The last n % 4 pixels are done by the first threads, one each.
+__global__ void __launch_bounds__(256, 6)
+k2_tonemap_v4(const float *__restrict__ rgb, const float *__restrict__ stars, uint32_t *__restrict__ argb,
+              uint32_t *__restrict__ shadow, size_t n, double inv_exposure_d, double gamma, double saturation) {
+    const float inv_exposure = (float)inv_exposure_d;
+    const size_t tid = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    const size_t groups = n >> 2;
+    if (tid < groups) {
+        const float4 *r4 = reinterpret_cast<const float4 *>(rgb), *s4 = reinterpret_cast<const float4 *>(stars);
+        float4 a = r4[3 * tid], b = r4[3 * tid + 1], c = r4[3 * tid + 2];
+        if (stars) {
+            const float4 p = s4[3 * tid], q = s4[3 * tid + 1], r = s4[3 * tid + 2];
+            a.x = __fadd_rn(a.x, p.x); a.y = __fadd_rn(a.y, p.y); a.z = __fadd_rn(a.z, p.z); a.w = __fadd_rn(a.w, p.w);
+            b.x = __fadd_rn(b.x, q.x); b.y = __fadd_rn(b.y, q.y); b.z = __fadd_rn(b.z, q.z); b.w = __fadd_rn(b.w, q.w);
+            c.x = __fadd_rn(c.x, r.x); c.y = __fadd_rn(c.y, r.y); c.z = __fadd_rn(c.z, r.z); c.w = __fadd_rn(c.w, r.w);
+        }
+        uint4 o, h;
+        tone_px(a.x, a.y, a.z, inv_exposure, gamma, saturation, o.x, h.x);
+        tone_px(a.w, b.x, b.y, inv_exposure, gamma, saturation, o.y, h.y);
+        tone_px(b.z, b.w, c.x, inv_exposure, gamma, saturation, o.z, h.z);
+        tone_px(c.y, c.z, c.w, inv_exposure, gamma, saturation, o.w, h.w);
+        if (argb)   reinterpret_cast<uint4 *>(argb)[tid] = o;
+        if (shadow) reinterpret_cast<uint4 *>(shadow)[tid] = h;
+    }
+    const size_t k = (groups << 2) + tid;
+    if (tid < 4 && k < n) {
         float x = rgb[3 * k], y = rgb[3 * k + 1], z = rgb[3 * k + 2];
         if (stars) { x = __fadd_rn(x, stars[3 * k]); y = __fadd_rn(y, stars[3 * k + 1]); z = __fadd_rn(z, stars[3 * k + 2]); }
         uint32_t o, h;
@@ -642,6 +683,12 @@ cudaError_t launch_k2(const float *rgb, const float *stars, uint32_t *argb, uint
     size_t cap = (size_t)sm_count * 4;          // 4 resident CTAs of 256 threads per SM (64 registers each), grid-stride
     int blocks = (int)(want < cap ? want : cap);
     if (blocks < 1) blocks = 1;
+    const uintptr_t al = (uintptr_t)rgb | (uintptr_t)stars | (uintptr_t)argb | (uintptr_t)shadow;
+    if ((al & 15u) == 0 && n >= 4) {
+        const size_t threads = (n >> 2) + 4;         // one group of four pixels per thread; the first threads also take the remainder
+        k2_tonemap_v4<<<(unsigned)((threads + 255) / 256), 256, 0, st>>>(rgb, stars, argb, shadow, n, 1.0 / exposure, gamma, saturation);
+        return cudaGetLastError();
+    }
     k2_tonemap<<<blocks, 256, 0, st>>>(rgb, stars, argb, shadow, n, 1.0 / exposure, gamma, saturation);
     return cudaGetLastError();
 }

@@ -12,6 +12,7 @@
 #include <thread>
 
 #include "gax.hpp"
+#include "fits_write.hpp"
 #include "png_write.hpp"
 #include "rasterizer_b200.hpp"
 #include "renderparams.hpp"
@@ -27,7 +28,8 @@ static void PrintUsage() {
                  " [ size = 256 ] [ filename = test{.png} ]\n"
                  "   - skybox [ method = omp/thread/b200 ] [ Renderingparams ] [ galaxy file ] [ png size ]\n"
                  "   - gaxdump [ galaxy gax file ]\n"
-                 "   - gaxcopy [ galaxy gax file ] [ out file ]\n";
+                 "   - gaxcopy [ galaxy gax file ] [ out file ]\n"
+                 "   environment: GAMER_B200_FITS=1 makes `galaxy` also write <filename>_red/_green/_blue.fits (linear planes)\n";
 }
 
 // QString::toFloat(): 0 on garbage
@@ -116,6 +118,16 @@ static int RenderSingleGalaxy(int n, char** param) {
             return 1;
         }
         std::cout << "Image saved to file " << outFile << ".png" << std::endl;
+        // the GUI's "Save FITS" (mainwindow.cpp:890-892) for the headless tool: GAMER_B200_FITS=1 also writes the linear
+        // planes <outfile>_red.fits / _green.fits / _blue.fits
+        const char* fits = std::getenv("GAMER_B200_FITS");
+        if (fits && *fits && std::string(fits) != "0") {
+            if (!save_fits_rgb(outFile, rasterizer.getRenderBuffer().data(), rasterizer.width(), rasterizer.height())) {
+                std::cout << "ERROR! cannot write " << outFile << "_red/_green/_blue.fits\n";
+                return 1;
+            }
+            std::cout << "Linear planes saved to " << outFile << "_{red,green,blue}.fits" << std::endl;
+        }
     } catch (const std::exception& e) {
         std::cout << "ERROR! " << e.what() << "\n";
         return 2;
@@ -245,6 +257,15 @@ int main(int argc, char** argv) {
                     img[size_t(y) * w + x] = 0xFF000000u | (uint32_t(x * 7 + y) & 0xFF) << 16 | (uint32_t(y * 5) & 0xFF) << 8 |
                                              (uint32_t(x ^ y) & 0xFF);
             return save_png_argb32(argv[2], img.data(), w, h) ? 0 : 1;
+        }
+        if (cmd == "fitstest" && argc == 5) {  // deterministic pattern through the FITS writer (CPU test of the writer)
+            const int w = std::atoi(argv[3]), h = std::atoi(argv[4]);
+            std::vector<float> rgb(size_t(w) * h * 3);
+            for (int y = 0; y < h; ++y)
+                for (int x = 0; x < w; ++x)
+                    for (int c = 0; c < 3; ++c)
+                        rgb[3 * (size_t(y) * w + x) + c] = float(x) * 0.37f - float(y) * 1.25f + float(c) * 1000.0f + 1e-3f * float(x * y);
+            return save_fits_rgb(argv[2], rgb.data(), w, h) ? 0 : 1;
         }
         if (cmd == "gaxcopy" && argc == 4) {
             Galaxy g;

@@ -218,6 +218,17 @@ def test_tonemap_ragged_sizes(gpu_ctx, oracle):
         a_g, s_g = gpu_ctx.tonemap(0.9, 1.0, 1.2, stars)
         a_c, s_c = oracle.tonemap(img, 0.9, 1.0, 1.2, stars)
         assert np.array_equal(a_g, a_c) and np.array_equal(s_g, s_c), size
+    # every remainder of the pixel count modulo 4, fewer pixels than one vector (scalar kernel), gamma != 1
+    full = scenes.single_galaxy_scene("Sombrero", 64, "oblique")
+    for (w, h), gamma in (((33, 2), 1.0), ((33, 3), 0.8), ((31, 4), 1.0), ((3, 1), 0.8), ((1, 1), 1.0), ((2, 1), 1.3)):
+        gpu_ctx.upload(full.tile(20, 30, w, h))
+        img = gpu_ctx.render()
+        assert img.shape[:2] == (h, w)
+        stars = np.random.default_rng(w * h).uniform(0, 2, img.shape).astype(np.float32)
+        for st in (stars, None):
+            a_g, s_g = gpu_ctx.tonemap(0.9, gamma, 1.2, st)
+            a_c, s_c = oracle.tonemap(img, 0.9, gamma, 1.2, st)
+            assert np.array_equal(a_g, a_c) and np.array_equal(s_g, s_c), (w, h, gamma)
 
 
 def test_more_galaxies_than_one_pass(gpu_ctx, oracle):

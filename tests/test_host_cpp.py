@@ -16,8 +16,9 @@ CLI = os.path.join(ROOT, "gamer_b200", "lib", "gamer_b200_cli")
 GAX = os.path.join(ROOT, "tests", "golden", "gax")
 
 
-def _run(*args, timeout=300):
-    return subprocess.run([CLI, *map(str, args)], capture_output=True, text=True, timeout=timeout)
+def _run(*args, timeout=300, env=None):
+    return subprocess.run([CLI, *map(str, args)], capture_output=True, text=True, timeout=timeout,
+                          env=dict(os.environ, **env) if env else None)
 
 
 def _read_png_rgba(path):
@@ -85,6 +86,25 @@ def test_png_writer(tmp_path):
     assert np.array_equal(img[..., 1], (y * 5) & 255)
     assert np.array_equal(img[..., 2], (x ^ y) & 255)
     assert (img[..., 3] == 255).all()
+
+
+def test_fits_writer_matches_python_writer(tmp_path):
+    """C++ fits_write.hpp against gamer_b200/fits.py byte for byte, and through the reader."""
+    from gamer_b200 import fits
+    w, h = 37, 23                                            # ragged: data not a multiple of the 2880-byte block
+    base = tmp_path / "p"
+    assert _run("fitstest", base, w, h).returncode == 0
+    y, x = np.mgrid[0:h, 0:w].astype(np.float32)
+    rgb = np.stack([(x * np.float32(0.37) - y * np.float32(1.25) + np.float32(c * 1000.0)) + np.float32(1e-3) * (x * y)
+                    for c in range(3)], axis=-1).astype(np.float32)
+    for no, suffix in enumerate(("_red.fits", "_green.fits", "_blue.fits")):
+        got = open(str(base) + suffix, "rb").read()
+        assert len(got) % 2880 == 0
+        plane = fits.read_plane(str(base) + suffix)
+        assert plane.shape == (h, w)
+        # the pattern is evaluated in float by both sides; compare through the reader, then the bytes of the Python writer
+        assert np.array_equal(got, fits.encode_plane(plane.astype(np.float32)))
+        assert np.allclose(plane, rgb[..., no], rtol=1e-6, atol=1e-3)
 
 
 def test_cli_usage_errors(tmp_path):
@@ -155,7 +175,8 @@ def test_cli_image_equals_python_pipeline(name, size, gamma, tmp_path):
     from gamer_b200.model import GalaxyInstance, RenderingParams
     from gamer_b200.rasterizer import Rasterizer
     out = tmp_path / "img"
-    p = _run("galaxy", "omp", 0.5, 0, 0, 0, 0, 0, 0, 1, 0, 90, 1.2, gamma, 1.1, 0.025, os.path.join(GAX, name + ".gax"), size, out)
+    p = _run("galaxy", "omp", 0.5, 0, 0, 0, 0, 0, 0, 1, 0, 90, 1.2, gamma, 1.1, 0.025, os.path.join(GAX, name + ".gax"), size, out,
+             env={"GAMER_B200_FITS": "1"})
     assert p.returncode == 0, p.stdout + p.stderr
     png = _read_png_rgba(str(out) + ".png")
     rp = RenderingParams(m_size=size, m_exposure=float(np.float32(1.2)), m_gamma=float(np.float32(gamma)),
@@ -173,3 +194,8 @@ def test_cli_image_equals_python_pipeline(name, size, gamma, tmp_path):
     want = np.stack([(sh >> 16) & 255, (sh >> 8) & 255, sh & 255, sh >> 24], axis=-1).astype(np.uint8)
     assert np.array_equal(png, want)
     assert want[..., :3].max() > 50        # a real image, not black
+    # GAMER_B200_FITS=1: the linear planes, bit for bit the render buffer widened to double
+    from gamer_b200 import fits
+    rb = np.asarray(r.getRenderBuffer()).reshape(size, size, 3)
+    for no, suffix in enumerate(("_red.fits", "_green.fits", "_blue.fits")):
+        assert np.array_equal(fits.read_plane(str(out) + suffix), rb[..., no].astype(np.float64)), suffix
