@@ -193,6 +193,9 @@ def port_value(arm: "CpuArm"):
 # summarised in profiles/r01_k1_ncu_summary.csv (the 50 MB framebuffer is still in the 126 MB L2 when the
 # kernel ends, so DRAM sees ~8 MB; the algorithmic bytes are 12 B/pixel = 50 MB)
 K1_DRAM_TRAFFIC = {"spiral_2048_oblique_orbit": 407040 + 7358976}
+# the same for one k2_tonemap_v4 launch at 2048^2 (profiles/r01_k2_ncu_summary.csv): the 50 MB frame is read from DRAM,
+# the two 16.8 MB images it writes are still in L2 when it ends (algorithmic bytes: 84 MB)
+K2_DRAM_TRAFFIC = {2048: 50363648 + 3948032}
 
 
 def run_ours(args):
@@ -380,7 +383,7 @@ def run_ours(args):
             "roofline_k2": {"kernel": "k2_tonemap_v4", "bound": "hbm", "achieved": k2_bytes / (k2_best * 1e-3) / 1e9,
                             "peak": float(peaks.get("hbm_gbs", 6650.0)), "unit": "GB/s",
                             "frac": k2_bytes / (k2_best * 1e-3) / 1e9 / float(peaks.get("hbm_gbs", 6650.0)),
-                            "traffic": None, "algorithmic_bytes_per_launch": k2_bytes, "launch_ms": k2_best,
+                            "traffic": K2_DRAM_TRAFFIC.get(size) if args.mode == "frames" else None, "algorithmic_bytes_per_launch": k2_bytes, "launch_ms": k2_best,
                             "peak_source": f"hbm_gbs of MEASURED_PEAKS.json ({peak_src})"},
             "kernel_ms": {"k1_avg": k1_avg_ms, "k2_avg_in_step": sum(k2_ms) / len(k2_ms), "k2_cold_l2": k2_best,
                           "wall_ms_per_step_incl_flush": wall_ms_max / K},
