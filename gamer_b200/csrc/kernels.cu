@@ -24,7 +24,11 @@ struct NoiseCtx {
 
 // The per-thread ray record of march(): K1_REC_WORDS floats per thread in shared memory behind the noise tables,
 // word k of thread t at [k][t] (conflict free). volatile: every access is a real load or store.
+#ifdef K1_NO_TWIRL_CACHE
 #define K1_REC_WORDS 17
+#else
+#define K1_REC_WORDS 21
+#endif
 struct Rec {
     volatile float *base;
     __device__ __forceinline__ volatile float &operator[](int k) const { return base[k * K1_THREADS]; }
@@ -100,7 +104,7 @@ __device__ __noinline__ float stars_helper_octaves(const DGalaxy &g, float noise
 }
 
 template <bool COUNT>
-__device__ __forceinline__ void eval_component(const DScene &sc, const DGalaxy &g, const DComp &c, Shared1 &s,
+__device__ __forceinline__ void eval_component(const DScene &sc, const DGalaxy &g, const DComp &c, Shared1 &s, const Rec rec,
                                                const NoiseCtx &nz, float &Ir, float &Ig, float &Ib, Counts &cn) {
     const float rs = sc.ray_step_f;
     if (c.cls == GAMER_CLASS_BULGE) {   // galaxycomponents.cpp:5-25 — evaluated at every sample, no gates
@@ -150,7 +154,23 @@ __device__ __forceinline__ void eval_component(const DScene &sc, const DGalaxy &
     if (cls > GAMER_CLASS_STARS) return;              // "stars small": no-op (see gamer_b200.h)
     const bool is_ridged = (cls == GAMER_CLASS_DUST2) | (cls == GAMER_CLASS_DUST_POSITIVE);
     f3 r = s.p;
+#ifdef K1_NO_TWIRL_CACHE
     if (cls != GAMER_CLASS_STARS) r = twirl_qt(g.axis_n, s.p, winding);
+#else
+    // components with the same winding factor twirl the sample to the same point (DComp::tgroup, scene_build.cpp):
+    // the point of the last twirl of this sample sits in the ray record, words 17 (group) and 18-20
+    if (cls != GAMER_CLASS_STARS) {
+        // decided for the lanes that are here together: a lane-wise branch would send the two sides through the
+        // noise call below one after the other (a lane that has the point recomputes the same bits)
+        const float tg = (float)c.tgroup;
+        const bool have = c.tgroup >= 0 && rec[17] == tg;
+        if (__all_sync(__activemask(), have)) r = {rec[18], rec[19], rec[20]};
+        else {
+            r = twirl_qt(g.axis_n, s.p, winding);
+            if (c.tgroup >= 0) { rec[17] = tg; rec[18] = r.x; rec[19] = r.y; rec[20] = r.z; }
+        }
+    }
+#endif
     float n;
     if (is_ridged) {                    // getRidgedMf(r * scale, ks, 9, 2.5, noiseOffset, noiseTilt)
         n = gnoise::ridged(nz.lane4, __fmul_rn(r.x, c.rscale), __fmul_rn(r.y, c.rscale), __fmul_rn(r.z, c.rscale),
@@ -325,9 +345,12 @@ __device__ __forceinline__ void march(const DScene &sc, const DGalaxy &g, const 
             // getWinding / getTheta once per sample, up front: a lazily set flag would have to live (in local memory)
             // across every noise call of the sample
             if (g.any_arm) arm_base(g, s, P);
+#ifndef K1_NO_TWIRL_CACHE
+            if (g.any_tshare) rec[17] = -1.0f;
+#endif
 #pragma unroll 1
             for (int k = 0; k < g.comp_count; k++)
-                eval_component<COUNT>(sc, g, sc.comp[g.comp_begin + k], s, nz, Ir, Ig, Ib, cn);
+                eval_component<COUNT>(sc, g, sc.comp[g.comp_begin + k], s, rec, nz, Ir, Ig, Ib, cn);
             if (COUNT) { cn.samples++; cn.gates += g.comp_count + g.noop_count; }
             const f3 dir = {rec[3], rec[4], rec[5]};
             const f3 p0 = {rec[0], rec[1], rec[2]};
@@ -337,6 +360,10 @@ __device__ __forceinline__ void march(const DScene &sc, const DGalaxy &g, const 
             rec[0] = pn.x; rec[1] = pn.y; rec[2] = pn.z;
             Ir = fmaxf(0.0f, Ir); Ig = fmaxf(0.0f, Ig); Ib = fmaxf(0.0f, Ib);   // Util::floor (util.h:62-64)
         }
+        // all 32 lanes are here in every trip (the votes of the run loop name the full warp). Without the explicit
+        // rendezvous the lanes that sat the in-slab sample out may go on through the run loop as a group of their own:
+        // the full-mask votes make that correct, but each side then pays for the loop (ncu: 26 threads per instruction)
+        __syncwarp();
     }
 }
 

@@ -189,6 +189,26 @@ int gk_build_scene(const GamerFrame *f, const GamerGalaxy *gal, const GamerCompo
             q.rwq = float(std::pow(2.5, w));
         }
         d.comp_count = nc - d.comp_begin;
+        // twirl sharing: every class but bulge and stars evaluates its noise at twirl(p, winding) with
+        // winding = getWinding(r) * cp.winding (0 without arm or winding): components with the same factor get the same
+        // point, so the kernel keeps the last twirled point of a sample and the group it belongs to
+        d.any_tshare = 0;
+        for (int a = 0; a < d.comp_count; a++) {
+            DComp &qa = s.comp[d.comp_begin + a];
+            qa.tgroup = -1;
+            if (qa.cls == GAMER_CLASS_BULGE || qa.cls >= GAMER_CLASS_STARS) continue;
+            const bool wa = (qa.flags & DC_HAS_ARM) && (qa.flags & DC_HAS_WINDING);
+            int first = -1, members = 0;
+            for (int b = 0; b < d.comp_count; b++) {
+                const DComp &qb = s.comp[d.comp_begin + b];
+                if (qb.cls == GAMER_CLASS_BULGE || qb.cls >= GAMER_CLASS_STARS) continue;
+                const bool wb = (qb.flags & DC_HAS_ARM) && (qb.flags & DC_HAS_WINDING);
+                if (wa != wb || (wa && qa.winding_d != qb.winding_d)) continue;
+                if (first < 0) first = b;
+                members++;
+            }
+            if (members >= 2) { qa.tgroup = first; d.any_tshare = 1; }
+        }
         d.fast_ok = d.n_bulge <= 2;
         // the bulge-only path also skips Util::floor (util.h:62-64): a bulge adds max(k v, 0) * spectrum, which
         // cannot take a non-negative I below zero unless a spectrum component is negative (or NaN)

@@ -47,6 +47,7 @@ struct DComp {
     float   rw[DEV_RIDGED_OCTAVES];   // pow(ks * 2.5^o, -0.05f)  (noise.cpp:119); the kernel uses rw[0] and the ratio below
     float   rwq;                      // pow(2.5, -0.05f): rw[o] = rw[0] * rwq^o
     int32_t octaves;         // fBm octave count of the class (10 disk/stars, 9 dust; 0 otherwise)
+    int32_t tgroup;          // twirl sharing: first component of this galaxy with the same twirl angle, -1 = nobody shares it
     double  nscale;          // fBm start frequency, as a double the way the reference forms it
     double  winding_d;       // cp.winding as the double the reference multiplies getWinding() with
 };
@@ -71,6 +72,7 @@ struct DGalaxy {
     float   slab_gate;                // max h_gate over the non-bulge components (-1 if none)
     int32_t noop_count;               // active "stars small" components: visited by the reference, no-op here
     int32_t any_arm;                  // some active component has arm != 0 (getWinding / getTheta are then needed)
+    int32_t any_tshare;               // some components share a twirl angle (DComp::tgroup >= 0)
     double  winding_b, winding_n;     // getWinding is evaluated in double (its result feeds the twirl angle)
 };
 
