@@ -192,7 +192,7 @@ def port_value(arm: "CpuArm"):
 # dram__bytes_read.sum + dram__bytes_write.sum of one k1_march launch, from the `ncu --set full` capture
 # summarised in profiles/r01_k1_ncu_summary.csv (the 50 MB framebuffer is still in the 126 MB L2 when the
 # kernel ends, so DRAM sees ~8 MB; the algorithmic bytes are 12 B/pixel = 50 MB)
-K1_DRAM_TRAFFIC = {"spiral_2048_oblique_orbit": 407040 + 7358976}
+K1_DRAM_TRAFFIC = {"spiral_2048_oblique_orbit": 74752 + 7794432, "spiral_2048_cli_view": 87552 + 9464832}
 # the same for one k2_tonemap_v4 launch at 2048^2 (profiles/r01_k2_ncu_summary.csv): the 50 MB frame is read from DRAM,
 # the two 16.8 MB images it writes are still in L2 when it ends (algorithmic bytes: 84 MB)
 K2_DRAM_TRAFFIC = {2048: 50363648 + 3948032}

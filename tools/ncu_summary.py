@@ -1,9 +1,9 @@
 """Write the metric/value/unit summary of one ncu report: python tools/ncu_summary.py rep.ncu-rep metrics.txt > out.csv
-(metrics.txt: one metric name per line; default = the names already listed in profiles/r01_k1_ncu_summary.csv)."""
+(metrics.txt: one metric name per line; default = tools/ncu_metrics.txt)."""
 import csv, subprocess, sys
 rep = sys.argv[1]
-names = [l.strip() for l in open(sys.argv[2])] if len(sys.argv) > 2 else \
-        [r[0] for r in list(csv.reader(open("profiles/r01_k1_ncu_summary.csv")))[1:]]
+import os
+names = [l.strip() for l in open(sys.argv[2] if len(sys.argv) > 2 else os.path.join(os.path.dirname(os.path.abspath(__file__)), "ncu_metrics.txt"))]
 raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
 rows = list(csv.reader(raw.splitlines()))
 h, u, v = rows[0], rows[1], rows[2]
