@@ -63,6 +63,19 @@ def synthetic_galaxy(kind="allclasses") -> Galaxy:
     if kind == "ellipsoid":
         p.axis = [1.0, 0.6, 0.8]
     C = ComponentParams
+    if kind == "sharing":
+        # twirl sharing (DComp::tgroup): three components with winding 0.12 and two without arms (winding factor 0),
+        # interleaved with a fourth factor so that the kept point is replaced between members of a group
+        g.componentParams = [
+            C("bulge", 30.0, "Yellow", 1.0, 0.02, 6.0, 1.0, 0.0, 0.1, 1.0, 0.0, 1.0, 1.0, 0.1, "b"),
+            C("disk", 2500.0, "Blue", 0.4, 0.03, 0.45, 1.0, 0.3, 0.12, 8.0, -0.05, 0.7, 1.0, 0.1, "d1"),
+            C("dust", 200.0, "Cyan", 0.2, 0.02, 0.45, 1.0, 1.0, 0.3, 4.0, 0.1, 1.3, 1.0, 0.0, "du"),
+            C("dust2", 90.0, "Blue", 0.3, 0.025, 0.4, 1.0, 0.0, 0.12, 5.0, 1.05, 1.5, 1.0, 0.2, "d2"),
+            C("dust positive", 120.0, "Purple", 0.0, 0.025, 0.4, 1.0, 0.0, 0.12, 6.0, 1.1, 1.4, 1.0, 0.15, "dp no arm"),
+            C("disk", 900.0, "White", 0.1, 0.02, 0.35, 1.0, 0.0, 0.12, 2.0, 0.0, 1.0, 1.0, 0.0, "d3"),
+            C("dust2", 60.0, "Red", 0.0, 0.02, 0.4, 1.0, 0.0, 0.3, 3.0, 1.0, 1.2, 1.0, 0.3, "d2 no arm"),
+        ]
+        return g
     g.componentParams = [
         C("bulge", 40.0, "Yellow", 1.0, 0.02, 6.0, 1.0, 0.0, 0.1, 1.0, 0.0, 1.0, 1.0, 0.1, "b"),
         C("disk", 2500.0, "Blue", 0.4, 0.03, 0.45, 1.0, 0.3, 0.15, 8.0, -0.05, 0.7, -0.5, 0.1, "d"),

@@ -148,6 +148,14 @@ def test_synthetic_classes(gpu_ctx, oracle, kind, view):
     check_scene(gpu_ctx, oracle, scenes.single_galaxy_scene(scenes.synthetic_galaxy(kind), 80, view), f"{kind}/{view}")
 
 
+def test_components_sharing_a_twirl(gpu_ctx, oracle):
+    """components with equal winding factors reuse one twirled point per sample (scene_build.cpp, DComp::tgroup)"""
+    g = scenes.synthetic_galaxy("sharing")
+    check_scene(gpu_ctx, oracle, scenes.single_galaxy_scene(g, 96, "oblique"), "sharing/oblique")
+    check_scene(gpu_ctx, oracle, scenes.single_galaxy_scene(g, 64, "cli", position=(0.1, -0.05, 0.2), orientation=(0.3, 0.8, -0.5)),
+                "sharing/tilted")
+
+
 def test_oriented_and_multi_galaxy(gpu_ctx, oracle):
     check_scene(gpu_ctx, oracle, scenes.single_galaxy_scene("Spiral", 80, "outside", position=(0.2, -0.1, 0.3),
                                                            orientation=(0.3, 0.8, -0.5), iscale=0.6), "oriented")
