@@ -252,3 +252,57 @@ int main() {
     assert float(me) <= 1.0 and float(ma) <= 1.0, (me, ma)
     assert float(ms) <= 3e-16 and float(mf) <= 5e-7, (ms, mf)
     assert int(mism) == 0
+
+
+def test_scene_builder_twirl_groups_and_step_thresholds(tmp_path):
+    """csrc/scene_build.cpp compiled for the host: components with the same winding factor form a twirl group
+    (DComp::tgroup = first member, -1 when alone), and the float thresholds of the step clamp are exact: the
+    reference's double expression clamp(len * rayStep, min, 0.01) (rasterizer.cpp:449) flips exactly there."""
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    src = tmp_path / "sb.cpp"
+    src.write_text(r'''
+#include "%s/gamer_b200/csrc/scene_build.cpp"
+#include <cmath>
+static GamerComponent comp(int cls, double arm, double winding, double active = 1.0) {
+    GamerComponent c; memset(&c, 0, sizeof c);
+    c.class_id = cls; c.active = active; c.strength = 100; c.arm = arm; c.z0 = 0.02; c.r0 = 0.4; c.inner = 0.1; c.delta = 0;
+    c.winding = winding; c.scale = 5; c.noise_offset = 0; c.noise_tilt = 1; c.ks = 1; c.spec[0] = c.spec[1] = c.spec[2] = 1;
+    return c;
+}
+int main() {
+    GamerComponent cs[9] = {
+        comp(GAMER_CLASS_BULGE, 1.0, 0.12), comp(GAMER_CLASS_DISK, 0.4, 0.12), comp(GAMER_CLASS_DUST, 0.2, 0.3),
+        comp(GAMER_CLASS_DISK, 0.3, 0.5, 0.0) /* inactive */, comp(GAMER_CLASS_DUST2, 0.3, 0.12),
+        comp(GAMER_CLASS_DUST_POSITIVE, 0.0, 0.12) /* no arm: factor 0 */, comp(GAMER_CLASS_STARS, 0.2, 0.12),
+        comp(GAMER_CLASS_DISK, 0.1, 0.12), comp(GAMER_CLASS_DUST2, 0.0, 0.3) /* no arm: factor 0 */ };
+    GamerGalaxy g; memset(&g, 0, sizeof g);
+    g.orient[1] = 1; g.rotmat[0] = 1; g.axis[0] = g.axis[1] = g.axis[2] = 1; g.intensity_scale = 1;
+    g.winding_b = 0.5; g.winding_n = 2; g.no_arms = 2; g.arm[1] = 3.14; g.comp_begin = 0; g.comp_count = 9;
+    GamerFrame f; memset(&f, 0, sizeof f);
+    f.width = f.height = f.full_size = 64; f.cam[0] = 0.5f; f.ray_step = (double)0.025f; f.min_ray_step = 0.001;
+    f.n_galaxies = 1; f.n_components = 9;
+    for (int i = 0; i < 4; i++) f.inv_vp[5 * i] = 1;
+    static DScene sc; char err[256] = "";
+    if (gk_build_scene(&f, &g, cs, &sc, err, sizeof err) != GAMER_OK) { printf("ERR %%s\n", err); return 1; }
+    const DGalaxy &d = sc.gal[0];
+    printf("%%d %%d", d.comp_count, d.any_tshare);
+    for (int k = 0; k < d.comp_count; k++) printf(" %%d:%%d", sc.comp[d.comp_begin + k].cls, sc.comp[d.comp_begin + k].tgroup);
+    printf("\n");
+    // the step clamp as the reference evaluates it, on both sides of each threshold
+    auto step = [&](float L) { double v = (double)L * f.ray_step; v = v < 0.01 ? v : 0.01; v = f.min_ray_step < v ? v : f.min_ray_step; return v; };
+    const float hi = sc.len_hi_thr, lo = sc.len_lo_thr;
+    printf("%%d %%d %%d %%d\n", step(hi) < 0.01, step(std::nextafter(hi, 2.0f)) == 0.01, step(lo) == f.min_ray_step,
+           step(std::nextafter(lo, 2.0f)) > f.min_ray_step);
+    printf("%%d\n", sc.est2_lo <= lo * lo && sc.est2_hi >= hi * hi);
+}
+''' % root)
+    exe = tmp_path / "sb"
+    subprocess.run(["g++", "-O2", "-ffp-contract=off", "-std=c++17", "-I", os.path.join(root, "gamer_b200", "csrc"), "-o", str(exe),
+                    str(src), os.path.join(root, "gamer_b200", "csrc", "host_math.cpp")], check=True)
+    out = subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.splitlines()
+    # active components in file order: bulge, disk, dust, dust2, dust positive, stars, disk, dust2
+    # groups: {disk, dust2, disk} share 0.12 -> first member (index 1); the arm-less pair shares factor 0 -> index 4
+    assert out[0] == "8 1 0:-1 1:1 2:-1 3:1 4:4 5:-1 1:1 3:4", out[0]
+    assert out[1] == "1 1 1 1", out[1]
+    assert out[2] == "1", out[2]
