@@ -254,7 +254,7 @@ int main() {
     assert int(mism) == 0
 
 
-def test_scene_builder_twirl_groups_and_step_thresholds(tmp_path):
+def test_scene_builder_twirl_groups_and_exact_thresholds(tmp_path):
     """csrc/scene_build.cpp compiled for the host: components with the same winding factor form a twirl group
     (DComp::tgroup = first member, -1 when alone), and the float thresholds of the step clamp are exact: the
     reference's double expression clamp(len * rayStep, min, 0.01) (rasterizer.cpp:449) flips exactly there."""
@@ -295,6 +295,14 @@ int main() {
     printf("%%d %%d %%d %%d\n", step(hi) < 0.01, step(std::nextafter(hi, 2.0f)) == 0.01, step(lo) == f.min_ray_step,
            step(std::nextafter(lo, 2.0f)) > f.min_ray_step);
     printf("%%d\n", sc.est2_lo <= lo * lo && sc.est2_hi >= hi * hi);
+    // the slab gate |height / z0| > 2 (galaxycomponent.h:61-64) and the radial gate intensity > 0.001
+    // (galaxycomponent.h:72-81, galaxycomponent.cpp:58-65) of the first disk, on both sides of their thresholds
+    const DComp &q = sc.comp[d.comp_begin + 1];
+    auto slab = [&](float a) { return !(std::fabs((double)a / cs[1].z0) > 2.0); };
+    auto radial = [&](float plen) { float radius = plen / g.axis[0]; double r = std::exp(-(double)radius / (cs[1].r0 * 0.5f));
+                                    double in = r - 0.01f; in = in < 1 ? in : 1; in = 0 < in ? in : 0; if (in > 0.1) in = 0.1; return in > 0.001; };
+    printf("%%d %%d %%d %%d %%d\n", slab(q.h_gate), !slab(std::nextafter(q.h_gate, 9.0f)), radial(q.plen_thr),
+           !radial(std::nextafter(q.plen_thr, 9.0f)), q.plen_lo < q.plen_thr && q.plen_thr < q.plen_hi);
 }
 ''' % root)
     exe = tmp_path / "sb"
@@ -306,3 +314,4 @@ int main() {
     assert out[0] == "8 1 0:-1 1:1 2:-1 3:1 4:4 5:-1 1:1 3:4", out[0]
     assert out[1] == "1 1 1 1", out[1]
     assert out[2] == "1", out[2]
+    assert out[3] == "1 1 1 1 1", out[3]
