@@ -24,6 +24,8 @@ struct NoiseCtx {
 
 // The per-thread ray record of march(): K1_REC_WORDS floats per thread in shared memory behind the noise tables,
 // word k of thread t at [k][t] (conflict free). volatile: every access is a real load or store.
+// Words: 0-2 p, 3-5 dir, 6-8 origin, 9-11 camera relative to the galaxy, 12 length, 13 loop bound (-inf: no ray),
+// 14 step, 15 weight, 16 distance marched (+inf: no ray), 17 twirl group of the point in 18-20 (-1: none yet).
 #ifdef K1_NO_TWIRL_CACHE
 #define K1_REC_WORDS 17
 #else
