@@ -93,6 +93,18 @@ def test_no_cpu_fallback_without_device():
     assert b"CUDA" in lib.gamer_b200_last_error(None) or b"cuda" in lib.gamer_b200_last_error(None)
 
 
+def test_missing_library_fails_loudly(tmp_path):
+    """no extension, no render path: the binding raises instead of falling back to anything"""
+    import subprocess, sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    code = ("import sys; sys.path.insert(0, %r)\n"
+            "from gamer_b200.rasterizer import Context\n"
+            "try:\n    Context([0])\nexcept ImportError as e:\n    print('ImportError', 'no CPU fallback' in str(e))\n" % root)
+    p = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=120,
+                       env=dict(os.environ, GAMER_B200_LIB=str(tmp_path / "nowhere.so")))
+    assert p.stdout.strip() == "ImportError True", p.stdout + p.stderr
+
+
 # ---- host math vs oracle's independent restatement -----------------------------------------------------
 @pytest.mark.parametrize("view", list(scenes.VIEWS))
 def test_camera_matrix(oracle, view):
