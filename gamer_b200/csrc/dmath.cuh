@@ -167,6 +167,39 @@ DM_FN void sincos_nc(double a, double &s, double &c) {
     c = ((k + 1) & 2) ? -cc : cc;
 }
 
+// sinf(y) and cosf(y) exactly as glibc >= 2.28 computes them (sysdeps/ieee754/flt-32/s_sincosf.h, s_sinf.c, s_cosf.c:
+// reduce_fast + sinf_poly, the non-TOINT_INTRINSICS branch that x86-64 builds use) for |y| < 120: a double-precision
+// quadrant reduction and two short polynomials, NOT correctly rounded (2.6 % of arguments give the neighbouring float).
+// The reference's twirl quaternion is built from these two calls (QQuaternion::fromAxisAndAngle, galaxycomponent.h:86-90)
+// and the ridged octaves magnify a 1-ulp change of it past the parity tolerance, so the libm the reference links is
+// part of the result; the oracle and the reference build (oracle/_ref) link glibc. Branch-free: glibc's own shortcuts
+// for |y| < 0.75 (no reduction) and |y| < 2^-12 (y, 1) return the same floats as the general path (n = 0; the
+// polynomial rounds back to y and 1). tests/test_cpu.py checks every float in [0, 16) against the host's libm.
+// Returns false for |y| >= 120 (glibc's large-argument path is not restated; callers fall back to sincos_nc).
+DM_FN bool sincosf_glibc(float y, float &s, float &c) {
+    double x = (double)y;
+    const double r = DM_MUL(x, 0x1.45F306DC9C883p+23);                 // x * 2/pi * 2^24
+    const int n = ((int)r + 0x800000) >> 24;                           // quadrant, round to nearest
+    x = DM_FMA(-(double)n, 0x1.921FB54442D18p0, x);
+    const double x2 = DM_MUL(x, x);
+    const double xs = (n + 1) & 2 ? -x : x;                            // sign[n & 3] = {1, -1, -1, 1}
+    // sine polynomial on xs
+    const double x3 = DM_MUL(xs, x2);
+    const double s1 = DM_FMA(x2, -0x1.994eb3774cf24p-13, 0x1.1107605230bc4p-7);
+    const double x7 = DM_MUL(x3, x2);
+    const double sp = DM_FMA(x7, s1, DM_FMA(x3, -0x1.555545995a603p-3, xs));
+    // cosine polynomial (negated as a whole in quadrants 2 and 3: glibc's second table holds the negated coefficients)
+    const double c2 = DM_FMA(x2, 0x1.99343027bf8c3p-16, -0x1.6c087e89a359dp-10);
+    const double c1 = DM_FMA(x2, 0x1.55553e1068f19p-5, -0x1.ffffffd0c621cp-2);
+    const double x6 = DM_MUL(DM_MUL(x2, x2), x2);
+    double cp = DM_FMA(x6, c2, DM_FMA(x2, c1, 1.0));
+    if (n & 2) cp = -cp;
+    const float fs = (float)sp, fc = (float)cp;
+    s = (n & 1) ? fc : fs;
+    c = (n & 1) ? fs : fc;
+    return fabsf(y) < 120.0f;
+}
+
 // atan2f(y, x) in float to ~1e-7 absolute (value arithmetic: the arm phase): quotient by reciprocal, one more
 // reciprocal for the (a-1)/(a+1) reduction above tan(pi/8), degree-9 odd minimax polynomial (error < 1e-9)
 DM_FN float atan2f_fast(float y, float x) {

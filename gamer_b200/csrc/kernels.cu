@@ -105,7 +105,25 @@ __device__ __noinline__ float stars_helper_octaves(const DGalaxy &g, float noise
     return add;
 }
 
-template <bool COUNT>
+// twirl of the sample point (galaxycomponent.h:86-90). ORIENT_Y: the axis is exactly (0,1,0) — twirl_y of qtf.cuh,
+// bit-identical to the general sequence, which stays out of line for the (never observed) case that the quaternion's
+// length is outside the two values twirl_y knows.
+__device__ __noinline__ void twirl_general(const float *axis_n, float px, float py, float pz, double winding, float *out) {
+    const f3 r = twirl_qt(axis_n, {px, py, pz}, winding);
+    out[0] = r.x; out[1] = r.y; out[2] = r.z;
+}
+template <bool ORIENT_Y>
+__device__ __forceinline__ f3 twirl_point(const DGalaxy &g, f3 p, double winding) {
+    if (ORIENT_Y) {
+        bool ok;
+        f3 r = twirl_y(p, winding, &ok);
+        if (!ok) { float o[3]; twirl_general(g.axis_n, p.x, p.y, p.z, winding, o); r = {o[0], o[1], o[2]}; }
+        return r;
+    }
+    return twirl_qt(g.axis_n, p, winding);
+}
+
+template <bool COUNT, bool ORIENT_Y>
 __device__ __forceinline__ void eval_component(const DScene &sc, const DGalaxy &g, const DComp &c, Shared1 &s, const Rec rec,
                                                const NoiseCtx &nz, float &Ir, float &Ig, float &Ib, Counts &cn) {
     const float rs = sc.ray_step_f;
@@ -128,7 +146,8 @@ __device__ __forceinline__ void eval_component(const DScene &sc, const DGalaxy &
     else if (s.Plen > c.plen_hi) pass = false;
     else {      // rare: inside the band where only the exact |P| decides; P = p - orient * dott like getRadius
         const f3 orient = {g.orient[0], g.orient[1], g.orient[2]};
-        pass = v_length(v_sub(s.p, v_mul(orient, s.dott))) <= c.plen_thr;
+        const f3 Pq = ORIENT_Y ? f3{s.p.x, 0.0f, s.p.z} : v_sub(s.p, v_mul(orient, s.dott));
+        pass = v_length(Pq) <= c.plen_thr;
     }
     if (!pass) return;
     float intensity = fminf(fmaxf(ex2(s.Plen * c.k_radial) - 0.01f, 0.0f), 0.1f);
@@ -157,7 +176,7 @@ __device__ __forceinline__ void eval_component(const DScene &sc, const DGalaxy &
     const bool is_ridged = (cls == GAMER_CLASS_DUST2) | (cls == GAMER_CLASS_DUST_POSITIVE);
     f3 r = s.p;
 #ifdef K1_NO_TWIRL_CACHE
-    if (cls != GAMER_CLASS_STARS) r = twirl_qt(g.axis_n, s.p, winding);
+    if (cls != GAMER_CLASS_STARS) r = twirl_point<ORIENT_Y>(g, s.p, winding);
 #else
     // components with the same winding factor twirl the sample to the same point (DComp::tgroup, scene_build.cpp):
     // the point of the last twirl of this sample sits in the ray record, words 17 (group) and 18-20
@@ -168,7 +187,7 @@ __device__ __forceinline__ void eval_component(const DScene &sc, const DGalaxy &
         const bool have = c.tgroup >= 0 && rec[17] == tg;
         if (__all_sync(__activemask(), have)) r = {rec[18], rec[19], rec[20]};
         else {
-            r = twirl_qt(g.axis_n, s.p, winding);
+            r = twirl_point<ORIENT_Y>(g, s.p, winding);
             if (c.tgroup >= 0) { rec[17] = tg; rec[18] = r.x; rec[19] = r.y; rec[20] = r.z; }
         }
     }
@@ -233,7 +252,7 @@ __device__ __forceinline__ void eval_component(const DScene &sc, const DGalaxy &
 // Control arithmetic is exact (see march.cuh). The loop test `dot(p-origin, ll) < length + step` compares a float with
 // a double; for a float d and double L, d < L  <=>  d < round_up_to_float(L), so the bound is kept as a float that is
 // refreshed only when the step length changes.
-template <bool COUNT>
+template <bool COUNT, bool ORIENT_Y>
 __device__ __forceinline__ void march(const DScene &sc, const DGalaxy &g, const Rec rec, bool active, f3 isp1, f3 isp2,
                                       f3 camrel, const NoiseCtx &nz, float &Ir, float &Ig, float &Ib, Counts &cn) {
     // The march has two kinds of samples with very different needs: off-slab samples (nine in ten in an exterior view)
@@ -317,7 +336,8 @@ __device__ __forceinline__ void march(const DScene &sc, const DGalaxy &g, const 
                             thr = __double2float_ru(__dadd_rn((double)length_f, step));
                         }
                     }
-                    const float dott = v_dot(p, orient);                         // getRadius (galaxycomponent.h:72-76)
+                    // getRadius (galaxycomponent.h:72-76); for orient = (0,1,0): (p.x*0 + p.y*1) + p.z*0 = p.y
+                    const float dott = ORIENT_Y ? p.y : v_dot(p, orient);
                     need = !(fast_ok && !(fabsf(dott) <= g.slab_gate));           // an in-slab sample at p
                     if (!need) {
                         const float plen3 = sqrta(fmaf(p.z, p.z, fmaf(p.y, p.y, p.x * p.x)));
@@ -340,8 +360,8 @@ __device__ __forceinline__ void march(const DScene &sc, const DGalaxy &g, const 
             const f3 orient = {g.orient[0], g.orient[1], g.orient[2]};
             Shared1 s;
             s.p = {rec[0], rec[1], rec[2]};
-            s.dott = v_dot(s.p, orient);
-            const f3 P = v_sub(s.p, v_mul(orient, s.dott));
+            s.dott = ORIENT_Y ? s.p.y : v_dot(s.p, orient);
+            const f3 P = ORIENT_Y ? f3{s.p.x, 0.0f, s.p.z} : v_sub(s.p, v_mul(orient, s.dott));   // p.y - p.y*1 = 0
             s.Plen = sqrta(fmaf(P.z, P.z, fmaf(P.y, P.y, P.x * P.x)));
             s.weight = rec[15];
             // getWinding / getTheta once per sample, up front: a lazily set flag would have to live (in local memory)
@@ -352,7 +372,7 @@ __device__ __forceinline__ void march(const DScene &sc, const DGalaxy &g, const 
 #endif
 #pragma unroll 1
             for (int k = 0; k < g.comp_count; k++)
-                eval_component<COUNT>(sc, g, sc.comp[g.comp_begin + k], s, rec, nz, Ir, Ig, Ib, cn);
+                eval_component<COUNT, ORIENT_Y>(sc, g, sc.comp[g.comp_begin + k], s, rec, nz, Ir, Ig, Ib, cn);
             if (COUNT) { cn.samples++; cn.gates += g.comp_count + g.noop_count; }
             const f3 dir = {rec[3], rec[4], rec[5]};
             const f3 p0 = {rec[0], rec[1], rec[2]};
@@ -377,10 +397,13 @@ __device__ __forceinline__ int image_row(const DScene &sc, int L) {
 // SINGLE: the frame holds one galaxy (the reference's CLI, the benchmarks, every shipped scene file): its index is a
 // compile-time 0, so every galaxy field is a constant-bank operand of the instruction that uses it - no load, no
 // register. The general kernel indexes the galaxy array at run time.
-template <bool COUNT, bool SINGLE>
+// MODE 2: SINGLE and the galaxy's orientation is exactly (0,1,0) with an identity rotmat (DGalaxy::orient_y) - every
+// shipped galaxy file and the reference's CLI: dot(p, orient) is p.y and the twirl takes the short sequence of qtf.cuh.
+template <bool COUNT, int MODE>
 __global__ void __launch_bounds__(K1_THREADS, K1_MINBLOCKS)
 k1_march(const __grid_constant__ DScene sc, float *__restrict__ out, unsigned long long *__restrict__ counters,
          const volatile int *abort_flag, unsigned int *progress, unsigned int n_tiles, unsigned int tiles_x) {
+    constexpr bool SINGLE = MODE >= 1, ORIENT_Y = MODE == 2;
     gnoise::table_init();
     __syncthreads();
 
@@ -443,7 +466,7 @@ k1_march(const __grid_constant__ DScene sc, float *__restrict__ out, unsigned lo
             f3 isp2 = v_add(o, v_mul(d, __double2float_rn(t1)));
             if (t1 > 0.0) isp2 = o;
             if (t0 > 0.0 && t1 > 0.0) hit = false;
-            march<COUNT>(sc, g, rec, hit, isp1, isp2, o, nz, Ir, Ig, Ib, cn);
+            march<COUNT, ORIENT_Y>(sc, g, rec, hit, isp1, isp2, o, nz, Ir, Ig, Ib, cn);
         }
         // rp.I * 0.01 / rayStep  (rasterizer.cpp:409): QVector3D*float then QVector3D/float
         if (!inimg) { }
@@ -677,10 +700,10 @@ namespace gk {
 
 // kernels that use the noise table need > 48 KB of dynamic shared memory: opt in once per device
 cudaError_t prepare_device() {
-    cudaError_t e = cudaFuncSetAttribute(k1_march<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)K1_DYN_SMEM);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(k1_march<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)K1_DYN_SMEM);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(k1_march<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)K1_DYN_SMEM);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(k1_march<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)K1_DYN_SMEM);
+    cudaError_t e = cudaSuccess;
+#define K1_ATTR(C, M) if (e == cudaSuccess) e = cudaFuncSetAttribute(k1_march<C, M>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)K1_DYN_SMEM)
+    K1_ATTR(true, 0); K1_ATTR(false, 0); K1_ATTR(true, 1); K1_ATTR(false, 1); K1_ATTR(true, 2); K1_ATTR(false, 2);
+#undef K1_ATTR
     if (e == cudaSuccess) e = cudaFuncSetAttribute(kp_simplex, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GN_DYN_SMEM);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(kp_fbm, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GN_DYN_SMEM);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(kp_ridged, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GN_DYN_SMEM);
@@ -696,12 +719,10 @@ cudaError_t launch_k1(const DScene &sc, float *out_dev, unsigned long long *coun
     const unsigned int wave = (unsigned int)sm_count * K1_MINBLOCKS;
     if (grid > wave) grid = wave;
     if (grid < 1) grid = 1;
-    const bool single = sc.n_galaxies == 1;
-#define K1_LAUNCH(C, S) k1_march<C, S><<<grid, K1_THREADS, K1_DYN_SMEM, st>>>(sc, out_dev, counters_dev, abort_dev, progress_dev, n_tiles, tiles_x)
-    if (counted && single)       K1_LAUNCH(true, true);
-    else if (counted)            K1_LAUNCH(true, false);
-    else if (single)             K1_LAUNCH(false, true);
-    else                         K1_LAUNCH(false, false);
+    const int mode = sc.n_galaxies != 1 ? 0 : (sc.gal[0].orient_y ? 2 : 1);
+#define K1_LAUNCH(C, M) k1_march<C, M><<<grid, K1_THREADS, K1_DYN_SMEM, st>>>(sc, out_dev, counters_dev, abort_dev, progress_dev, n_tiles, tiles_x)
+    if (counted) { if (mode == 2) K1_LAUNCH(true, 2); else if (mode == 1) K1_LAUNCH(true, 1); else K1_LAUNCH(true, 0); }
+    else         { if (mode == 2) K1_LAUNCH(false, 2); else if (mode == 1) K1_LAUNCH(false, 1); else K1_LAUNCH(false, 0); }
 #undef K1_LAUNCH
     return cudaGetLastError();
 }

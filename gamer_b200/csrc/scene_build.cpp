@@ -69,6 +69,8 @@ int gk_build_scene(const GamerFrame *f, const GamerGalaxy *gal, const GamerCompo
         double hi = 0.01 * (1.0 + 2e-5) / f->ray_step, lo = f->min_ray_step * (1.0 - 2e-5) / f->ray_step;
         s.est2_hi = float(hi * hi * (1.0 + 1e-6));
         s.est2_lo = float(lo * lo * (1.0 - 1e-6));
+        s.d_hi = float(hi * (1.0 + 1e-5));
+        s.d_lo = float(lo * (1.0 - 1e-5));
         // the same decision made exactly, on the float length the reference multiplies (rasterizer.cpp:449)
         const double rs = f->ray_step, mn = f->min_ray_step;
         auto step_of = [&](float L) { return ref_clamp(double(L) * rs, mn, 0.01); };
@@ -104,6 +106,9 @@ int gk_build_scene(const GamerFrame *f, const GamerGalaxy *gal, const GamerCompo
         for (int i = 0; i < 4; i++) { d.rot[i] = g.rotmat[i]; d.arm[i] = float(g.arm[i]); }
         d.rot_identity = (g.rotmat[0] == 1.f && g.rotmat[1] == 0.f && g.rotmat[2] == 0.f && g.rotmat[3] == 0.f);
         d.axis_x = g.axis[0];
+        d.orient_y = d.rot_identity && g.orient[0] == 0.f && g.orient[1] == 1.f && g.orient[2] == 0.f &&
+                     d.axis_n[0] == 0.f && d.axis_n[1] == 1.f && d.axis_n[2] == 0.f;
+        d.inv_winding_b_d = 1.0 / g.winding_b;
         d.inv_axis_x = 1.0f / g.axis[0];
         d.inv_winding_b = float(1.0 / g.winding_b);
         d.winding_2n = float(2.0 * g.winding_n);

@@ -74,6 +74,10 @@ struct DGalaxy {
     int32_t any_arm;                  // some active component has arm != 0 (getWinding / getTheta are then needed)
     int32_t any_tshare;               // some components share a twirl angle (DComp::tgroup >= 0)
     double  winding_b, winding_n;     // getWinding is evaluated in double (its result feeds the twirl angle)
+    double  inv_winding_b_d;          // 1 / windingB (double)
+    int32_t orient_y;                 // orientation and twirl axis are exactly (0,1,0) and rotmat is the identity:
+                                      // dot(p, orient) = p.y, P = (p.x, 0, p.z), twirl_y (qtf.cuh) — every shipped galaxy
+    int32_t _padg;
 };
 
 struct DScene {
@@ -91,6 +95,7 @@ struct DScene {
     float   len_hi_thr;      // exact: the step is the upper clamp iff |p-cam| (float, as QVector3D::length) > len_hi_thr
     float   len_lo_thr;      // exact: ... the lower clamp iff |p-cam| <= len_lo_thr (tested second)
     float   alive_margin;    // bound on |(-dot(p - origin, dir)) - sum of steps| over a whole march (+inf: always test exactly)
+    float   d_hi, d_lo;      // |p - cam| above d_hi: the step is certainly 0.01; below d_lo: certainly minRayStep (sqrt of est2_*)
     DGalaxy gal[DEV_MAX_GALAXIES];
     DComp   comp[DEV_MAX_COMPONENTS];
 };

@@ -327,3 +327,106 @@ int main() {
     assert out[1] == "1 1 1 1", out[1]
     assert out[2] == "1", out[2]
     assert out[3] == "1 1 1 1 1", out[3]
+
+
+def test_qtf_twirl_y_equals_qt_sequence_and_oracle_shim(tmp_path):
+    """csrc/qtf.cuh compiled for the host: (1) twirl_y — the short sequence K1 uses when the galaxy's orientation is
+    exactly (0,1,0) — equals the full Qt 5.15 sequence twirl_qt (galaxycomponent.h:86-90 via QQuaternion::fromAxisAndAngle,
+    normalized, two operator*) bit for bit on 4 M random points/angles and never leaves its two known quaternion lengths;
+    (2) twirl_qt equals the oracle's Qt stand-in (oracle/qt5_math.h, what the reference's own sources were compiled
+    against) on every one of them: the half-angle sine / cosine are glibc's sinf / cosf restated (dmath::sincosf_glibc),
+    not the correctly rounded values, which differ from glibc's on 2.6 % of angles; (3) the three double constants that say when float(sqrt(len)) is 1 or 1 - 2^-24 are re-derived."""
+    import subprocess
+    src = tmp_path / "tw.cpp"
+    src.write_text(r'''
+#include "%s/gamer_b200/csrc/qtf.cuh"
+#include "%s/oracle/qt5_math.h"
+#include <cstdio>
+#include <cstdlib>
+#include <cmath>
+static double lowest(bool (*pred)(double), double lo, double hi) {   // smallest double in (lo, hi] with pred true
+    uint64_t a = dmath::to_bits(lo), b = dmath::to_bits(hi);
+    while (b - a > 1) { uint64_t m = a + (b - a) / 2; if (pred(dmath::from_bits(m))) b = m; else a = m; }
+    return dmath::from_bits(b);
+}
+int main() {
+    srand(7);
+    long bad = 0, notok = 0, shim_bad = 0, sc_diff = 0, n = 4000000;
+    const float ax[3] = {0.f, 1.f, 0.f};
+    for (long i = 0; i < n; i++) {
+        qtf::f3 p = {(float)(2.0 * rand() / RAND_MAX - 1), (float)(0.2 * rand() / RAND_MAX - 0.1), (float)(2.0 * rand() / RAND_MAX - 1)};
+        double tw = 1.3 * rand() / RAND_MAX * ((i & 1) ? 1 : -0.3);
+        if (i %% 1000 == 0) tw = 0.0;
+        bool ok;
+        qtf::f3 a = qtf::twirl_qt(ax, p, tw), b = qtf::twirl_y(p, tw, &ok);
+        notok += !ok;
+        bad += (a.x != b.x || a.y != b.y || a.z != b.z);
+        // the oracle's path: QQuaternion::fromAxisAndAngle(orientation, float(tw * 180)) * p with the host's sinf / cosf
+        const float deg = (float)(tw * 180.0);
+        q5::V3 r = q5::rotate(q5::from_axis_angle(q5::V3(0.f, 1.f, 0.f), deg), q5::V3(p.x, p.y, p.z));
+        float s, c; qtf::half_angle_sc(tw, s, c);
+        const float ha = q5::deg2rad_f(deg / 2.0f);
+        const bool same_sc = (s == std::sin(ha)) && (c == std::cos(ha));
+        sc_diff += !same_sc;
+        if (same_sc) shim_bad += (r.x != a.x || r.y != a.y || r.z != a.z);
+    }
+    printf("%%ld %%ld %%ld %%ld %%ld\n", bad, notok, shim_bad, sc_diff, n);
+    auto l_of = [](double d) { return (float)std::sqrt(d); };
+    (void)l_of;
+    const double one_lo = lowest([](double d) { return (float)std::sqrt(d) >= 1.0f; }, 0.9999, 1.0);
+    const double one_hi = lowest([](double d) { return (float)std::sqrt(d) > 1.0f; }, 1.0, 1.001);
+    const double below_lo = lowest([](double d) { return (float)std::sqrt(d) >= std::nextafter(1.0f, 0.0f); }, 0.9999, 1.0);
+    printf("%%d %%d %%d\n", one_lo == QT_LEN_ONE_LO, one_hi == QT_LEN_ONE_HI, below_lo == QT_LEN_BELOW_LO);
+    // x / (1 - 2^-24) is the next float away from zero for every normal float
+    long div_bad = 0; const float l = std::nextafter(1.0f, 0.0f);
+    for (long i = 0; i < 4000000; i++) {
+        float x = (float)(2.0 * rand() / RAND_MAX - 1) * std::ldexp(1.0f, -(rand() %% 40));
+        if (x == 0.f || std::fabs(x) < 1.2e-38f) continue;
+        div_bad += (x / l != std::nextafter(x, x > 0 ? 2.0f : -2.0f));
+    }
+    printf("%%ld\n", div_bad);
+}
+''' % (ROOT, ROOT))
+    exe = tmp_path / "tw"
+    subprocess.run(["g++", "-O2", "-ffp-contract=off", "-std=c++17", "-o", str(exe), str(src)], check=True)
+    out = subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.splitlines()
+    bad, notok, shim_bad, sc_diff, n = (int(v) for v in out[0].split())
+    assert bad == 0 and notok == 0, out[0]
+    assert shim_bad == 0 and sc_diff == 0, out[0]
+    assert out[1] == "1 1 1", out[1]
+    assert out[2] == "0", out[2]
+
+
+def test_sincosf_glibc_equals_host_libm(tmp_path):
+    """dmath::sincosf_glibc (csrc/dmath.cuh) — the restatement of glibc's sinf / cosf that K1's twirl uses — against the
+    host's libm on every 16th float of [0, 16) with both signs, plus every float of [0.01, 0.02) and [1, 1.25): bit
+    equal (the whole of [0, 16), 2.2 G values, was checked once the same way: one difference, the sign of sin(-0))."""
+    import subprocess
+    src = tmp_path / "sc.cpp"
+    src.write_text(r'''
+#include "%s/gamer_b200/csrc/dmath.cuh"
+#include <cstdio>
+#include <cstring>
+static inline uint32_t asu(float f) { uint32_t u; memcpy(&u, &f, 4); return u; }
+static inline float asf(uint32_t u) { float f; memcpy(&f, &u, 4); return f; }
+static long bad = 0, n = 0;
+static void range(float lo, float hi, uint32_t stride) {
+    for (uint32_t b = asu(lo); b < asu(hi); b += stride)
+        for (int sg = 0; sg < 2; sg++) {
+            const float y = asf(b | (sg ? 0x80000000u : 0));
+            if (y == 0.0f) continue;
+            float s, c; volatile float vy = y;
+            const bool ok = dmath::sincosf_glibc(y, s, c);
+            bad += !ok || asu(sinf(vy)) != asu(s) || asu(cosf(vy)) != asu(c); n++;
+        }
+}
+int main() {
+    range(0.0f, 16.0f, 16); range(0.01f, 0.02f, 1); range(1.0f, 1.25f, 1); range(16.0f, 119.0f, 64);
+    float s, c;
+    printf("%%ld %%ld %%d\n", bad, n, (int)dmath::sincosf_glibc(121.0f, s, c));
+}
+''' % ROOT)
+    exe = tmp_path / "sc"
+    subprocess.run(["g++", "-O2", "-ffp-contract=off", "-std=c++17", "-o", str(exe), str(src)], check=True)
+    bad, n, big = (int(v) for v in subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.split())
+    assert bad == 0 and n > 100_000_000 and big == 0, (bad, n, big)
