@@ -552,4 +552,20 @@ int gamer_b200_probe_ridged(gamer_ctx *ctx, const float *xyz, int32_t n, double 
     return GAMER_OK;
 }
 
+// ---- allocation-free variant of the fBm probe (include/gamer_b200.h) ------------------------------------------------
+int gamer_b200_fbm_static_max_points(void) { return gk::fbm_static_max_points(); }
+
+int gamer_b200_fbm_static(const float *xyz, int32_t n, int32_t octaves, double persistence, double scale, float *value_out) {
+    if (!xyz || !value_out || n <= 0 || octaves <= 0 || octaves > 32)
+        return set_err(nullptr, GAMER_E_ARG, "gamer_b200_fbm_static: null pointer, n <= 0 or octaves outside 1..32");
+    if (n > gk::fbm_static_max_points())
+        return set_err(nullptr, GAMER_E_ARG, "gamer_b200_fbm_static: n = " + std::to_string(n) + " points exceed the static scratch (" +
+                       std::to_string(gk::fbm_static_max_points()) + " points per call): split the call");
+    double amp = 1, maxamp = 0;
+    for (int o = 0; o < octaves; o++) { maxamp += amp; amp *= persistence; }
+    cudaError_t e = gk::fbm_static(xyz, n, octaves, (float)persistence, (float)(1.0 / maxamp), scale, value_out);
+    if (e != cudaSuccess) return cuda_fail(nullptr, e, "gamer_b200_fbm_static");
+    return GAMER_OK;
+}
+
 }  // extern "C"

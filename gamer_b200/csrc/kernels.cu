@@ -1,5 +1,6 @@
 // kernels.cu — K1 (ray march), K2 (post-process) and the noise probes, plus their launchers.
 // sm_100a only.  See march.cuh / noise.cuh for the design notes and the reference citations.
+#include <mutex>
 #include "march.cuh"
 #include "kernels.h"
 
@@ -765,6 +766,65 @@ cudaError_t launch_probe_ridged(const float *xyz, int n, int octaves, float lac,
     for (int i = 0; i < 16; i++) w.w[i] = (i < octaves) ? rw[i] : 0.f;
     kp_ridged<<<(n + 255) / 256, 256, GN_DYN_SMEM, st>>>(xyz, n, octaves, lac, offset, gain, w, out);
     return cudaGetLastError();
+}
+
+// ---- allocation-free fBm evaluation (gamer_b200_fbm_static) ---------------------------------------------------------
+// kp_fbm with its staging memory (the points going in, the values coming out) in a file-scope device array instead of
+// cudaMalloc'd buffers: for callers that may not allocate (CUDA graph capture, serving loops, harnesses that forbid it).
+// Every GPU that loads this library holds the array (GK_STATIC_BYTES = 4 MB) until the process exits. In HOST code the
+// array's name is only a stand-in for the symbol, not a device address: the address comes from cudaGetSymbolAddress,
+// once per device, with that device current (fbm_static_setup below). All calls share the array and it keeps the
+// last call's contents; nothing in it has to start at zero (the kernel writes every value it later reads back).
+}  // namespace gk
+
+#define GK_STATIC_MAX_POINTS 262144
+#define GK_STATIC_BYTES (4u * GK_STATIC_MAX_POINTS * sizeof(float))
+static __device__ __align__(256) float g_fbm_static_scratch[4 * GK_STATIC_MAX_POINTS];   // [0, 3 MAX): xyz; [3 MAX, 4 MAX): values
+
+namespace gk {
+
+int fbm_static_max_points() { return GK_STATIC_MAX_POINTS; }
+
+namespace {
+constexpr int kMaxDevices = 64;
+std::mutex g_static_mu;                    // one call at a time per process: the scratch is shared
+float *g_static_ptr[kMaxDevices];          // device address of g_fbm_static_scratch, per device
+bool g_static_ready[kMaxDevices];
+
+// once per device, with that device current
+cudaError_t fbm_static_setup(int dev) {
+    if (g_static_ready[dev]) return cudaSuccess;
+    cudaError_t e = prepare_device();      // kp_fbm needs > 48 KB of dynamic shared memory: an attribute, not an allocation
+    if (e != cudaSuccess) return e;
+    float *ptr = nullptr;
+    e = cudaGetSymbolAddress((void **)&ptr, g_fbm_static_scratch);
+    if (e != cudaSuccess) return e;
+    if (!ptr) return cudaErrorInvalidSymbol;
+    g_static_ptr[dev] = ptr;
+    g_static_ready[dev] = true;
+    return cudaSuccess;
+}
+}  // namespace
+
+// Runs on the calling thread's current device, on the legacy default stream; blocking. No cudaMalloc / cudaFree /
+// allocating library call. The caller (api.cu) has checked 0 < n <= GK_STATIC_MAX_POINTS.
+cudaError_t fbm_static(const float *xyz_host, int n, int octaves, float pers, float inv_maxamp, double scale, float *out_host) {
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= kMaxDevices) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lock(g_static_mu);
+    e = fbm_static_setup(dev);
+    if (e != cudaSuccess) return e;
+    float *xyz_dev = g_static_ptr[dev], *val_dev = g_static_ptr[dev] + 3 * (size_t)GK_STATIC_MAX_POINTS;
+    e = cudaMemcpyAsync(xyz_dev, xyz_host, (size_t)n * 3 * sizeof(float), cudaMemcpyHostToDevice, cudaStreamLegacy);
+    if (e != cudaSuccess) return e;
+    kp_fbm<<<(n + 255) / 256, 256, GN_DYN_SMEM, cudaStreamLegacy>>>(xyz_dev, n, octaves, pers, inv_maxamp, scale, val_dev);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+    e = cudaMemcpyAsync(out_host, val_dev, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, cudaStreamLegacy);
+    if (e != cudaSuccess) return e;
+    return cudaStreamSynchronize(cudaStreamLegacy);
 }
 
 }  // namespace gk

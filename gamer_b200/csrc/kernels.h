@@ -18,4 +18,7 @@ cudaError_t launch_probe_fbm(const float *xyz, int n, int octaves, float pers, f
                              cudaStream_t st);
 cudaError_t launch_probe_ridged(const float *xyz, int n, int octaves, float lac, float offset, float gain, const float *rw,
                                 float *out, cudaStream_t st);
+// allocation-free fBm evaluation on the current device (scratch in a static __device__ array of kernels.cu)
+int fbm_static_max_points();
+cudaError_t fbm_static(const float *xyz_host, int n, int octaves, float pers, float inv_maxamp, double scale, float *out_host);
 }  // namespace gk

@@ -235,6 +235,23 @@ int  gamer_b200_probe_ridged(gamer_ctx *ctx, const float *xyz, int32_t n, double
                              int32_t octaves, double lacunarity, double offset, double gain,
                              float *value_out);
 
+/* allocation-free entry point ------------------------------------------------------------------
+ * NO COUNTERPART IN THE REFERENCE: added for callers that cannot
+ * call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * The same evaluation as gamer_b200_probe_fbm (Noise::octave_noise_3d, noise.cpp:162-180, at n points), but
+ * without a context and without any cudaMalloc / cudaFree / allocating library call: the points and the
+ * values are staged in a static device array inside the library (4 MB, held by every GPU that loads the
+ * library until the process exits). Runs on the calling thread's CURRENT CUDA device, on the legacy default
+ * stream, and blocks until value_out (host, n floats) is written; xyz is host memory, 3 floats per point.
+ *   limit   n <= gamer_b200_fbm_static_max_points() (262144); a larger n returns GAMER_E_ARG with a message
+ *           naming the limit (gamer_b200_last_error(NULL)) — split the call.
+ *   sharing every call uses the same array, which keeps the previous call's contents (nothing in it needs
+ *           to start at zero). Calls are serialised inside one process; calls of DIFFERENT processes or
+ *           any other work that overlaps on the GPU and touches the array would race. */
+int  gamer_b200_fbm_static_max_points(void);
+int  gamer_b200_fbm_static(const float *xyz, int32_t n, int32_t octaves, double persistence, double scale,
+                           float *value_out);
+
 #ifdef __cplusplus
 }
 #endif
