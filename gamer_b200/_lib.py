@@ -114,8 +114,9 @@ def load():
     lib.gamer_b200_star_list.argtypes = [C.c_int32, C.c_int32, C.c_double, C.c_double, C.c_double, C.c_uint64,
                                          C.POINTER(GamerStar)]
     lib.gamer_b200_render_stars.argtypes = [p, C.POINTER(GamerStar), C.c_int32, p]
-    lib.gamer_b200_fbm_static_max_points.restype = C.c_int
-    lib.gamer_b200_fbm_static.argtypes = [p, C.c_int32, C.c_int32, C.c_double, C.c_double, p]
+    if hasattr(lib, "gamer_b200_fbm_static"):       # absent only from older A/B builds selected through GAMER_B200_LIB
+        lib.gamer_b200_fbm_static_max_points.restype = C.c_int
+        lib.gamer_b200_fbm_static.argtypes = [p, C.c_int32, C.c_int32, C.c_double, C.c_double, p]
     _lib = lib
     return lib
 

@@ -26,39 +26,52 @@ struct NoiseCtx {
 // The per-thread ray record of march(): K1_REC_WORDS floats per thread in shared memory behind the noise tables,
 // word k of thread t at [k][t] (conflict free). volatile: every access is a real load or store.
 // Words: 0-2 p, 3-5 dir, 6-8 origin, 9-11 camera relative to the galaxy, 12 length, 13 loop bound (-inf: no ray),
-// 14 step, 15 weight, 16 distance marched (+inf: no ray), 17 twirl group of the point in 18-20 (-1: none yet).
-#ifdef K1_NO_TWIRL_CACHE
-#define K1_REC_WORDS 17
-#else
-#define K1_REC_WORDS 21
-#endif
+// 14 step, 15 weight, 16 distance marched (+inf: no ray), 17 / 18 the fast-sample windows (marched < [17]: the step is
+// certainly 0.01 and the ray alive; marched > [18]: certainly minRayStep), 19 / 20 the loop bound for those two steps,
+// 21 twirl group of the point in 22-24 (-1: none yet).
+#define REC_HI_LIM 17
+#define REC_LO_FROM 18
+#define REC_THR_HI 19
+#define REC_THR_LO 20
+#define REC_TG 21
+// values of ONE in-slab sample shared by every component of the galaxy. They live here and not in registers because
+// they are needed on both sides of the noise calls: what ptxas cannot keep in a register across a call it keeps in
+// LOCAL memory for its whole life, and with 768 threads a 96-byte stack is 72 KB per SM against 28 KB of L1 (ncu: 61 %
+// local hit rate, long-scoreboard stalls on every reload). A shared-memory load costs one issue slot and ~25 cycles.
+#define REC_DOTT 25      // height above the plane along the axis (exact)
+#define REC_PLEN 26      // |P| fast float
+#define REC_W 27         // getWinding(radius) narrowed
+#define REC_WD 28        // ... in double (it feeds the twirl angle): words 28, 29
+#define REC_THETA 30     // atan2(q.x, q.z), q = rotmat * P
+#define REC_IVAL 31      // val * weight of the component being evaluated (live across its noise call)
+#define REC_K 32         // index of the component being evaluated (the loop counter, as float bits)
+#define K1_REC_WORDS 33
+static_assert(GN_DYN_SMEM + K1_REC_WORDS * K1_THREADS * 4u <= 232448u, "tables + ray records exceed the 227 KB a CTA can have");
 struct Rec {
     volatile float *base;
     __device__ __forceinline__ volatile float &operator[](int k) const { return base[k * K1_THREADS]; }
 };
 #define K1_DYN_SMEM (GN_DYN_SMEM + K1_REC_WORDS * K1_THREADS * 4u)
 
-struct Shared1 {          // values of one sample shared by every component of a galaxy
-    f3 p;                 // sample position (exact)
-    float dott;           // height above the plane along the axis (exact)
-    float Plen;           // |P| fast float
-    float weight;         // step * 200
-    float W;              // getWinding(radius), narrowed
-    double Wd;            // getWinding(radius) in double: it feeds the twirl angle
-    float theta0;         // atan2(q.x, q.z), q = rotmat * P
-};
+__device__ __forceinline__ double rec_get_d(const Rec rec, int k) {
+    return __hiloint2double(__float_as_int(rec[k + 1]), __float_as_int(rec[k]));
+}
+__device__ __forceinline__ void rec_set_d(const Rec rec, int k, double v) {
+    rec[k] = __int_as_float(__double2loint(v)); rec[k + 1] = __int_as_float(__double2hiint(v));
+}
 
 // getWinding (galaxycomponent.h:156-165) and the atan2 of getTheta (:150-153), once per sample
-__device__ __forceinline__ void arm_base(const DGalaxy &g, Shared1 &s, f3 P) {
+__device__ __forceinline__ void arm_base(const DGalaxy &g, const Rec rec, f3 P) {
     // radius exactly as getRadius returns it: float |P| (double sqrt) / float axis.x, then the
     // reference's double expression atan(exp(-0.25/(0.5*r))/windingB)*2*windingN
     const float radius = fdiv_nc(v_length(P), g.axis_x, frcp_nc(g.axis_x));
     const double r = __dadd_rn((double)radius, 0.05);
     const double e = dmath::exp_nc(dmath::div_nc(-0.25, __dmul_rn(0.5, r)));
-    s.Wd = __dmul_rn(__dmul_rn(dmath::atan_nc(dmath::div_nc(e, g.winding_b)), 2.0), g.winding_n);
-    s.W = (float)s.Wd;
+    const double Wd = __dmul_rn(__dmul_rn(dmath::atan_nc(dmath::div_nc(e, g.winding_b)), 2.0), g.winding_n);
+    rec_set_d(rec, REC_WD, Wd);
+    rec[REC_W] = (float)Wd;
     f3 q = g.rot_identity ? P : q_rotate(g.rot, P);
-    s.theta0 = dmath::atan2f_fast(q.x, q.z);
+    rec[REC_THETA] = dmath::atan2f_fast(q.x, q.z);
 }
 
 // findDifference (galaxycomponent.h:103-118) with M_PI = 3.14159265 (util.h:20)
@@ -72,8 +85,8 @@ __device__ __forceinline__ float find_difference(float d) {
 }
 
 // calculateArmValue (galaxycomponent.h:120-146). max_j pow(1 - v_j/pi, e) = pow(1 - min_j v_j/pi, e) for e > 0.
-__device__ __forceinline__ float arm_value(const DGalaxy &g, const DComp &c, const Shared1 &s) {
-    float base = s.W + s.theta0 + c.delta;    // winding - (-(theta) + disp) = W + theta + delta - disp
+__device__ __forceinline__ float arm_value(const DGalaxy &g, const DComp &c, const Rec rec) {
+    float base = rec[REC_W] + rec[REC_THETA] + c.delta;    // winding - (-(theta) + disp) = W + theta + delta - disp
     float v = find_difference(base - g.arm[0]);
     bool want_min = c.arm15 > 0.0f;
     for (int j = 1; j < g.no_arms; j++) {
@@ -92,6 +105,14 @@ __device__ __forceinline__ void bulge_add(float k, float r0, float sr, float sg,
     float v = ex2a(fmaf(-1.4426950408889634f, ex2a(0.25f * L), -0.855f * L)) - 0.05f;
     float i = fmaxf(k * v, 0.0f);
     Ir = fmaf(i, sr, Ir); Ig = fmaf(i, sg, Ig); Ib = fmaf(i, sb, Ib);
+}
+
+// the scalar of bulge_add alone: max(k (rad^-0.855 exp(-rad^0.25) - 0.05), 0)
+__device__ __forceinline__ float bulge_term(float k, float r0, float plen3) {
+    float rad = fmaf(plen3 + 0.01f, r0, 0.01f);
+    float L = lg2a(rad);
+    float v = ex2a(fmaf(-1.4426950408889634f, ex2a(0.25f * L), -0.855f * L)) - 0.05f;
+    return fmaxf(k * v, 0.0f);
 }
 
 // Stars with noiseOffset != 0 (galaxycomponents.cpp:144-148): two 4-octave helpers, persistence -2
@@ -125,17 +146,18 @@ __device__ __forceinline__ f3 twirl_point(const DGalaxy &g, f3 p, double winding
 }
 
 template <bool COUNT, bool ORIENT_Y>
-__device__ __forceinline__ void eval_component(const DScene &sc, const DGalaxy &g, const DComp &c, Shared1 &s, const Rec rec,
+__device__ __forceinline__ void eval_component(const DScene &sc, const DGalaxy &g, const DComp &c, const Rec rec,
                                                const NoiseCtx &nz, float &Ir, float &Ig, float &Ib, Counts &cn) {
     const float rs = sc.ray_step_f;
     if (c.cls == GAMER_CLASS_BULGE) {   // galaxycomponents.cpp:5-25 — evaluated at every sample, no gates
-        bulge_add(c.strength * c.iscale * rs * s.weight, c.r0, c.spec[0], c.spec[1], c.spec[2],
-                  sqrta(fmaf(s.p.z, s.p.z, fmaf(s.p.y, s.p.y, s.p.x * s.p.x))), Ir, Ig, Ib);
+        const f3 pb = {rec[0], rec[1], rec[2]};
+        bulge_add(c.strength * c.iscale * rs * rec[15], c.r0, c.spec[0], c.spec[1], c.spec[2],
+                  sqrta(fmaf(pb.z, pb.z, fmaf(pb.y, pb.y, pb.x * pb.x))), Ir, Ig, Ib);
         if (COUNT) cn.evals++;
         return;
     }
     // ---- slab gate: h = |dott/z0| > 2 -> 0 (galaxycomponent.h:61-64), exact --------------------
-    float ad = fabsf(s.dott);
+    float ad = fabsf(rec[REC_DOTT]);
     if (!(ad <= c.h_gate)) return;
     float e = fexp(ad * c.inv_z0);
     float ch = 0.5f * (e + rcpa(e));
@@ -143,18 +165,20 @@ __device__ __forceinline__ void eval_component(const DScene &sc, const DGalaxy &
     if (!(z > 0.01f)) return;
     // ---- radial gate: intensity > 0.001 (galaxycomponent.cpp:62-65), exact -----------------------
     bool pass;
-    if (s.Plen < c.plen_lo) pass = true;
-    else if (s.Plen > c.plen_hi) pass = false;
+    const float Plen = rec[REC_PLEN];
+    if (Plen < c.plen_lo) pass = true;
+    else if (Plen > c.plen_hi) pass = false;
     else {      // rare: inside the band where only the exact |P| decides; P = p - orient * dott like getRadius
         const f3 orient = {g.orient[0], g.orient[1], g.orient[2]};
-        const f3 Pq = ORIENT_Y ? f3{s.p.x, 0.0f, s.p.z} : v_sub(s.p, v_mul(orient, s.dott));
+        const f3 pq = {rec[0], rec[1], rec[2]};
+        const f3 Pq = ORIENT_Y ? f3{pq.x, 0.0f, pq.z} : v_sub(pq, v_mul(orient, rec[REC_DOTT]));
         pass = v_length(Pq) <= c.plen_thr;
     }
     if (!pass) return;
-    float intensity = fminf(fmaxf(ex2(s.Plen * c.k_radial) - 0.01f, 0.0f), 0.1f);
+    float intensity = fminf(fmaxf(ex2(Plen * c.k_radial) - 0.01f, 0.0f), 0.1f);
     float scale = 1.0f;
     if (!(c.flags & DC_INNER_ZERO)) {
-        float x = fminf(fmaxf(s.Plen * g.inv_axis_x * c.inv_inner, 0.0f), 1.0f);
+        float x = fminf(fmaxf(Plen * g.inv_axis_x * c.inv_inner, 0.0f), 1.0f);
         float sm = x * x * (3.0f - 2.0f * x);
         sm *= sm;
         scale = sm * sm;
@@ -162,12 +186,15 @@ __device__ __forceinline__ void eval_component(const DScene &sc, const DGalaxy &
     float armv = 1.0f;
     double winding = 0.0;
     if (c.flags & DC_HAS_ARM) {
-        armv = arm_value(g, c, s);
-        if (c.flags & DC_HAS_WINDING) winding = __dmul_rn(s.Wd, c.winding_d);
+        armv = arm_value(g, c, rec);
+        if (c.flags & DC_HAS_WINDING) winding = __dmul_rn(rec_get_d(rec, REC_WD), c.winding_d);
     }
     float val = c.strength * scale * armv * z * intensity;
-    float ival = val * s.weight;
-    if (!(ival > 0.0005f)) return;
+    {
+        const float ival0 = val * rec[15];
+        if (!(ival0 > 0.0005f)) return;
+        rec[REC_IVAL] = ival0;
+    }
     if (COUNT) cn.evals++;
 
     // One twirl and ONE noise evaluation site for every class (keeps the hot loop small enough for the
@@ -175,9 +202,10 @@ __device__ __forceinline__ void eval_component(const DScene &sc, const DGalaxy &
     const int cls = c.cls;
     if (cls > GAMER_CLASS_STARS) return;              // "stars small": no-op (see gamer_b200.h)
     const bool is_ridged = (cls == GAMER_CLASS_DUST2) | (cls == GAMER_CLASS_DUST_POSITIVE);
-    f3 r = s.p;
+    const f3 sp = {rec[0], rec[1], rec[2]};
+    f3 r = sp;
 #ifdef K1_NO_TWIRL_CACHE
-    if (cls != GAMER_CLASS_STARS) r = twirl_point<ORIENT_Y>(g, s.p, winding);
+    if (cls != GAMER_CLASS_STARS) r = twirl_point<ORIENT_Y>(g, sp, winding);
 #else
     // components with the same winding factor twirl the sample to the same point (DComp::tgroup, scene_build.cpp):
     // the point of the last twirl of this sample sits in the ray record, words 17 (group) and 18-20
@@ -185,15 +213,19 @@ __device__ __forceinline__ void eval_component(const DScene &sc, const DGalaxy &
         // decided for the lanes that are here together: a lane-wise branch would send the two sides through the
         // noise call below one after the other (a lane that has the point recomputes the same bits)
         const float tg = (float)c.tgroup;
-        const bool have = c.tgroup >= 0 && rec[17] == tg;
-        if (__all_sync(__activemask(), have)) r = {rec[18], rec[19], rec[20]};
+        const bool have = c.tgroup >= 0 && rec[REC_TG] == tg;
+        if (__all_sync(__activemask(), have)) r = {rec[REC_TG + 1], rec[REC_TG + 2], rec[REC_TG + 3]};
         else {
-            r = twirl_point<ORIENT_Y>(g, s.p, winding);
-            if (c.tgroup >= 0) { rec[17] = tg; rec[18] = r.x; rec[19] = r.y; rec[20] = r.z; }
+            r = twirl_point<ORIENT_Y>(g, sp, winding);
+            if (c.tgroup >= 0) { rec[REC_TG] = tg; rec[REC_TG + 1] = r.x; rec[REC_TG + 2] = r.y; rec[REC_TG + 3] = r.z; }
         }
     }
 #endif
     float n;
+#ifdef K1_DIAG_NONOISE                  // timing experiment only (results are wrong): everything but the noise octaves
+    n = 0.37f + 1e-3f * r.x;
+    if (COUNT) cn.octaves += is_ridged ? DEV_RIDGED_OCTAVES : c.octaves;
+#else
     if (is_ridged) {                    // getRidgedMf(r * scale, ks, 9, 2.5, noiseOffset, noiseTilt)
         n = gnoise::ridged(nz.lane4, __fmul_rn(r.x, c.rscale), __fmul_rn(r.y, c.rscale), __fmul_rn(r.z, c.rscale),
                            DEV_RIDGED_OCTAVES, 2.5f, c.noise_offset, c.noise_tilt, c.rw[0], c.rwq);
@@ -202,9 +234,11 @@ __device__ __forceinline__ void eval_component(const DScene &sc, const DGalaxy &
         n = gnoise::fbm(nz.lane4, r.x, r.y, r.z, c.nscale, c.octaves, c.pers, c.inv_maxamp);
         if (COUNT) cn.octaves += c.octaves;
     }
+#endif
 
     float k;                            // emission coefficient (k >= 0 classes) or absorption exponent
     bool absorb = false;
+    const float ival = rec[REC_IVAL];
     switch (cls) {
     case GAMER_CLASS_DISK: {            // galaxycomponents.cpp:41-59
         float p2 = fpow(fmaxf(fabsf(n), 0.01f), c.noise_tilt) + c.noise_offset;
@@ -232,7 +266,10 @@ __device__ __forceinline__ void eval_component(const DScene &sc, const DGalaxy &
     default: {                          // GAMER_CLASS_STARS, galaxycomponents.cpp:139-155
         float add = 0.0f;
         if (c.flags & DC_HAS_NOFF) {
-            add = stars_helper_octaves(g, c.noise_offset, s.p.x, s.p.y, s.p.z, nz.lane4, winding);
+            // (the winding is formed again here rather than kept across the noise call above)
+            double w2 = 0.0;
+            if ((c.flags & DC_HAS_ARM) && (c.flags & DC_HAS_WINDING)) w2 = __dmul_rn(rec_get_d(rec, REC_WD), c.winding_d);
+            add = stars_helper_octaves(g, c.noise_offset, rec[0], rec[1], rec[2], nz.lane4, w2);
             if (COUNT) cn.octaves += 8;
         }
         float base = fabsf(n) + 1.0f + add;
@@ -277,6 +314,18 @@ __device__ __forceinline__ void march(const DScene &sc, const DGalaxy &g, const 
         rec[16] = active ? 0.0f : INFINITY;            // distance marched so far (estimate, see the run loop)
         // the first test uses step = rayStep; a ray that is not marched has no bound at all
         rec[13] = active ? __double2float_ru(__dadd_rn((double)length_f, sc.ray_step)) : -INFINITY;
+        // Every ray starts at the camera, so p - camera is parallel to dir and |p - camera| = dist0 - (distance marched)
+        // up to rounding (bounded by sc.alive_margin like the loop test): it falls monotonically along the march. The
+        // step clamp(|p - camera| * rayStep, minRayStep, 0.01) is therefore CERTAINLY 0.01 while marched < dist0 - d_hi -
+        // margin and certainly minRayStep once marched > dist0 - d_lo + margin: samples inside those windows need
+        // neither the distance nor the exact loop test (the fast sample of the run loop).
+        const f3 oc = v_sub(origin, camrel);
+        const float dist0 = sqrta(fmaf(oc.z, oc.z, fmaf(oc.y, oc.y, oc.x * oc.x)));
+        const float sure_below = length_f - sc.alive_margin;
+        rec[REC_HI_LIM] = (active && g.fast_ok) ? fminf(dist0 - sc.d_hi - sc.alive_margin, sure_below) : -INFINITY;
+        rec[REC_LO_FROM] = (active && g.fast_ok) ? dist0 - sc.d_lo + sc.alive_margin : INFINITY;
+        rec[REC_THR_HI] = __double2float_ru(__dadd_rn((double)length_f, 0.01));
+        rec[REC_THR_LO] = __double2float_ru(__dadd_rn((double)length_f, sc.min_ray_step));
     }
     if (COUNT && active) cn.rays++;
     const bool fast_ok = g.fast_ok != 0;
@@ -303,8 +352,8 @@ __device__ __forceinline__ void march(const DScene &sc, const DGalaxy &g, const 
             // rounding involved), so the loop test dot(p - origin, ll) < thr is evaluated as -dot(p - origin, dir) < thr.
             const f3 orient = {g.orient[0], g.orient[1], g.orient[2]};
             // the two clamped step states (rasterizer.cpp:449): step = 0.01 and step = minRayStep
-            const float thr_hi = __double2float_ru(__dadd_rn((double)length_f, 0.01));
-            const float thr_lo = __double2float_ru(__dadd_rn((double)length_f, sc.min_ray_step));
+            const float thr_hi = rec[REC_THR_HI], thr_lo = rec[REC_THR_LO];
+            const float hi_lim = rec[REC_HI_LIM], lo_from = rec[REC_LO_FROM];
             const float s_hi = __double2float_rn(0.01), s_lo = __double2float_rn(sc.min_ray_step);
             const float w_hi = (float)(0.01 * 200.0), w_lo = (float)(sc.min_ray_step * 200.0);
             // bulges of this galaxy in registers
@@ -317,17 +366,57 @@ __device__ __forceinline__ void march(const DScene &sc, const DGalaxy &g, const 
                 const DComp &c = sc.comp[g.bulge_idx[1]];
                 bk1 = c.strength * c.iscale * sc.ray_step_f; br1 = c.r0; bs1r = c.spec[0]; bs1g = c.spec[1]; bs1b = c.spec[2];
             }
+            // Fast samples. A lane may take them while marched < lim: the ray is then certainly alive and its step
+            // certainly the clamped one of the lane's last general sample (windows of the ray record), so ds = dir * step
+            // and the bulge coefficients kw = k * weight of that sample still hold. The warp takes a fast sample only when
+            // EVERY lane that still has a ray can, and is off the slab: one vote, no distance, no loop test, no step logic.
+            float lim = -INFINITY, kw0 = 0.f, kw1 = 0.f;
+            f3 ds = {0.f, 0.f, 0.f};
+            unsigned idle = 0u;                     // lanes whose ray has ended (or never began)
             for (;;) {
+#ifndef K1_NO_FAST_RUN
+                {   // two fast samples per trip: the bulge term is a serial chain of four MUFU latencies (sqrt, lg2, ex2,
+                    // ex2); the chains of two consecutive samples are independent and overlap, and one vote serves both
+                    const f3 p1 = v_sub(p, ds);
+                    const float m1 = marched + stepf;
+                    const float dott0 = ORIENT_Y ? p.y : v_dot(p, orient), dott1 = ORIENT_Y ? p1.y : v_dot(p1, orient);
+#ifdef K1_DIAG_NOSLAB
+                    const bool go = m1 < lim && dott0 == dott0 && dott1 == dott1;
+#else
+                    const bool go = m1 < lim && !(fabsf(dott0) <= g.slab_gate) && !(fabsf(dott1) <= g.slab_gate);
+#endif
+                    const unsigned b = __ballot_sync(FULL, go);
+                    if (b != 0u && (b | idle) == FULL) {
+                        if (go) {
+                            const float q0 = sqrta(fmaf(p.z, p.z, fmaf(p.y, p.y, p.x * p.x)));
+                            const float q1 = sqrta(fmaf(p1.z, p1.z, fmaf(p1.y, p1.y, p1.x * p1.x)));
+                            const float i00 = bulge_term(kw0, br0, q0), i01 = bulge_term(kw0, br0, q1);
+                            float i10 = 0.f, i11 = 0.f;
+                            if (g.n_bulge > 1) { i10 = bulge_term(kw1, br1, q0); i11 = bulge_term(kw1, br1, q1); }
+                            // accumulation in the reference's order: sample 0 (bulge 0, bulge 1), then sample 1
+                            Ir = fmaf(i00, bs0r, Ir); Ig = fmaf(i00, bs0g, Ig); Ib = fmaf(i00, bs0b, Ib);
+                            if (g.n_bulge > 1) { Ir = fmaf(i10, bs1r, Ir); Ig = fmaf(i10, bs1g, Ig); Ib = fmaf(i10, bs1b, Ib); }
+                            Ir = fmaf(i01, bs0r, Ir); Ig = fmaf(i01, bs0g, Ig); Ib = fmaf(i01, bs0b, Ib);
+                            if (g.n_bulge > 1) { Ir = fmaf(i11, bs1r, Ir); Ig = fmaf(i11, bs1g, Ig); Ib = fmaf(i11, bs1b, Ib); }
+                            if (COUNT) { cn.evals += 2 * g.n_bulge; cn.samples += 2; cn.gates += 2 * (g.comp_count + g.noop_count); }
+                            p = v_sub(p1, ds);
+                            marched = m1 + stepf;
+                        }
+                        continue;
+                    }
+                }
+#endif
                 const bool alive = marched < sure_below || -v_dot(v_sub(p, origin), dir) < thr;
                 if (alive) {
                     // step = clamp(|p - camera| * rayStep, minRayStep, 0.01)
                     const f3 dc = v_sub(p, camrel_);
                     const float e2 = fmaf(dc.z, dc.z, fmaf(dc.y, dc.y, dc.x * dc.x));
-                    if (e2 > sc.est2_hi) { stepf = s_hi; weight = w_hi; thr = thr_hi; }
-                    else if (e2 < sc.est2_lo) { stepf = s_lo; weight = w_lo; thr = thr_lo; }
+                    if (e2 > sc.est2_hi) { stepf = s_hi; weight = w_hi; thr = thr_hi; lim = hi_lim; }
+                    else if (e2 < sc.est2_lo) { stepf = s_lo; weight = w_lo; thr = thr_lo; lim = marched > lo_from ? sure_below : -INFINITY; }
                     else {
                         // the clamps as exact float thresholds on the length (scene_build.cpp), FP64 only in between
                         const float len_f = v_length(dc);
+                        lim = -INFINITY;
                         if (len_f > sc.len_hi_thr) { stepf = s_hi; weight = w_hi; thr = thr_hi; }
                         else if (len_f <= sc.len_lo_thr) { stepf = s_lo; weight = w_lo; thr = thr_lo; }
                         else {
@@ -340,17 +429,24 @@ __device__ __forceinline__ void march(const DScene &sc, const DGalaxy &g, const 
                     // getRadius (galaxycomponent.h:72-76); for orient = (0,1,0): (p.x*0 + p.y*1) + p.z*0 = p.y
                     const float dott = ORIENT_Y ? p.y : v_dot(p, orient);
                     need = !(fast_ok && !(fabsf(dott) <= g.slab_gate));           // an in-slab sample at p
+#ifdef K1_DIAG_NOSLAB                   // timing experiment only (results are wrong): the march and the bulge alone
+                    need = false;
+#endif
                     if (!need) {
                         const float plen3 = sqrta(fmaf(p.z, p.z, fmaf(p.y, p.y, p.x * p.x)));
-                        bulge_add(bk0 * weight, br0, bs0r, bs0g, bs0b, plen3, Ir, Ig, Ib);
-                        if (g.n_bulge > 1) bulge_add(bk1 * weight, br1, bs1r, bs1g, bs1b, plen3, Ir, Ig, Ib);
+                        kw0 = bk0 * weight; kw1 = bk1 * weight;
+                        bulge_add(kw0, br0, bs0r, bs0g, bs0b, plen3, Ir, Ig, Ib);
+                        if (g.n_bulge > 1) bulge_add(kw1, br1, bs1r, bs1g, bs1b, plen3, Ir, Ig, Ib);
                         if (COUNT) { cn.evals += g.n_bulge; cn.samples++; cn.gates += g.comp_count + g.noop_count; }
-                        p = v_sub(p, v_mul(dir, stepf));
+                        ds = v_mul(dir, stepf);
+                        p = v_sub(p, ds);
                         marched += stepf;
                         // I only grew: the floor of the general path is the identity here (scene_build.cpp, fast_ok)
                     }
                 }
-                any_alive = __any_sync(FULL, alive);
+                const unsigned alive_mask = __ballot_sync(FULL, alive);
+                idle = ~alive_mask;
+                any_alive = alive_mask != 0u;
                 if (__any_sync(FULL, need) || !any_alive) break;
             }
             rec[0] = p.x; rec[1] = p.y; rec[2] = p.z;
@@ -359,21 +455,22 @@ __device__ __forceinline__ void march(const DScene &sc, const DGalaxy &g, const 
         if (!any_alive) break;
         if (need) {   // ---- one in-slab sample ------------------------------------------------------------------
             const f3 orient = {g.orient[0], g.orient[1], g.orient[2]};
-            Shared1 s;
-            s.p = {rec[0], rec[1], rec[2]};
-            s.dott = ORIENT_Y ? s.p.y : v_dot(s.p, orient);
-            const f3 P = ORIENT_Y ? f3{s.p.x, 0.0f, s.p.z} : v_sub(s.p, v_mul(orient, s.dott));   // p.y - p.y*1 = 0
-            s.Plen = sqrta(fmaf(P.z, P.z, fmaf(P.y, P.y, P.x * P.x)));
-            s.weight = rec[15];
-            // getWinding / getTheta once per sample, up front: a lazily set flag would have to live (in local memory)
-            // across every noise call of the sample
-            if (g.any_arm) arm_base(g, s, P);
+            {
+                const f3 sp = {rec[0], rec[1], rec[2]};
+                const float dott = ORIENT_Y ? sp.y : v_dot(sp, orient);
+                const f3 P = ORIENT_Y ? f3{sp.x, 0.0f, sp.z} : v_sub(sp, v_mul(orient, dott));   // p.y - p.y*1 = 0
+                rec[REC_DOTT] = dott;
+                rec[REC_PLEN] = sqrta(fmaf(P.z, P.z, fmaf(P.y, P.y, P.x * P.x)));
+                // getWinding / getTheta once per sample, up front
+                if (g.any_arm) arm_base(g, rec, P);
+            }
 #ifndef K1_NO_TWIRL_CACHE
-            if (g.any_tshare) rec[17] = -1.0f;
+            if (g.any_tshare) rec[REC_TG] = -1.0f;
 #endif
-#pragma unroll 1
-            for (int k = 0; k < g.comp_count; k++)
-                eval_component<COUNT, ORIENT_Y>(sc, g, sc.comp[g.comp_begin + k], s, rec, nz, Ir, Ig, Ib, cn);
+            for (int k = 0; k < g.comp_count; k = __float_as_int(rec[REC_K]) + 1) {
+                rec[REC_K] = __int_as_float(k);
+                eval_component<COUNT, ORIENT_Y>(sc, g, sc.comp[g.comp_begin + k], rec, nz, Ir, Ig, Ib, cn);
+            }
             if (COUNT) { cn.samples++; cn.gates += g.comp_count + g.noop_count; }
             const f3 dir = {rec[3], rec[4], rec[5]};
             const f3 p0 = {rec[0], rec[1], rec[2]};

@@ -169,6 +169,11 @@ __device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) { f32x2 r; asm("mul.rn.f
 //     predicated 128-bit gradient loads each (exactly one of them executes) — no address selects;
 //   * max(t, 0) is the saturation modifier of the last FMA of t (t <= 0.6 < 1, so the upper clamp never acts);
 //   * corners are processed as pairs (0,3) and (1,2) with packed FFMA2 / FMUL2.
+#ifdef GN_DIAG_LDS32   // timing experiment only (results are wrong): a quarter of the shared-memory wavefronts per gradient
+#define GN_LDG(r0, r1, r2, r3, addr) "ld.shared.b32 " r0 ", [" addr "];\n\tmov.b32 " r1 ", " r0 ";\n\tmov.b32 " r2 ", " r0 ";\n\tmov.b32 " r3 ", " r0 ";\n\t"
+#else
+#define GN_LDG(r0, r1, r2, r3, addr) "ld.shared.v4.b32 {" r0 "," r1 "," r2 "," r3 "}, [" addr "];\n\t"
+#endif
 template <bool PROBE>
 __device__ __forceinline__ float simplex_cell(uint32_t lane4, uint32_t lane16, uint32_t I7, uint32_t J7, uint32_t K7,
                                               float fu, float fv, float fw, Lattice *lat) {
@@ -220,14 +225,14 @@ __device__ __forceinline__ float simplex_cell(uint32_t lane4, uint32_t lane16, u
         "add.u32 c10, B10, %29;\n\t"
         "add.u32 c01, B01, %29;\n\t"
         "add.u32 c11, B11, %29;\n\t"
-        "ld.shared.v4.b32 {%9,%10,%11,%12}, [c00+" GN_STR(GN_GRAD_IMM) "];\n\t"
-        "ld.shared.v4.b32 {%21,%22,%23,%24}, [c11+" GN_STR(GN_GRAD_IMM) "+128];\n\t"
-        "@i1 ld.shared.v4.b32 {%13,%14,%15,%16}, [c00+" GN_STR(GN_GRAD_IMM) "+128];\n\t"
-        "@j1 ld.shared.v4.b32 {%13,%14,%15,%16}, [c10+" GN_STR(GN_GRAD_IMM) "];\n\t"
-        "@k1 ld.shared.v4.b32 {%13,%14,%15,%16}, [c01+" GN_STR(GN_GRAD_IMM) "];\n\t"
-        "@!i2 ld.shared.v4.b32 {%17,%18,%19,%20}, [c11+" GN_STR(GN_GRAD_IMM) "];\n\t"
-        "@!j2 ld.shared.v4.b32 {%17,%18,%19,%20}, [c01+" GN_STR(GN_GRAD_IMM) "+128];\n\t"
-        "@!k2 ld.shared.v4.b32 {%17,%18,%19,%20}, [c10+" GN_STR(GN_GRAD_IMM) "+128];\n\t"
+        GN_LDG("%9", "%10", "%11", "%12", "c00+" GN_STR(GN_GRAD_IMM))
+        GN_LDG("%21", "%22", "%23", "%24", "c11+" GN_STR(GN_GRAD_IMM) "+128")
+        "@i1 " GN_LDG("%13", "%14", "%15", "%16", "c00+" GN_STR(GN_GRAD_IMM) "+128")
+        "@j1 " GN_LDG("%13", "%14", "%15", "%16", "c10+" GN_STR(GN_GRAD_IMM))
+        "@k1 " GN_LDG("%13", "%14", "%15", "%16", "c01+" GN_STR(GN_GRAD_IMM))
+        "@!i2 " GN_LDG("%17", "%18", "%19", "%20", "c11+" GN_STR(GN_GRAD_IMM))
+        "@!j2 " GN_LDG("%17", "%18", "%19", "%20", "c01+" GN_STR(GN_GRAD_IMM) "+128")
+        "@!k2 " GN_LDG("%17", "%18", "%19", "%20", "c10+" GN_STR(GN_GRAD_IMM) "+128")
         "}"
         : "+f"(x0), "+f"(y0), "+f"(z0), "=f"(x1), "=f"(y1), "=f"(z1), "=f"(x2), "=f"(y2), "=f"(z2),
           "=f"(C0.x), "=f"(C0.y), "=f"(C0.z), "=r"(C0.g), "=f"(C1.x), "=f"(C1.y), "=f"(C1.z), "=r"(C1.g),

@@ -1,6 +1,6 @@
 """python tools/sass_dump.py lo hi [lib.so] — SASS of k1_march<false> between two addresses (hex)."""
 import os, re, subprocess, sys
-KERN = os.environ.get("KERN", "k1_marchILb0ELb1")
+KERN = os.environ.get("KERN", "k1_marchILb0ELi2")
 lo, hi = int(sys.argv[1], 16), int(sys.argv[2], 16)
 lib = sys.argv[3] if len(sys.argv) > 3 else "gamer_b200/lib/libgamer_b200.so"
 out = subprocess.run(["cuobjdump", "-sass", lib], capture_output=True, text=True).stdout

@@ -1,7 +1,7 @@
 """Static view of the hot loops of k1_march<false>: python tools/sass_loops.py [lib.so] — lists every backward branch
 (loop) with its instruction count and pipe mix (ALU = half-rate pipe on sm_100)."""
 import os, re, subprocess, sys, collections
-KERN = os.environ.get("KERN", "k1_marchILb0ELb1")
+KERN = os.environ.get("KERN", "k1_marchILb0ELi2")
 lib = sys.argv[1] if len(sys.argv) > 1 else "gamer_b200/lib/libgamer_b200.so"
 out = subprocess.run(["cuobjdump", "-sass", lib], capture_output=True, text=True).stdout
 fn = None; ins = []
