@@ -84,17 +84,27 @@ __device__ __forceinline__ float find_difference(float d) {
     return v;
 }
 
-// calculateArmValue (galaxycomponent.h:120-146). max_j pow(1 - v_j/pi, e) = pow(1 - min_j v_j/pi, e) for e > 0.
-__device__ __forceinline__ float arm_value(const DGalaxy &g, const DComp &c, const Rec rec) {
-    float base = rec[REC_W] + rec[REC_THETA] + c.delta;    // winding - (-(theta) + disp) = W + theta + delta - disp
-    float v = find_difference(base - g.arm[0]);
-    bool want_min = c.arm15 > 0.0f;
-    for (int j = 1; j < g.no_arms; j++) {
-        float vj = find_difference(base - g.arm[j]);
-        v = want_min ? fminf(v, vj) : fmaxf(v, vj);
+// calculateArmValue (galaxycomponent.h:120-146): max over the arms of pow(1 - v_j / pi, e), where an arm whose base is
+// negative (wrapped phase difference beyond 3.14159265) gives NaN and is dropped by the reference's fmax; with every arm
+// out of range, or a single one (no fmax then), the NaN reaches `val` and fails the `val * weight > 0.0005` test.
+// e > 0: the maximum is pow(1 - min_j v_j / pi, e), and a base clamped to 0 gives 0, which also contributes nothing.
+// e < 0 (no shipped galaxy; out of line): the maximum is at the LARGEST in-range v_j; none in range -> 0.
+__device__ __noinline__ float arm_value_neg(const DGalaxy &g, float arm15, float base) {
+    float best = -1.0f;
+    for (int j = 0; j < g.no_arms; j++) {
+        const float vj = find_difference(base - g.arm[j]);
+        if (1.0f - vj * (1.0f / 3.14159265f) >= 0.0f) best = fmaxf(best, vj);
     }
-    float b = fmaxf(1.0f - v * (1.0f / 3.14159265f), 0.0f);   // a negative base is NaN in the reference and contributes nothing
-    return fpow(b, c.arm15);
+    if (best < 0.0f) return 0.0f;
+    return ex2a(arm15 * lg2a(1.0f - best * (1.0f / 3.14159265f)));
+}
+__device__ __forceinline__ float arm_value(const DGalaxy &g, float arm15, float base) {
+    if (!(arm15 > 0.0f)) return arm_value_neg(g, arm15, base);
+    float v = find_difference(base - g.arm[0]);
+    if (g.no_arms > 1) v = fminf(v, find_difference(base - g.arm[1]));
+    if (g.no_arms > 2) v = fminf(v, find_difference(base - g.arm[2]));
+    if (g.no_arms > 3) v = fminf(v, find_difference(base - g.arm[3]));
+    return ex2a(arm15 * lg2a(fmaxf(fmaf(v, -1.0f / 3.14159265f, 1.0f), 0.0f)));
 }
 
 // Bulge emission (galaxycomponents.cpp:5-18): rad = (|p|+0.01) r0 + 0.01; i = k (rad^-0.855 exp(-rad^0.25) - 0.05), i >= 0
@@ -149,23 +159,20 @@ template <bool COUNT, bool ORIENT_Y>
 __device__ __forceinline__ void eval_component(const DScene &sc, const DGalaxy &g, const DComp &c, const Rec rec,
                                                const NoiseCtx &nz, float &Ir, float &Ig, float &Ib, Counts &cn) {
     const float rs = sc.ray_step_f;
-    if (c.cls == GAMER_CLASS_BULGE) {   // galaxycomponents.cpp:5-25 — evaluated at every sample, no gates
+    const int cls = c.cls;
+    if (cls == GAMER_CLASS_BULGE) {   // galaxycomponents.cpp:5-25 — evaluated at every sample, no gates
         const f3 pb = {rec[0], rec[1], rec[2]};
-        bulge_add(c.strength * c.iscale * rs * rec[15], c.r0, c.spec[0], c.spec[1], c.spec[2],
-                  sqrta(fmaf(pb.z, pb.z, fmaf(pb.y, pb.y, pb.x * pb.x))), Ir, Ig, Ib);
+        const float i = bulge_term(c.bk * rec[15], c.r0, sqrta(fmaf(pb.z, pb.z, fmaf(pb.y, pb.y, pb.x * pb.x))));
+        Ir = fmaf(i, c.spec[0], Ir); Ig = fmaf(i, c.spec[1], Ig); Ib = fmaf(i, c.spec[2], Ib);
         if (COUNT) cn.evals++;
         return;
     }
     // ---- slab gate: h = |dott/z0| > 2 -> 0 (galaxycomponent.h:61-64), exact --------------------
-    float ad = fabsf(rec[REC_DOTT]);
+    const float ad = fabsf(rec[REC_DOTT]);
     if (!(ad <= c.h_gate)) return;
-    float e = fexp(ad * c.inv_z0);
-    float ch = 0.5f * (e + rcpa(e));
-    float z = rcpa(ch * ch);
-    if (!(z > 0.01f)) return;
     // ---- radial gate: intensity > 0.001 (galaxycomponent.cpp:62-65), exact -----------------------
-    bool pass;
     const float Plen = rec[REC_PLEN];
+    bool pass;
     if (Plen < c.plen_lo) pass = true;
     else if (Plen > c.plen_hi) pass = false;
     else {      // rare: inside the band where only the exact |P| decides; P = p - orient * dott like getRadius
@@ -175,21 +182,24 @@ __device__ __forceinline__ void eval_component(const DScene &sc, const DGalaxy &
         pass = v_length(Pq) <= c.plen_thr;
     }
     if (!pass) return;
-    float intensity = fminf(fmaxf(ex2(Plen * c.k_radial) - 0.01f, 0.0f), 0.1f);
-    float scale = 1.0f;
-    if (!(c.flags & DC_INNER_ZERO)) {
-        float x = fminf(fmaxf(Plen * g.inv_axis_x * c.inv_inner, 0.0f), 1.0f);
-        float sm = x * x * (3.0f - 2.0f * x);
+    // ---- val = strength * scale * armVal * z * intensity (galaxycomponent.cpp:58-79), value arithmetic: raw MUFU ------
+    // z = sech^2(h) = 4 E / (1 + E)^2 with E = exp(-2h): one exponential, one reciprocal. h <= 2 behind the slab gate,
+    // so z >= 0.07 and the reference's `z > 0.01` test (galaxycomponent.cpp:55) cannot fail here.
+    const int flags = c.flags;
+    const float E = ex2a(-ad * c.hz2), onepE = 1.0f + E;
+    float val = c.strength4 * E * rcpa(onepE * onepE);
+    val *= fminf(fmaxf(ex2a(Plen * c.k_radial) - 0.01f, 0.0f), 0.1f);
+    if (!(flags & DC_INNER_ZERO)) {
+        const float x = __saturatef(Plen * c.inner_k);
+        float sm = x * x * fmaf(-2.0f, x, 3.0f);
         sm *= sm;
-        scale = sm * sm;
+        val *= sm * sm;
     }
-    float armv = 1.0f;
     double winding = 0.0;
-    if (c.flags & DC_HAS_ARM) {
-        armv = arm_value(g, c, rec);
-        if (c.flags & DC_HAS_WINDING) winding = __dmul_rn(rec_get_d(rec, REC_WD), c.winding_d);
+    if (flags & DC_HAS_ARM) {
+        val *= arm_value(g, c.arm15, rec[REC_W] + rec[REC_THETA] + c.delta);   // winding - (-theta + disp): W + theta + delta - disp
+        if (flags & DC_HAS_WINDING) winding = __dmul_rn(rec_get_d(rec, REC_WD), c.winding_d);
     }
-    float val = c.strength * scale * armv * z * intensity;
     {
         const float ival0 = val * rec[15];
         if (!(ival0 > 0.0005f)) return;
@@ -199,7 +209,6 @@ __device__ __forceinline__ void eval_component(const DScene &sc, const DGalaxy &
 
     // One twirl and ONE noise evaluation site for every class (keeps the hot loop small enough for the
     // instruction cache); the class-specific use of the noise value follows.
-    const int cls = c.cls;
     if (cls > GAMER_CLASS_STARS) return;              // "stars small": no-op (see gamer_b200.h)
     const bool is_ridged = (cls == GAMER_CLASS_DUST2) | (cls == GAMER_CLASS_DUST_POSITIVE);
     const f3 sp = {rec[0], rec[1], rec[2]};
@@ -338,7 +347,6 @@ __device__ __forceinline__ void march(const DScene &sc, const DGalaxy &g, const 
         {   // ---- run of off-slab samples ---------------------------------------------------------------------
             f3 p = {rec[0], rec[1], rec[2]};
             const f3 dir = {rec[3], rec[4], rec[5]};
-            const f3 origin = {rec[6], rec[7], rec[8]};
             const f3 camrel_ = {rec[9], rec[10], rec[11]};
             const float length_f = rec[12];
             float thr = rec[13];
@@ -406,7 +414,11 @@ __device__ __forceinline__ void march(const DScene &sc, const DGalaxy &g, const 
                     }
                 }
 #endif
-                const bool alive = marched < sure_below || -v_dot(v_sub(p, origin), dir) < thr;
+                bool alive = marched < sure_below;
+                if (!alive) {                       // the exact test, only near the ray's end: its operands come from the record
+                    const f3 origin = {rec[6], rec[7], rec[8]};
+                    alive = -v_dot(v_sub(p, origin), dir) < thr;
+                }
                 if (alive) {
                     // step = clamp(|p - camera| * rayStep, minRayStep, 0.01)
                     const f3 dc = v_sub(p, camrel_);

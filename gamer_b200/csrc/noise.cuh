@@ -276,6 +276,22 @@ __device__ __forceinline__ void skew(double x, double y, double z, Skewed &su, S
     sw = to_fixed(__dadd_rn(z, s));
 }
 
+// The same three fixed-point images from a FLOAT point (the ridged multifractal, whose point is a float QVector3D),
+// without the three double -> int64 conversions: x * 2^32 is exact in float and widens exactly; the reference's
+// roundings s = RN(RN(RN(x + y) + z) / 3), u = RN(x + s) commute with the power-of-two scaling, so the doubles below are
+// exactly 2^32 times the reference's; and floor(u 2^32) is read off the significand after a round-DOWN add of
+// 1.5 * 2^52 (low word = the fraction, the next 20 bits = the cell modulo 2^20; |u 2^32| < 2^51). `d` is not set.
+__device__ __forceinline__ void skew_float(float x, float y, float z, Skewed &su, Skewed &sv, Skewed &sw) {
+    const double X = (double)__fmul_rn(x, 4294967296.0f), Y = (double)__fmul_rn(y, 4294967296.0f),
+                 Z = (double)__fmul_rn(z, 4294967296.0f);
+    const double s = __dmul_rn(__dadd_rn(__dadd_rn(X, Y), Z), 1.0 / 3.0);
+    const double M = 6755399441055744.0;
+    const double tu = __dadd_rd(__dadd_rn(X, s), M), tv = __dadd_rd(__dadd_rn(Y, s), M), tw = __dadd_rd(__dadd_rn(Z, s), M);
+    su.lo = (uint32_t)__double2loint(tu); su.hi = __double2hiint(tu);
+    sv.lo = (uint32_t)__double2loint(tv); sv.hi = __double2hiint(tv);
+    sw.lo = (uint32_t)__double2loint(tw); sw.hi = __double2hiint(tw);
+}
+
 // one octave: cells/fractions of (2^k u, 2^k v, 2^k w) and the raw simplex value. QUIRK selects the
 // (almost never needed) variant that checks for the reference's fastfloor behaviour at exact integers.
 template <bool QUIRK>
@@ -346,7 +362,7 @@ __device__ GN_NOISE_LINKAGE float ridged(uint32_t lane4, float vx, float vy, flo
 #pragma unroll 1
     for (int o = 0; o < octaves; o++) {
         Skewed su, sv, sw;
-        skew((double)vx, (double)vy, (double)vz, su, sv, sw);
+        skew_float(vx, vy, vz, su, sv, sw);
         float signal;
         if (maybe_integer(su, sv, sw, 0)) signal = octave_quirk(lane4, vx, vy, vz);
         else signal = octave<false>(lane4, lane16, su, sv, sw, 0);

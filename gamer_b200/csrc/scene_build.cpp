@@ -149,6 +149,10 @@ int gk_build_scene(const GamerFrame *f, const GamerGalaxy *gal, const GamerCompo
             q.noise_tilt = float(c.noise_tilt);
             q.rscale = float(c.scale);
             q.r0 = float(c.r0);
+            q.hz2 = float(2.0 * 1.4426950408889634 / std::fabs(c.z0));
+            q.strength4 = 4.0f * q.strength;
+            q.inner_k = float(1.0 / (double(g.axis[0]) * inner));
+            q.bk = q.strength * q.iscale * float(f->ray_step);
             for (int i = 0; i < 3; i++) q.spec[i] = c.spec[i];
 
             // slab gate (galaxycomponent.h:61-64): h = |height/z0|; h > 2 -> 0

@@ -50,6 +50,11 @@ struct DComp {
     int32_t tgroup;          // twirl sharing: first component of this galaxy with the same twirl angle, -1 = nobody shares it
     double  nscale;          // fBm start frequency, as a double the way the reference forms it
     double  winding_d;       // cp.winding as the double the reference multiplies getWinding() with
+    // value-arithmetic constants of the gate code (kernels.cu, eval_component)
+    float   hz2;             // 2 log2(e) / |z0|: sech^2(h) = 4 E / (1 + E)^2 with E = exp(-2h) = exp2(-|dott| * hz2)
+    float   strength4;       // 4 * strength (the 4 of sech^2)
+    float   inner_k;         // 1 / (axis.x * inner): smoothstep argument = |P| * inner_k
+    float   bk;              // bulge: strength * iscale * float(rayStep), the factor of `weight` in its emission
 };
 
 struct DGalaxy {
