@@ -61,7 +61,7 @@ SYMBOLS = [
     "gamer_b200_host_alloc", "gamer_b200_host_free",
     "gamer_b200_probe_simplex", "gamer_b200_probe_fbm", "gamer_b200_probe_ridged",
     "gamer_b200_star_list", "gamer_b200_render_stars",
-    "gamer_b200_fbm_static_max_points", "gamer_b200_fbm_static",
+    "gamer_b200_fbm_static_max_points", "gamer_b200_fbm_static", "gamer_b200_copy_bands",
 ]
 
 _lib = None
@@ -114,6 +114,8 @@ def load():
     lib.gamer_b200_star_list.argtypes = [C.c_int32, C.c_int32, C.c_double, C.c_double, C.c_double, C.c_uint64,
                                          C.POINTER(GamerStar)]
     lib.gamer_b200_render_stars.argtypes = [p, C.POINTER(GamerStar), C.c_int32, p]
+    if hasattr(lib, "gamer_b200_copy_bands"):
+        lib.gamer_b200_copy_bands.argtypes = [p, C.c_int32, p]
     if hasattr(lib, "gamer_b200_fbm_static"):       # absent only from older A/B builds selected through GAMER_B200_LIB
         lib.gamer_b200_fbm_static_max_points.restype = C.c_int
         lib.gamer_b200_fbm_static.argtypes = [p, C.c_int32, C.c_int32, C.c_double, C.c_double, p]

@@ -46,6 +46,7 @@ struct gamer_ctx {
     std::vector<Dev> devs;
     GamerFrame frame;
     bool uploaded = false, rendered = false, counted = false;
+    bool skipped = false;                      // the last render was not launched at all (abort requested before it)
     std::string err;
     std::atomic<int> abort_req{0};
     std::atomic<int> rendering{0};
@@ -119,7 +120,6 @@ int launch_render(gamer_ctx *ctx, bool counted) {
         if (d.rows <= 0) continue;
         CK(cudaSetDevice(d.device));
         CK(cudaMemsetAsync(d.progress, 0, 2 * sizeof(unsigned int), d.st));
-        CK(cudaMemsetAsync(d.abort_flag, 0, sizeof(int), d.st));
         if (counted) CK(cudaMemsetAsync(d.counters, 0, GAMER_CNT_N * sizeof(unsigned long long), d.st));
         if (!(d.scene.flags & GAMER_FRAME_CONTINUE))
             CK(cudaMemsetAsync(d.rgb, 0, (size_t)d.rows * d.scene.width * 3 * sizeof(float), d.st));
@@ -144,8 +144,8 @@ int finish_render(gamer_ctx *ctx, bool counted) {
     if (rc) return rc;
     Dev &d0 = ctx->devs[0];
     CK(cudaSetDevice(d0.device));
-    if (d0.rows > 0) CK(cudaEventElapsedTime(&ctx->k1_ms, d0.ev[0], d0.ev[1]));
-    if (counted) {
+    if (d0.rows > 0 && !ctx->skipped) CK(cudaEventElapsedTime(&ctx->k1_ms, d0.ev[0], d0.ev[1]));
+    if (counted && !ctx->skipped) {
         for (auto &v : ctx->counters) v = 0;
         for (Dev &d : ctx->devs) {
             if (d.rows <= 0) continue;
@@ -157,7 +157,25 @@ int finish_render(gamer_ctx *ctx, bool counted) {
     }
     ctx->counted = counted;
     ctx->rendered = true;
-    if (ctx->abort_req.exchange(0)) return set_err(ctx, GAMER_E_ABORTED, "render aborted");
+    // Rasterizer::Abort sets m_abort at any time and RenderPixelsOMP resets it when it ends (rasterizer.cpp:296-297,311):
+    // a request cancels the render in flight or, made while idle, the next one, and is consumed by that render. Whether
+    // THIS render was cut short is read from the device (tiles finished < tiles), not from the request: an abort that
+    // lands after the last tile leaves a complete frame, which is delivered.
+    if (ctx->abort_req.exchange(0) || ctx->skipped) {
+        bool cut = ctx->skipped;
+        for (Dev &d : ctx->devs) {
+            if (d.rows <= 0) continue;
+            CK(cudaSetDevice(d.device));
+            if (!ctx->skipped) {
+                unsigned int done = 0;
+                CK(cudaMemcpy(&done, d.progress, sizeof(done), cudaMemcpyDeviceToHost));
+                if (done < d.n_blocks) cut = true;
+            }
+            CK(cudaMemset(d.abort_flag, 0, sizeof(int)));      // only here: never in the render stream of a live render
+        }
+        ctx->skipped = false;
+        if (cut) return set_err(ctx, GAMER_E_ABORTED, "render aborted");
+    }
     return GAMER_OK;
 }
 
@@ -246,6 +264,11 @@ int gamer_b200_create(gamer_ctx **out, const int32_t *device_ids, int32_t n_devi
         if (e == cudaSuccess) e = cudaHostAlloc(&d.progress_host, sizeof(unsigned int), cudaHostAllocDefault);
         if (e == cudaSuccess) e = cudaMemset(d.abort_flag, 0, sizeof(int));
         if (e == cudaSuccess) e = cudaMemset(d.progress, 0, 2 * sizeof(unsigned int));
+        if (e == cudaErrorNotSupported) {
+            gamer_b200_destroy(c);
+            return set_err(nullptr, GAMER_E_CUDA, "the dynamic shared-memory window does not start at the offset the noise tables are "
+                                                  "addressed with (a debugger, sanitizer or driver that reserves a different amount)");
+        }
         if (e != cudaSuccess) {
             gamer_b200_destroy(c);
             return cuda_fail(nullptr, e, "context creation");
@@ -296,8 +319,16 @@ static int render_common(gamer_ctx *ctx, bool counted, float *host_out) {
     if (!ctx) return GAMER_E_ARG;
     std::lock_guard<std::mutex> lock(ctx->mu);
     if (!ctx->uploaded) return set_err(ctx, GAMER_E_STATE, "render before upload");
-    ctx->rendering.store(1);
-    int rc = launch_render(ctx, counted);
+    ctx->rendering.store(1);           // before the request is looked at: an abort() that misses the look sees rendering == 1
+    int rc = GAMER_OK;
+    if (ctx->abort_req.load()) {       // requested before this render began: nothing is launched (every pixel "skipped")
+        ctx->skipped = true;
+        for (Dev &d : ctx->devs) {
+            if (d.rows <= 0 || (d.scene.flags & GAMER_FRAME_CONTINUE)) continue;
+            if (cudaSetDevice(d.device) == cudaSuccess)
+                cudaMemsetAsync(d.rgb, 0, (size_t)d.rows * d.scene.width * 3 * sizeof(float), d.st);
+        }
+    } else rc = launch_render(ctx, counted);
     if (!rc) rc = finish_render(ctx, counted);
     ctx->rendering.store(0);
     if (rc) return rc;
@@ -436,8 +467,8 @@ int gamer_b200_progress(gamer_ctx *ctx, double *fraction) {
 // Rasterizer::Abort (rasterizer.h:91-98): blocks that have not started skip their pixels. Any thread.
 int gamer_b200_abort(gamer_ctx *ctx) {
     if (!ctx) return GAMER_E_ARG;
+    ctx->abort_req.store(1);           // sticky: consumed by the render in flight or, if none is, by the next one
     if (!ctx->rendering.load()) return GAMER_OK;
-    ctx->abort_req.store(1);
     static const int one = 1;
     for (Dev &d : ctx->devs) {
         if (cudaSetDevice(d.device) != cudaSuccess) continue;
@@ -455,6 +486,34 @@ int gamer_b200_device_buffers(gamer_ctx *ctx, int32_t which, void **rgb_dev, voi
     if (argb_dev) *argb_dev = d.argb;
     if (argb_shadow_dev) *argb_shadow_dev = d.shadow;
     if (rows_out) *rows_out = d.rows;
+    return GAMER_OK;
+}
+
+// This context's tile, copied to its place in a full_size x full_size HOST image (which_buf: 0 float RGB, 1 ARGB32,
+// 2 shadow ARGB32). One process per GPU, each with the bands of one frame (GamerFrame x0/y0/band_rows/band_stride),
+// writes them into ONE host frame the processes share (shared memory, ideally cudaHostRegister'ed): the final gather of
+// the tile partition without a device-side collective and without a serial copy by one rank.
+int gamer_b200_copy_bands(gamer_ctx *ctx, int32_t which_buf, void *host_full_frame) {
+    if (!ctx || !host_full_frame || which_buf < 0 || which_buf > 2) return GAMER_E_ARG;
+    std::lock_guard<std::mutex> lock(ctx->mu);
+    if (!ctx->rendered) return set_err(ctx, GAMER_E_STATE, "copy_bands before render");
+    if (ctx->devs.size() != 1) return set_err(ctx, GAMER_E_STATE, "copy_bands is for single-device contexts (a multi-device context gathers by itself)");
+    Dev &d = ctx->devs[0];
+    const GamerFrame &f = ctx->frame;
+    const size_t elem = which_buf == 0 ? 3 * sizeof(float) : sizeof(uint32_t);
+    const char *src = which_buf == 0 ? (const char *)d.rgb : which_buf == 1 ? (const char *)d.argb : (const char *)d.shadow;
+    if (f.x0 < 0 || f.y0 < 0 || f.x0 + f.width > f.full_size) return set_err(ctx, GAMER_E_ARG, "tile outside the full image");
+    CK(cudaSetDevice(d.device));
+    const int run = f.band_rows > 0 ? f.band_rows : f.height;          // local rows that are contiguous in the image
+    const size_t src_pitch = (size_t)f.width * elem, dst_pitch = (size_t)f.full_size * elem;
+    for (int L = 0; L < f.height; L += run) {
+        const int rows = (L + run <= f.height) ? run : f.height - L;
+        const int y = f.band_rows > 0 ? f.y0 + (L / f.band_rows) * f.band_stride : f.y0 + L;
+        if (y + rows > f.full_size) return set_err(ctx, GAMER_E_ARG, "tile outside the full image");
+        char *dst = (char *)host_full_frame + ((size_t)y * f.full_size + f.x0) * elem;
+        CK(cudaMemcpy2DAsync(dst, dst_pitch, src + (size_t)L * src_pitch, src_pitch, src_pitch, rows, cudaMemcpyDeviceToHost, d.st));
+    }
+    CK(cudaStreamSynchronize(d.st));
     return GAMER_OK;
 }
 
@@ -489,30 +548,37 @@ int gamer_b200_host_free(void *ptr) {
 }
 
 // ---- probes ------------------------------------------------------------------------------------
-static int probe_io(gamer_ctx *ctx, const float *xyz, int32_t n, float **xyz_dev, float **val_dev) {
+}  // extern "C"
+namespace {
+struct DevBuf {                    // freed on every path out of a probe
+    void *p = nullptr;
+    ~DevBuf() { if (p) cudaFree(p); }
+    template <class T> T *as() const { return static_cast<T *>(p); }
+};
+int probe_io(gamer_ctx *ctx, const float *xyz, int32_t n, DevBuf &xyz_dev, DevBuf &val_dev) {
     Dev &d = ctx->devs[0];
     CK(cudaSetDevice(d.device));
-    CK(cudaMalloc(xyz_dev, (size_t)n * 3 * sizeof(float)));
-    CK(cudaMalloc(val_dev, (size_t)n * sizeof(float)));
-    CK(cudaMemcpyAsync(*xyz_dev, xyz, (size_t)n * 3 * sizeof(float), cudaMemcpyHostToDevice, d.st));
+    CK(cudaMalloc(&xyz_dev.p, (size_t)n * 3 * sizeof(float)));
+    CK(cudaMalloc(&val_dev.p, (size_t)n * sizeof(float)));
+    CK(cudaMemcpyAsync(xyz_dev.p, xyz, (size_t)n * 3 * sizeof(float), cudaMemcpyHostToDevice, d.st));
     return GAMER_OK;
 }
+}  // namespace
+extern "C" {
 
 int gamer_b200_probe_simplex(gamer_ctx *ctx, const float *xyz, int32_t n, double frequency, int32_t *lattice_out, float *value_out) {
     if (!ctx || !xyz || n <= 0) return GAMER_E_ARG;
     std::lock_guard<std::mutex> lock(ctx->mu);
     Dev &d = ctx->devs[0];
-    float *xd = nullptr, *vd = nullptr;
-    int32_t *ld = nullptr;
-    int rc = probe_io(ctx, xyz, n, &xd, &vd);
+    DevBuf xd, vd, ld;
+    int rc = probe_io(ctx, xyz, n, xd, vd);
     if (rc) return rc;
-    CK(cudaMalloc(&ld, (size_t)n * 10 * sizeof(int32_t)));
-    CK(gk::launch_probe_simplex(xd, n, frequency, ld, vd, d.st));
+    CK(cudaMalloc(&ld.p, (size_t)n * 10 * sizeof(int32_t)));
+    CK(gk::launch_probe_simplex(xd.as<float>(), n, frequency, ld.as<int32_t>(), vd.as<float>(), d.st));
     ctx->launches += 1;
-    if (value_out) CK(cudaMemcpyAsync(value_out, vd, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, d.st));
-    if (lattice_out) CK(cudaMemcpyAsync(lattice_out, ld, (size_t)n * 10 * sizeof(int32_t), cudaMemcpyDeviceToHost, d.st));
+    if (value_out) CK(cudaMemcpyAsync(value_out, vd.p, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, d.st));
+    if (lattice_out) CK(cudaMemcpyAsync(lattice_out, ld.p, (size_t)n * 10 * sizeof(int32_t), cudaMemcpyDeviceToHost, d.st));
     CK(cudaStreamSynchronize(d.st));
-    cudaFree(xd); cudaFree(vd); cudaFree(ld);
     return GAMER_OK;
 }
 
@@ -520,16 +586,15 @@ int gamer_b200_probe_fbm(gamer_ctx *ctx, const float *xyz, int32_t n, int32_t oc
     if (!ctx || !xyz || !value_out || n <= 0 || octaves <= 0 || octaves > 32) return GAMER_E_ARG;
     std::lock_guard<std::mutex> lock(ctx->mu);
     Dev &d = ctx->devs[0];
-    float *xd = nullptr, *vd = nullptr;
-    int rc = probe_io(ctx, xyz, n, &xd, &vd);
+    DevBuf xd, vd;
+    int rc = probe_io(ctx, xyz, n, xd, vd);
     if (rc) return rc;
     double amp = 1, maxamp = 0;
     for (int o = 0; o < octaves; o++) { maxamp += amp; amp *= persistence; }
-    CK(gk::launch_probe_fbm(xd, n, octaves, (float)persistence, (float)(1.0 / maxamp), scale, vd, d.st));
+    CK(gk::launch_probe_fbm(xd.as<float>(), n, octaves, (float)persistence, (float)(1.0 / maxamp), scale, vd.as<float>(), d.st));
     ctx->launches += 1;
-    CK(cudaMemcpyAsync(value_out, vd, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, d.st));
+    CK(cudaMemcpyAsync(value_out, vd.p, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, d.st));
     CK(cudaStreamSynchronize(d.st));
-    cudaFree(xd); cudaFree(vd);
     return GAMER_OK;
 }
 
@@ -538,17 +603,16 @@ int gamer_b200_probe_ridged(gamer_ctx *ctx, const float *xyz, int32_t n, double 
     if (!ctx || !xyz || !value_out || n <= 0 || octaves <= 0 || octaves > 16) return GAMER_E_ARG;
     std::lock_guard<std::mutex> lock(ctx->mu);
     Dev &d = ctx->devs[0];
-    float *xd = nullptr, *vd = nullptr;
-    int rc = probe_io(ctx, xyz, n, &xd, &vd);
+    DevBuf xd, vd;
+    int rc = probe_io(ctx, xyz, n, xd, vd);
     if (rc) return rc;
     float rw[16];
     const double w = -0.05f;
     for (int o = 0; o < octaves; o++) { rw[o] = (float)pow(frequency, w); frequency *= lacunarity; }
-    CK(gk::launch_probe_ridged(xd, n, octaves, (float)lacunarity, (float)offset, (float)gain, rw, vd, d.st));
+    CK(gk::launch_probe_ridged(xd.as<float>(), n, octaves, (float)lacunarity, (float)offset, (float)gain, rw, vd.as<float>(), d.st));
     ctx->launches += 1;
-    CK(cudaMemcpyAsync(value_out, vd, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, d.st));
+    CK(cudaMemcpyAsync(value_out, vd.p, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, d.st));
     CK(cudaStreamSynchronize(d.st));
-    cudaFree(xd); cudaFree(vd);
     return GAMER_OK;
 }
 

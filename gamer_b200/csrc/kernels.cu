@@ -197,6 +197,13 @@ __device__ __forceinline__ void eval_component(const DScene &sc, const DGalaxy &
     }
     double winding = 0.0;
     if (flags & DC_HAS_ARM) {
+        // getWinding / getTheta of the sample, formed by the first component that gets this far (a NaN marks "not yet"):
+        // a fifth of the in-slab samples of an exterior view lie beyond every armed component's radial cut-off
+        if (rec[REC_W] != rec[REC_W]) {
+            const f3 pa = {rec[0], rec[1], rec[2]};
+            const f3 orient = {g.orient[0], g.orient[1], g.orient[2]};
+            arm_base(g, rec, ORIENT_Y ? f3{pa.x, 0.0f, pa.z} : v_sub(pa, v_mul(orient, rec[REC_DOTT])));
+        }
         val *= arm_value(g, c.arm15, rec[REC_W] + rec[REC_THETA] + c.delta);   // winding - (-theta + disp): W + theta + delta - disp
         if (flags & DC_HAS_WINDING) winding = __dmul_rn(rec_get_d(rec, REC_WD), c.winding_d);
     }
@@ -473,8 +480,7 @@ __device__ __forceinline__ void march(const DScene &sc, const DGalaxy &g, const 
                 const f3 P = ORIENT_Y ? f3{sp.x, 0.0f, sp.z} : v_sub(sp, v_mul(orient, dott));   // p.y - p.y*1 = 0
                 rec[REC_DOTT] = dott;
                 rec[REC_PLEN] = sqrta(fmaf(P.z, P.z, fmaf(P.y, P.y, P.x * P.x)));
-                // getWinding / getTheta once per sample, up front
-                if (g.any_arm) arm_base(g, rec, P);
+                rec[REC_W] = __int_as_float(0x7fc00000);       // getWinding / getTheta: not formed yet (eval_component)
             }
 #ifndef K1_NO_TWIRL_CACHE
             if (g.any_tshare) rec[REC_TG] = -1.0f;
@@ -533,7 +539,7 @@ k1_march(const __grid_constant__ DScene sc, float *__restrict__ out, unsigned lo
         if (lane == 0) tile = atomicAdd(progress + 1, 1u);
         tile = __shfl_sync(0xffffffffu, tile, 0);
         if (tile >= n_tiles) break;
-        if (*abort_flag) break;             // rasterizer.cpp:296-297: skipped pixels keep their old value
+        if (*abort_flag) break;             // rasterizer.cpp:296-297; skipped pixels stay 0 (the frame is cleared before the pass)
         const int lx = (int)(tile % tiles_x) * 8 + (lane & 7);
         const int ly = (int)(tile / tiles_x) * 4 + (lane >> 3);
     // Every lane of the warp walks the same control flow (the march keeps the 32 rays in lockstep with warp votes);
@@ -808,7 +814,27 @@ kp_ridged(const float *__restrict__ xyz, int n, int octaves, float lac, float of
 // ---- launchers (host) -----------------------------------------------------------------------------
 namespace gk {
 
+}  // namespace gk
+namespace {
+// The noise code addresses its tables with immediates that assume the dynamic shared window begins at GN_DYN_BASE
+// (noise.cuh). That offset is the driver's reservation and could differ under a debugger, a sanitizer or another driver:
+// it is checked here, once per device, so that context creation fails with a message; the __trap() in table_init stays
+// as an assertion only.
+__device__ unsigned int g_dyn_smem_base_probe;
+__global__ void k_dyn_smem_base() { g_dyn_smem_base_probe = (unsigned int)__cvta_generic_to_shared(gnoise::gn_dyn_smem); }
+}  // namespace
+namespace gk {
+
 // kernels that use the noise table need > 48 KB of dynamic shared memory: opt in once per device
+cudaError_t check_dyn_smem_base() {
+    k_dyn_smem_base<<<1, 1, 1024>>>();
+    cudaError_t e = cudaGetLastError();
+    unsigned int base = 0;
+    if (e == cudaSuccess) e = cudaMemcpyFromSymbol(&base, g_dyn_smem_base_probe, sizeof(base));
+    if (e == cudaSuccess && base != GN_DYN_BASE) e = cudaErrorNotSupported;   // api.cu turns this into a message
+    return e;
+}
+
 cudaError_t prepare_device() {
     cudaError_t e = cudaSuccess;
 #define K1_ATTR(C, M) if (e == cudaSuccess) e = cudaFuncSetAttribute(k1_march<C, M>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)K1_DYN_SMEM)
@@ -817,6 +843,7 @@ cudaError_t prepare_device() {
     if (e == cudaSuccess) e = cudaFuncSetAttribute(kp_simplex, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GN_DYN_SMEM);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(kp_fbm, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GN_DYN_SMEM);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(kp_ridged, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GN_DYN_SMEM);
+    if (e == cudaSuccess) e = check_dyn_smem_base();
     return e;
 }
 

@@ -4,6 +4,7 @@
 #include <cmath>
 #include <cstdio>
 #include <cstring>
+#include <initializer_list>
 #include <limits>
 #include "scene_build.h"
 
@@ -97,6 +98,20 @@ int gk_build_scene(const GamerFrame *f, const GamerGalaxy *gal, const GamerCompo
         DGalaxy &d = s.gal[gi];
         if (g.comp_begin < 0 || g.comp_count < 0 || g.comp_begin + g.comp_count > f->n_components)
             return fail("galaxy component range outside the component array");
+        // The kernels use reciprocal / division / square-root sequences without the library's slow paths: their operands
+        // must be finite, normal and non-zero. And the march must make progress: once ulp(p) exceeds the smallest step,
+        // p - dir*step == p and the loop test never turns false (the reference would hang as well; a persistent kernel
+        // that never ends wedges the context). |p| < 1024 keeps ulp(p) <= 6.1e-5 < min step for every legal step.
+        for (int i = 0; i < 3; i++) {
+            if (!std::isfinite(g.axis[i]) || !(std::fabs(g.axis[i]) >= 1e-6f) || !(std::fabs(g.axis[i]) <= 256.0f))
+                return fail("galaxy axis must be finite, non-zero and at most 256");
+            if (!std::isfinite(g.pos[i]) || !std::isfinite(g.orient[i]) || !std::isfinite(f->cam[i]))
+                return fail("galaxy position / orientation and the camera must be finite");
+            if (!(std::fabs(g.pos[i] - f->cam[i]) <= 512.0f)) return fail("galaxy farther than 512 from the camera");
+        }
+        if (!std::isfinite(g.winding_b) || g.winding_b == 0.0 || !std::isfinite(g.winding_n) || !std::isfinite(g.intensity_scale))
+            return fail("windingB must be finite and non-zero, windingN and intensityScale finite");
+        if (f->min_ray_step < 1e-4) return fail("min_ray_step below 1e-4");
         for (int i = 0; i < 3; i++) {
             d.pos[i] = g.pos[i];
             d.orient[i] = g.orient[i];
@@ -124,6 +139,10 @@ int gk_build_scene(const GamerFrame *f, const GamerGalaxy *gal, const GamerCompo
             if (!(c.active == 1)) continue;                                   // rasterizer.cpp:458
             if (c.class_id < GAMER_CLASS_BULGE || c.class_id > GAMER_CLASS_STARS_SMALL) return fail("unknown class_id");
             if (c.class_id == GAMER_CLASS_STARS_SMALL) { d.noop_count++; continue; }   // no-op, see gamer_b200.h
+            for (double v : {c.strength, c.arm, c.z0, c.r0, c.inner, c.delta, c.winding, c.scale, c.noise_offset, c.noise_tilt, c.ks})
+                if (!std::isfinite(v)) return fail("component parameters must be finite");
+            if (c.class_id != GAMER_CLASS_BULGE && !(std::fabs(c.z0) >= 1e-9)) return fail("component z0 must be non-zero");
+            if (std::fabs(c.scale) >= 65536.0) return fail("noise scale too large (|scale| must stay below 65536)");
             if (nc >= DEV_MAX_COMPONENTS) return fail("too many active components (max 64 per frame)");
             DComp &q = s.comp[nc++];
             q.cls = c.class_id;

@@ -46,7 +46,9 @@ def band_tile(scene, rank: int, world: int, band: int = BAND):
     n = len(band_rows(rank, world, f.height, band))
     if world == 1:
         return scene.tile(f.x0, f.y0, f.width, f.height)
-    return scene.tile(f.x0, f.y0 + rank * band, f.width, max(n, 0), band_rows=band, band_stride=band * world)
+    if n == 0:          # more ranks than bands (a small frame): this rank owns nothing and neither uploads nor renders
+        return None
+    return scene.tile(f.x0, f.y0 + rank * band, f.width, n, band_rows=band, band_stride=band * world)
 
 
 def gather_bands(local: torch.Tensor, height: int, rank: int, world: int, band: int = BAND, dst: int = 0):
@@ -56,6 +58,8 @@ def gather_bands(local: torch.Tensor, height: int, rank: int, world: int, band: 
         return local
     counts = [len(band_rows(r, world, height, band)) for r in range(world)]
     pad = max(counts)
+    if local is None:                               # a rank without rows (band_tile returned None) still takes part
+        raise ValueError("gather_bands needs a tensor on every rank: pass an empty one (shape [0, ...]) for a rank without rows")
     if local.shape[0] != pad:                       # gather needs equal shapes: pad the short ranks
         padded = local.new_zeros((pad,) + tuple(local.shape[1:]))
         padded[: local.shape[0]] = local
@@ -68,6 +72,30 @@ def gather_bands(local: torch.Tensor, height: int, rank: int, world: int, band: 
     for r in range(world):
         out.index_copy_(0, _row_index(r, world, height, band, local.device), bufs[r][: counts[r]])
     return out
+
+
+def job_cost(scene) -> float:
+    """Cost proxy of one render job that needs no rendering to evaluate: pixels x the noise octaves its
+    active components would run at an in-slab sample (10 disk / stars, 9 dust / dust2 / dust positive; a bulge counts 1)."""
+    octaves = {0: 1, 1: 10, 2: 9, 3: 9, 4: 9, 5: 10, 6: 0}
+    per_sample = sum(octaves[int(c.class_id)] for c in scene.components if c.active == 1.0)
+    return float(scene.frame.width) * float(scene.frame.height) * per_sample
+
+
+def longest_job_first(costs: List[float], world: int) -> List[List[int]]:
+    """Greedy longest-processing-time assignment of independent jobs (galaxies of a batch, frames of a sequence) to
+    ranks: jobs in descending cost, each to the least loaded rank so far. Deterministic (ties by job index), so every
+    rank computes the same table without communication. The reference's queue runs its jobs one at a time in
+    submission order (renderqueue.cpp:63-87); with several GPUs the order is what balances them.
+    Returns the job indices of every rank, in execution order."""
+    order = sorted(range(len(costs)), key=lambda j: (-costs[j], j))
+    load = [0.0] * world
+    jobs = [[] for _ in range(world)]
+    for j in order:
+        r = min(range(world), key=lambda q: (load[q], q))
+        jobs[r].append(j)
+        load[r] += costs[j]
+    return jobs
 
 
 def max_over_ranks(values: List[float], device) -> List[float]:

@@ -139,6 +139,12 @@ class Context:
                                                               C.byref(rows)))
         return p[0].value, p[1].value, p[2].value, rows.value
 
+    def copy_bands(self, which_buf: int, host_full_frame) -> None:
+        """gamer_b200_copy_bands: this context's tile into its place in a full_size x full_size host image
+        (numpy array or raw address; which_buf 0 float RGB, 1 ARGB32, 2 shadow)."""
+        ptr = host_full_frame if isinstance(host_full_frame, int) else host_full_frame.ctypes.data
+        _lib.check(self.h, self.lib.gamer_b200_copy_bands(self.h, which_buf, ptr))
+
     def device_tensors(self, which=0):
         """Zero-copy torch views of the device framebuffers of the last render: (rgb [rows,W,3] float32,
         argb [rows,W] int32, shadow [rows,W] int32). For callers that keep results on the GPU (NCCL gather)."""

@@ -195,6 +195,10 @@ int  gamer_b200_render_stars(gamer_ctx *ctx, const GamerStar *stars, int32_t n_s
 
 /* control (callable from any thread; rasterizer.h:91-118) ----------------------------------- */
 int  gamer_b200_progress(gamer_ctx *ctx, double *fraction);
+/* Rasterizer::Abort. Like m_abort (set at any time, reset when RenderPixelsOMP ends, rasterizer.cpp:296-297,311) the
+ * request is sticky: it stops the render in flight or, made while none is, cancels the next one, and that render
+ * consumes it. A render returns GAMER_E_ABORTED only if it was actually cut short (tiles left undrawn are 0); an abort
+ * that arrives after the last tile leaves a complete frame, which is delivered with GAMER_OK. */
 int  gamer_b200_abort   (gamer_ctx *ctx);
 
 /* device-side access for callers that keep data on the GPU (multi-GPU gather, benchmarks) ---- */
@@ -202,6 +206,12 @@ int  gamer_b200_abort   (gamer_ctx *ctx);
  * ARGB images; rows_out = number of rows that device holds (its bands, in band order). */
 int  gamer_b200_device_buffers(gamer_ctx *ctx, int32_t which, void **rgb_dev, void **argb_dev,
                                void **argb_shadow_dev, int32_t *rows_out);
+/* The final gather of the tile partition, host side: copies this (single-device) context's tile — its rows at
+ * x0 / y0 / band_rows / band_stride — to their place in a full_size x full_size HOST image. which_buf: 0 = linear float
+ * RGB (12 B/pixel), 1 = ARGB32, 2 = shadow ARGB32. With one process per GPU, every process calls it on the SAME host
+ * frame (shared memory): no device collective and no serial copy by one rank. Reference analogue: RasterThread's
+ * threads writing their chunk of the shuffled render list into the one m_renderBuffer (rasterthread.cpp:6-25,36-51). */
+int  gamer_b200_copy_bands(gamer_ctx *ctx, int32_t which_buf, void *host_full_frame);
 /* The CUDA stream (cudaStream_t) device `which` of this context launches on, so a caller can order its
  * own work (events, copies, collectives) with the kernels. */
 int  gamer_b200_stream(gamer_ctx *ctx, int32_t which, void **stream_out);

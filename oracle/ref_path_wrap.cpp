@@ -163,6 +163,25 @@ int refpath_assemble(void *hp, double exposure, double gamma, double saturation,
     return 0;
 }
 
+// The background star layer's stamping: the reference's own Buffer2D::RenderGaussian (util/buffer2d.cpp:224-243) for every
+// star of a list, on a zeroed size x size buffer — what Buffer2D::RenderStars (:140-173) does once it has drawn a star's
+// parameters. The parameters themselves come from libc rand() there and cannot be reproduced; the stamping can.
+// stars: n records {int32 x, y, w; float cs[3]} (the layout of GamerStar, include/gamer_b200.h). layer_out = size*size*3.
+struct RefStar { int32_t x, y, w; float cs[3]; };
+int refpath_stamp_stars(int size, const void *stars, int n, float *layer_out) {
+    Buffer2D buf(size);
+    buf.fill(QVector3D(0, 0, 0));
+    const RefStar *st = static_cast<const RefStar *>(stars);
+    for (int k = 0; k < n; k++) buf.RenderGaussian(st[k].x, st[k].y, st[k].w, QVector3D(st[k].cs[0], st[k].cs[1], st[k].cs[2]));
+    for (int j = 0; j < size; j++)
+        for (int i = 0; i < size; i++) {
+            const QVector3D v = buf.Get(i, j);
+            float *o = layer_out + (size_t(j) * size + i) * 3;
+            o[0] = v.x(); o[1] = v.y(); o[2] = v.z();
+        }
+    return 0;
+}
+
 void refpath_destroy(void *hp) {
     RefPath *h = static_cast<RefPath *>(hp);
     delete h->ras;

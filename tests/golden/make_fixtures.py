@@ -9,6 +9,8 @@
   noise_class_ref.npz  Noise::octave_noise_3d and Noise::getRidgedMf of the reference's OWN noise.cpp / simplex.cpp
                    (class Simplex(1,1,1,1), as Rasterizer constructs it), compiled in place against oracle/qtshim,
                    with the argument patterns of galaxycomponents.cpp (disk/dust/stars fBm, dust2 ridged)
+  ref_star_layers.npz  star layers stamped by the reference's OWN Buffer2D::RenderGaussian (util/buffer2d.cpp:224-243) from
+                   star lists of gamer_b200_star_list (`python make_fixtures.py stars` regenerates this file alone)
   ref_path_frames.npz  whole frames rendered by the reference's OWN Rasterizer (Prepare, RenderPixels, renderPixel,
                    getIntensity, the GalaxyComponent classes, GamerCamera, Buffer2D::ToColorBuffer ...) compiled in
                    place against oracle/qtshim (oracle/ref_path_wrap.cpp), for the scenes of tests/ref_cases.py:
@@ -107,5 +109,32 @@ def ref_path_frames():
     print("wrote", len(frames), "reference frames/images")
 
 
+STAR_CASES = {   # name: (size, no_stars, base_size, size_spread, strength, seed)
+    # stamp width = star size * image size / 245 (buffer2d.cpp:165): sizes chosen so stamps are 4..20 pixels wide,
+    # overlap heavily (the per-channel max decides) and many hang over the image edges
+    "dense96": (96, 400, 20.0, 8.0, 1.0, 7),
+    "big_stamps64": (64, 60, 60.0, 20.0, 2.5, 11),
+    "edges33": (33, 120, 40.0, 20.0, 0.7, 3),
+}
+
+
+def star_layers():
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import ref_path_lib
+    from gamer_b200 import rasterizer
+    out = {}
+    for name, (size, n, base, spread, strength, seed) in STAR_CASES.items():
+        lst = rasterizer.star_list(size, n, base, spread, strength, seed)
+        out[name + "|xyw"] = np.array([[s.x, s.y, s.w] for s in lst], dtype=np.int32)
+        out[name + "|cs"] = np.array([list(s.cs) for s in lst], dtype=np.float32)
+        out[name + "|layer"] = ref_path_lib.stamp_stars(size, lst)
+        print(name, size, n, float(out[name + "|layer"].max()), int((out[name + "|layer"] > 0).sum()))
+    np.savez_compressed(os.path.join(HERE, "ref_star_layers.npz"), **out)
+
+
 if __name__ == "__main__":
-    main()
+    if sys.argv[1:] == ["stars"]:
+        star_layers()
+    else:
+        main()
+        star_layers()

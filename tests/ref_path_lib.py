@@ -45,8 +45,17 @@ def _lib(kind):
         L.refpath_trace.argtypes = [p, C.c_int, C.c_int, C.c_int, p]
         L.refpath_assemble.argtypes = [p, C.c_double, C.c_double, C.c_double, p, p]
         L.refpath_destroy.argtypes = [p]
+        L.refpath_stamp_stars.argtypes = [C.c_int, p, C.c_int, p]
         _loaded[kind] = L
     return _loaded[kind]
+
+
+def stamp_stars(size, stars, kind="src"):
+    """Buffer2D::RenderGaussian (util/buffer2d.cpp:224-243) of the reference itself for every star of a GamerStar
+    ctypes array, on a zeroed size x size buffer -> float32 [size, size, 3]."""
+    out = np.zeros((size, size, 3), np.float32)
+    assert _lib(kind).refpath_stamp_stars(int(size), C.addressof(stars) if len(stars) else None, len(stars), out.ctypes.data) == 0
+    return out
 
 
 def _f3(v):

@@ -315,6 +315,22 @@ int main() {
                                     double in = r - 0.01f; in = in < 1 ? in : 1; in = 0 < in ? in : 0; if (in > 0.1) in = 0.1; return in > 0.001; };
     printf("%%d %%d %%d %%d %%d\n", slab(q.h_gate), !slab(std::nextafter(q.h_gate, 9.0f)), radial(q.plen_thr),
            !radial(std::nextafter(q.plen_thr, 9.0f)), q.plen_lo < q.plen_thr && q.plen_thr < q.plen_hi);
+    // validation: operands the kernels' slow-path-free division / sqrt cannot take, and scenes whose march cannot
+    // make progress, are refused with GAMER_E_ARG instead of producing NaN or a kernel that never ends
+    int bad = 0, tried = 0;
+    auto refused = [&](GamerGalaxy gg, GamerComponent c1, GamerFrame ff) {
+        GamerComponent cc[9]; memcpy(cc, cs, sizeof cc); cc[1] = c1;
+        tried++; bad += gk_build_scene(&ff, &gg, cc, &sc, err, sizeof err) == GAMER_E_ARG;
+    };
+    { GamerGalaxy x = g; x.axis[0] = 0; refused(x, cs[1], f); }
+    { GamerGalaxy x = g; x.axis[1] = NAN; refused(x, cs[1], f); }
+    { GamerGalaxy x = g; x.winding_b = 0; refused(x, cs[1], f); }
+    { GamerGalaxy x = g; x.pos[2] = 1e6f; refused(x, cs[1], f); }
+    { GamerComponent c = cs[1]; c.z0 = 0; refused(g, c, f); }
+    { GamerComponent c = cs[1]; c.scale = 1e6; refused(g, c, f); }
+    { GamerComponent c = cs[1]; c.r0 = INFINITY; refused(g, c, f); }
+    { GamerFrame x = f; x.min_ray_step = 1e-7; refused(g, cs[1], x); }
+    printf("%%d %%d %%d\n", bad, tried, gk_build_scene(&f, &g, cs, &sc, err, sizeof err) == GAMER_OK);
 }
 ''' % root)
     exe = tmp_path / "sb"
@@ -327,6 +343,7 @@ int main() {
     assert out[1] == "1 1 1 1", out[1]
     assert out[2] == "1", out[2]
     assert out[3] == "1 1 1 1 1", out[3]
+    assert out[4] == "8 8 1", out[4]
 
 
 def test_qtf_twirl_y_equals_qt_sequence_and_oracle_shim(tmp_path):

@@ -413,7 +413,92 @@ def test_progress_and_abort_from_another_thread():
             assert box["err"].code == _lib.E_ABORTED
         else:                                  # the frame finished before the abort was seen: a complete image
             assert np.isfinite(box["img"]).all()
-        full = ctx.render()                    # the context is usable again and renders the whole frame
+        # the context is usable again and renders the whole frame (a request that arrived after that render had
+        # consumed its own is sticky, like m_abort, and cancels exactly one more)
+        try:
+            full = ctx.render()
+        except _lib.GamerError as e:
+            assert e.code == _lib.E_ABORTED
+            full = ctx.render()
         assert ctx.progress() == 1.0 and (full > 0).any()
+    finally:
+        ctx.close()
+
+
+def test_abort_is_sticky_and_consumed_by_one_render():
+    """Rasterizer::Abort sets m_abort whenever it is called and RenderPixelsOMP resets it when it ends
+    (rasterizer.h:91-98, rasterizer.cpp:296-297,311): a request made while nothing renders — between the passes of a
+    multi-pass scene, during Prepare — cancels the NEXT render, once."""
+    from gamer_b200 import _lib
+    from gamer_b200.rasterizer import Context
+    ctx = Context([0])
+    try:
+        sc = scenes.single_galaxy_scene("Spiral", 96, "oblique")
+        ctx.upload(sc)
+        want = ctx.render().copy()
+        ctx.abort()                                            # idle: remembered
+        with pytest.raises(_lib.GamerError) as e:
+            ctx.render()
+        assert e.value.code == _lib.E_ABORTED
+        part = np.full((96, 96, 3), np.nan, dtype=np.float32)
+        ctx.copy_bands(0, part)                                # not a tile was drawn: the cleared frame
+        assert (part == 0).all()
+        assert np.array_equal(ctx.render(), want)              # the request is gone
+        ctx.abort()                                            # ... and across an upload
+        ctx.upload(sc)
+        with pytest.raises(_lib.GamerError):
+            ctx.render_device()
+        assert np.array_equal(ctx.render(), want)
+    finally:
+        ctx.close()
+
+
+def test_abort_reports_aborted_only_for_a_frame_cut_short():
+    """An abort fired at a random moment of a render: GAMER_E_ABORTED iff the device frame is incomplete; a request
+    that lands after the last tile leaves a complete frame, which is delivered (it used to be lost)."""
+    import threading, time
+    from gamer_b200 import _lib
+    from gamer_b200.rasterizer import Context
+    ctx = Context([0])
+    try:
+        n = 512
+        sc = scenes.single_galaxy_scene("Spiral", n, "oblique")
+        ctx.upload(sc)
+        want = ctx.render().copy()
+        t0 = time.perf_counter(); ctx.render_device(); dur = time.perf_counter() - t0
+        rng = np.random.default_rng(5)
+        outcomes = {"cut": 0, "complete": 0}
+        for trial in range(24):
+            delay = float(rng.uniform(0.0, 1.6 * dur))
+            box = {}
+
+            def work():
+                try:
+                    ctx.render_device()
+                except _lib.GamerError as e:
+                    box["err"] = e
+            t = threading.Thread(target=work)
+            t.start()
+            time.sleep(delay)
+            ctx.abort()
+            t.join(30)
+            assert not t.is_alive()
+            got = np.empty((n, n, 3), dtype=np.float32)
+            ctx.copy_bands(0, got)
+            complete = np.array_equal(got, want)
+            if "err" in box:
+                assert box["err"].code == _lib.E_ABORTED and not complete, f"trial {trial}: complete frame reported as aborted"
+                tiles_ok = np.array_equal(got[got.any(axis=2)], want[got.any(axis=2)])      # what was drawn is right
+                assert tiles_ok
+                outcomes["cut"] += 1
+            else:
+                assert complete, f"trial {trial}: incomplete frame reported as complete"
+                outcomes["complete"] += 1
+            # a request that arrived after the render consumed its own is still pending: drain it
+            try:
+                ctx.render_device()
+            except _lib.GamerError:
+                pass
+        assert outcomes["cut"] + outcomes["complete"] == 24
     finally:
         ctx.close()

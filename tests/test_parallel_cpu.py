@@ -75,3 +75,39 @@ def test_gloo_world2_gather(tmp_path):
     p = subprocess.run(cmd, capture_output=True, text=True, timeout=300, env=env)
     assert p.returncode == 0, p.stdout[-2000:] + p.stderr[-2000:]
     assert "rank 0 ok" in p.stdout and "rank 1 ok" in p.stdout
+
+
+def test_band_tile_of_a_frame_smaller_than_the_band_fan():
+    """height < BAND * world: some ranks own no band. band_tile returns None for them (they neither upload nor render)
+    and the others still cover the frame exactly (it used to produce a height-0 tile that upload rejects)."""
+    sc = scenes.single_galaxy_scene("Spiral", 64, "oblique")
+    tiles = [parallel.band_tile(sc, r, 4) for r in range(4)]
+    assert tiles[2] is None and tiles[3] is None
+    assert [t.frame.height for t in tiles[:2]] == [32, 32]
+    rows = sorted(y for r in range(4) for y in parallel.band_rows(r, 4, 64))
+    assert rows == list(range(64))
+
+
+def test_longest_job_first_balances_and_is_deterministic():
+    """The galaxy batch / frame sequence queue: greedy longest-processing-time on a cost proxy."""
+    rng = np.random.default_rng(0)
+    costs = list(rng.uniform(1, 100, 256))
+    for world in (1, 2, 4, 8):
+        jobs = parallel.longest_job_first(costs, world)
+        assert sorted(j for r in jobs for j in r) == list(range(256))                 # every job exactly once
+        loads = [sum(costs[j] for j in r) for r in jobs]
+        assert max(loads) - min(loads) <= max(costs)                                   # LPT bound on the spread
+        assert max(loads) <= sum(costs) / world * 4 / 3 + 1e-9                         # Graham's 4/3 bound (vs the mean)
+        assert all(costs[a] >= costs[b] for r in jobs for a, b in zip(r, r[1:]))       # each rank runs its longest first
+        assert jobs == parallel.longest_job_first(costs, world)                        # same table on every rank
+    # modulo assignment of a cost-sorted batch can be far worse: that is what the queue is for
+    skew = [100.0] * 8 + [1.0] * 56
+    lpt = max(sum(skew[j] for j in r) for r in parallel.longest_job_first(skew, 8))
+    mod = max(sum(skew[j] for j in parallel.units_of(r, 8, 64)) for r in range(8))
+    assert lpt <= mod
+
+
+def test_job_cost_counts_octaves_of_active_components():
+    sc = scenes.single_galaxy_scene("Spiral", 64, "oblique")
+    # Spiral.gax: bulge, disk(10), dust2(9), [inactive bulge], stars(10), disk(10)
+    assert parallel.job_cost(sc) == 64 * 64 * (1 + 10 + 9 + 10 + 10)

@@ -11,6 +11,8 @@ import pytest
 import ref_cases
 import ref_path_lib
 
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref_path_frames.npz")
 CASES = ref_cases.cases()
 KINDS = {"src": False, "o2": True}       # fixture suffix -> no_radial_gate
@@ -116,3 +118,55 @@ def test_gpu_tonemap_equals_reference_assemble(golden, gpu_ctx):
             img, shadow = gpu_ctx.tonemap(e, g, s, rgb)
             assert np.array_equal(img, golden["%s|tm%d|image" % (name, k)])
             assert np.array_equal(shadow, golden["%s|tm%d|shadow" % (name, k)])
+
+
+# ---- the star layer's stamping, pinned by the reference's own Buffer2D::RenderGaussian ------------------------------
+def _golden_star_cases():
+    g = np.load(os.path.join(ROOT, "tests", "golden", "ref_star_layers.npz"))
+    from gamer_b200._lib import GamerStar
+    for name in sorted({k.split("|")[0] for k in g.files}):
+        xyw, cs, layer = g[name + "|xyw"], g[name + "|cs"], g[name + "|layer"]
+        lst = (GamerStar * len(xyw))()
+        for s, (x, y, w), c in zip(lst, xyw, cs):
+            s.x, s.y, s.w = int(x), int(y), int(w)
+            s.cs[:] = [float(v) for v in c]
+        yield name, lst, layer
+
+
+def test_oracle_star_stamp_equals_reference_rendergaussian(oracle):
+    """tests/golden/ref_star_layers.npz holds layers stamped by the reference's OWN Buffer2D::RenderGaussian
+    (util/buffer2d.cpp:224-243, compiled in place: oracle/ref_path_wrap.cpp refpath_stamp_stars) from three star lists
+    with overlapping and border-crossing stamps. The oracle's restatement go_stamp_stars reproduces every float."""
+    n = 0
+    for name, lst, layer in _golden_star_cases():
+        assert (layer > 0).mean() > 0.2, name
+        assert np.array_equal(oracle.stamp_stars(layer.shape[0], lst), layer), name
+        n += 1
+    assert n == 3
+
+
+def test_reference_star_stamp_reproduces_golden():
+    """Where the reference library is present (the build container), it reproduces the committed layers."""
+    if not ref_path_lib.available("src"):
+        pytest.skip("oracle/_ref not built here")
+    for name, lst, layer in _golden_star_cases():
+        assert np.array_equal(ref_path_lib.stamp_stars(layer.shape[0], lst), layer), name
+
+
+@pytest.mark.gpu
+def test_gpu_star_layer_equals_reference_rendergaussian(gpu_ctx):
+    """K4 against the reference's own stamping: within one float ulp (the device's double exp and glibc's agree to an
+    ulp of double; the product with the colour is then rounded once), including tiles of the frame."""
+    import scenes
+    for name, lst, layer in _golden_star_cases():
+        size = layer.shape[0]
+        full = scenes.single_galaxy_scene("Spiral", size, "oblique")
+        gpu_ctx.upload(full)
+        got = gpu_ctx.render_stars(lst, want_layer=True)
+        ulp = np.spacing(np.abs(layer).astype(np.float32)).astype(np.float64)
+        assert np.all(np.abs(got.astype(np.float64) - layer) <= ulp), name
+        assert (got == layer).mean() > 0.98, name                  # and nearly all of it bit for bit
+        h = size // 2
+        gpu_ctx.upload(full.tile(3, 5, size - 7, h))
+        part = gpu_ctx.render_stars(lst, want_layer=True)
+        assert np.all(np.abs(part.astype(np.float64) - layer[5:5 + h, 3:size - 4]) <= ulp[5:5 + h, 3:size - 4]), name
