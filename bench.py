@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """bench.py — headline benchmark of the galaxy volume integrator (BASELINE.json metric).
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload NAME]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload NAME] [--mode frames|tiles]
 
 A "step" is one frame: K1 (ray march) + K2 (post-process) of a 2048x2048 render of Spiral.gax
 (arms + dust + stars; 10/9/10 noise octaves hard-coded per class) at the reference step count
@@ -11,6 +11,13 @@ one per rank (weak scaling, no data-path collective).  `value` = ray samples/s (
 Rasterizer::getIntensity, counted exactly by the instrumented kernel; same integer as the CPU
 oracle) with the scene resident on the device; `e2e` = the same through the host-buffer C-ABI
 calls (scene upload, D2H of the float framebuffer and the 8-bit image inside the timed region).
+
+Beside the headline the line carries, under "also", the other BASELINE configs as measured workloads:
+  tiles_sombrero_4096   C3: one 4096^2 edge-on frame split into interleaved 32-row bands over the ranks + the final gather
+  sequence_1920x1080    C4: the 360-frame rotating-camera sequence, frame k on rank k mod N
+  batch_256_1024        C5: 256 seeded random galaxies at 1024^2, longest-job-first over the ranks
+and, at N = 1, "parity": the rows the cpu_baseline leg renders with the reference's own code compared with the same
+rows of the GPU frame, and the C2a in-disk view ("cli_view").
 """
 import argparse
 import json
@@ -29,8 +36,8 @@ import numpy as np  # noqa: E402
 
 METRIC = "ray samples/s (and ms/frame) at 2048x2048"
 UNIT = "ray samples/s"
-SIZE = 2048
 FP32_LANES_PER_SM = 128
+RTOL, ATOL = 1e-3, 1e-5          # the parity bar on linear intensity (tests/test_gpu_parity.py)
 
 
 def orbit_view(frame_index: int, radius=0.9, elevation=math.asin(1 / math.sqrt(3)), fov=60.0):
@@ -49,6 +56,8 @@ WORKLOADS = {
     "spiral_512_cli_view": ("Spiral", 512, "cli"),
     "sombrero_4096_edge": ("Sombrero", 4096, "edge"),
 }
+L2_NOTE = ("GPU arm: a 256 MB device buffer is zeroed between timed iterations (outside the event bracket), inputs are a few KB "
+           "of scene parameters; CPU arm: not applicable")
 
 
 def make_scene(workload: str, frame_index: int, size=None):
@@ -57,9 +66,28 @@ def make_scene(workload: str, frame_index: int, size=None):
     return scenes.single_galaxy_scene(gal, size or sz, orbit_view(frame_index) if view is None else view)
 
 
+def workload_config(wl: str, mode: str, world: int) -> dict:
+    """The `config` object: what is rendered and how it is partitioned. Built the same way by both arms."""
+    from gamer_b200 import parallel
+    tiles = mode == "tiles"
+    return {"workload": wl, "mode": mode, "galaxy": WORKLOADS[wl][0] + ".gax (tests/golden/gax)", "size": WORKLOADS[wl][1],
+            "ray_step": "0.025f", "frames_per_step": 1 if tiles else world,
+            "parallelism": (f"interleaved {parallel.BAND}-row bands x{world} + gather to rank 0" if tiles else f"frames x{world}"),
+            "l2": L2_NOTE}
+
+
 def algorithmic_flop(cnt: dict) -> float:
     """100 per simplex octave + 64 per component evaluation + 32 per sample + 18 per gate."""
     return 100.0 * cnt["octaves"] + 64.0 * cnt["comp_evals"] + 32.0 * cnt["samples"] + 18.0 * cnt["gates"]
+
+
+def host_threads() -> int:
+    """The host cores this process may use. Asked for explicitly everywhere: under torch.distributed.run
+    OMP_NUM_THREADS is 1, which silently reduced the reference arm of round 1 to one thread at N > 1."""
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
 
 
 class ClockSampler:
@@ -124,30 +152,39 @@ class CpuArm:
     (-Ofast -fopenmp, OpenMP over pixels like RenderPixelsOMP) — used whenever that library travelled here and
     the host has AVX2. kind "port": the oracle restatement built on this machine with -Ofast -march=native
     -fopenmp. Ray samples are counted by the oracle on the same rows (its march is bit-identical to the
-    reference's, tests/test_ref_path.py); the count is outside the timed region."""
+    reference's, tests/test_ref_path.py); the count is outside the timed region.
+    Nothing here loads libgamer_b200.so: the scene's camera matrix and galaxy rotation come from the oracle's host math."""
 
     def __init__(self, workload: str, row_stride: int, threads: int = 0, force_port: bool = False):
         import oracle_lib
         import ref_path_lib
-        import scenes
-        from gamer_b200.model import GalaxyInstance
-        self.workload, self.row_stride = workload, row_stride
-        self.scene = cpu_sample_scene(workload, row_stride)
+        from gamer_b200 import model
         self.oracle = oracle_lib.load(fast=True)
-        self.rows, self.size = self.scene.frame.height, self.scene.frame.full_size
-        self.ref = None
-        self.threads = threads
-        if ref_path_lib.available("fast") and not force_port:
-            name, size, view = WORKLOADS[workload]
-            view = orbit_view(0) if view is None else view
-            rp = scenes.rendering_params(size, view)
-            gi = GalaxyInstance(scenes.load_galaxy(name), name, (0, 0, 0), (0, 1, 0), 1.0, 0.0)
-            self.ref = ref_path_lib.RefRasterizer(rp, [gi], "fast")
-            self.ref.render_rows(0, row_stride, 0, 1, prepare=True)      # Rasterizer::Prepare, once, untimed
+        model.set_host_math(self.oracle.camera_inv_vp, self.oracle.rotation_to)
+        try:
+            import scenes
+            self.workload, self.row_stride = workload, row_stride
+            self.scene = cpu_sample_scene(workload, row_stride)
+            self.rows, self.size = self.scene.frame.height, self.scene.frame.full_size
+            self.ref = None
+            self.threads = threads or host_threads()
+            if ref_path_lib.available("fast") and not force_port:
+                name, size, view = WORKLOADS[workload]
+                view = orbit_view(0) if view is None else view
+                rp = scenes.rendering_params(size, view)
+                gi = model.GalaxyInstance(scenes.load_galaxy(name), name, (0, 0, 0), (0, 1, 0), 1.0, 0.0)
+                self.ref = ref_path_lib.RefRasterizer(rp, [gi], "fast")
+                self.ref.render_rows(0, row_stride, 0, 1, prepare=True)      # Rasterizer::Prepare, once, untimed
+        finally:
+            model.set_host_math()
         self.kind = "reference" if self.ref else "port"
-        _, cnt = self.oracle.render(self.scene)
+        # the exact work and the parity pixels come from the STRICT oracle build (IEEE arithmetic, bit-equal to the
+        # reference's own sources on the golden frames); the timed builds use the reference's -Ofast flags, whose
+        # fast-math changes roundings (and drops the `intensity > 0.001` test, see gamer_b200.h) — a few samples in 7e7
+        self.strict_pixels, cnt = oracle_lib.load().render(self.scene, self.threads)
+        self.counts = cnt
         self.samples = cnt["samples"]
-        self.cores = threads or self.oracle.max_threads()
+        self.cores = self.threads
 
     def step(self) -> float:
         t0 = time.perf_counter()
@@ -161,20 +198,11 @@ class CpuArm:
         what = ("the reference's own code (oracle/_ref/libgamer_ref_path_fast.so: -Ofast -march=x86-64-v3 -fopenmp)"
                 if self.ref else "oracle port (-Ofast -march=native -fopenmp)")
         return (f"frame 0 of {self.workload}, every {self.row_stride}th row ({self.rows} of {self.size} rows, "
-                f"{self.samples} ray samples), pixel loop only, {what}")
+                f"{self.samples} ray samples), pixel loop only, {self.cores} threads, {what}")
 
     def close(self):
         if self.ref:
             self.ref.close()
-
-
-def time_cpu(workload: str, row_stride: int, repeats: int = 1):
-    """cpu_baseline leg. Returns (samples/s, cores, sample description, seconds, kind)."""
-    arm = CpuArm(workload, row_stride)
-    best = min(arm.step() for _ in range(repeats))
-    out = (arm.samples / best, arm.cores, arm.describe() + f", best of {repeats}", best, arm.kind, port_value(arm))
-    arm.close()
-    return out
 
 
 def port_value(arm: "CpuArm"):
@@ -184,23 +212,206 @@ def port_value(arm: "CpuArm"):
     the STRONGER CPU baseline and is reported beside the reference."""
     if arm.kind != "reference":
         return None
-    port = CpuArm(arm.workload, arm.row_stride, force_port=True)
+    port = CpuArm(arm.workload, arm.row_stride, arm.threads, force_port=True)
     dt = min(port.step() for _ in range(2))
     return {"value": port.samples / dt, "unit": UNIT, "cores": port.cores, "kind": "port"}
 
 
-# dram__bytes_read.sum + dram__bytes_write.sum of one k1_march launch, from the `ncu --set full` capture
-# summarised in profiles/r01_k1_ncu_summary.csv (the 50 MB framebuffer is still in the 126 MB L2 when the
-# kernel ends, so DRAM sees ~8 MB; the algorithmic bytes are 12 B/pixel = 50 MB)
-K1_DRAM_TRAFFIC = {"spiral_2048_oblique_orbit": 74752 + 7794432, "spiral_2048_cli_view": 87552 + 9464832}
-# the same for one k2_tonemap_v4 launch at 2048^2 (profiles/r01_k2_ncu_summary.csv): the 50 MB frame is read from DRAM,
-# the two 16.8 MB images it writes are still in L2 when it ends (algorithmic bytes: 84 MB)
-K2_DRAM_TRAFFIC = {2048: 50363648 + 3948032}
+def parity_against_cpu_rows(ctx, arm: "CpuArm") -> dict:
+    """Parity AT THE BENCHMARKED SIZE: the rows of the cpu_baseline sample rendered by the strict CPU oracle (bit-equal
+    to the reference's own sources on the golden frames, tests/test_ref_path.py) against the same rows of the GPU frame,
+    through the C ABI; the GPU's exact counters for those rows against the oracle's; and the reference harness's own
+    criterion — identical 8-bit values (tools/galaxy_repro.py:988-995) — as the fraction of equal channel values."""
+    ctx.upload(arm.scene)
+    cnt = ctx.render_counted()
+    gpu = ctx.render()
+    _, gpu_img = ctx.tonemap(1.0, 1.0, 1.0)
+    cpu = arm.strict_pixels.reshape(gpu.shape)
+    _, cpu_img = arm.oracle.tonemap(cpu)
+    err = np.abs(gpu.astype(np.float64) - cpu) / (RTOL * np.abs(cpu.astype(np.float64)) + ATOL)
+    g8 = gpu_img.view(np.uint8).reshape(-1, 4)[:, :3]
+    c8 = cpu_img.view(np.uint8).reshape(-1, 4)[:, :3]
+    return {"against": "CPU oracle, strict IEEE build (oracle/gamer_oracle.cpp)", "rows": int(arm.rows), "row_stride": int(arm.row_stride), "size": int(arm.size),
+            "max_err_over_bound": float(err.max()), "bound": f"|gpu-cpu| <= {RTOL}*|cpu| + {ATOL} per channel",
+            "samples_equal": bool(cnt["samples"] == arm.counts["samples"] and cnt["rays"] == arm.counts["rays"]
+                                  and cnt["gates"] == arm.counts["gates"]),
+            "ray_samples": int(cnt["samples"]), "eight_bit_equal_frac": float((g8 == c8).mean()),
+            "eight_bit_max_diff": int(np.abs(g8.astype(np.int16) - c8.astype(np.int16)).max())}
+
+
+class SharedHostFrame:
+    """One page-locked host buffer that every rank of the node maps (a file in /dev/shm, cudaHostRegister'ed by each
+    process): the destination of gamer_b200_copy_bands, so the tile partition's frame is assembled on the host by all
+    ranks in parallel, each over its own PCIe link, instead of one rank copying the gathered 268 MB alone."""
+
+    def __init__(self, tag: str, nbytes: int, rank: int, barrier):
+        import torch
+        self.rank, self.barrier, self.nbytes = rank, barrier, nbytes
+        self.path = f"/dev/shm/gamer_b200_{tag}_{os.environ.get('MASTER_PORT', str(os.getppid()))}"
+        if rank == 0:
+            with open(self.path, "wb") as fh:
+                fh.truncate(nbytes)
+        barrier()
+        self.mm = np.memmap(self.path, dtype=np.uint8, mode="r+", shape=(nbytes,))
+        self.ptr = self.mm.ctypes.data
+        rc = torch.cuda.cudart().cudaHostRegister(self.ptr, nbytes, 0)
+        self.registered = int(rc) == 0
+
+    def close(self):
+        import torch
+        if self.registered:
+            torch.cuda.cudart().cudaHostUnregister(self.ptr)
+        del self.mm
+        self.barrier()
+        if self.rank == 0 and os.path.exists(self.path):
+            os.unlink(self.path)
+
+
+def run_jobs(ctx, jobs, my_ids, rank, world, barrier, reduce_max, reduce_sum, unit_name, e2e_contexts=3):
+    """A list of independent render jobs (frames of a sequence, galaxies of a batch): this rank renders jobs[i] for i in
+    my_ids, in that order. No collective in the data path. Device time over the whole list with CUDA events on the
+    context's stream (max over ranks); e2e through host buffers, frames alternating over e2e_contexts contexts."""
+    import torch
+    from gamer_b200.rasterizer import Context
+    mine = [jobs[i] for i in my_ids]
+    counts = {"samples": 0, "octaves": 0}
+    for sc in mine:                                   # exact work, instrumented kernel, untimed
+        ctx.upload(sc)
+        c = ctx.render_counted()
+        counts["samples"] += c["samples"]
+        counts["octaves"] += c["octaves"]
+    stream = torch.cuda.ExternalStream(ctx.stream(0), device=torch.device("cuda", torch.cuda.current_device()))
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    for sc in mine[:3]:                               # warm-up
+        ctx.upload(sc); ctx.render_device(); ctx.tonemap_device(1.0, 1.0, 1.0)
+    barrier()
+    l0 = ctx.launches()
+    e0.record(stream)
+    for sc in mine:
+        ctx.upload(sc)
+        ctx.render_device()
+        ctx.tonemap_device(1.0, 1.0, 1.0)
+    e1.record(stream)
+    barrier()
+    dev_ms = e0.elapsed_time(e1) if mine else 0.0
+    launches = ctx.launches() - l0
+    # e2e: upload + K1 + D2H float frame + K2 + D2H image per job, host buffers sized for the largest job
+    px = max((sc.frame.width * sc.frame.height for sc in mine), default=1)
+    nctx = max(1, min(e2e_contexts, len(mine)))
+    ctxs = [ctx] + [Context([torch.cuda.current_device()]) for _ in range(nctx - 1)]
+    bufs = [(torch.empty(px * 3, dtype=torch.float32).pin_memory(), torch.empty(px, dtype=torch.int32).pin_memory()) for _ in ctxs]
+
+    def worker(w):
+        c, (hr, hi) = ctxs[w], bufs[w]
+        for sc in mine[w::nctx]:
+            c.upload(sc)
+            c.render_ptr(hr.data_ptr())
+            c.tonemap_ptr(1.0, 1.0, 1.0, None, hi.data_ptr())
+    barrier()
+    t0 = time.perf_counter()
+    th = [threading.Thread(target=worker, args=(w,)) for w in range(nctx)]
+    for t_ in th:
+        t_.start()
+    for t_ in th:
+        t_.join()
+    e2e_mine = time.perf_counter() - t0
+    barrier()
+    for c in ctxs[1:]:
+        c.close()
+    del bufs
+    dmax, emax = reduce_max([dev_ms, e2e_mine * 1e3])
+    dsum, nsum, ssum, lsum, bsum = reduce_sum([dev_ms, float(len(mine)), float(counts["samples"]), float(launches),
+                                               float(sum(sc.frame.width * sc.frame.height * 16 for sc in mine))])
+    return {"unit": unit_name + "/s", "value": nsum / (dmax * 1e-3) if dmax else None, "n_units": int(nsum), "ms_total": dmax,
+            "rank_ms_max": dmax, "rank_ms_mean": dsum / world, "ray_samples_per_s": ssum / (dmax * 1e-3) if dmax else None,
+            "e2e": {"value": nsum / (emax * 1e-3) if emax else None, "unit": unit_name + "/s", "ms_total": emax, "contexts": nctx,
+                    "d2h_bytes_total": int(bsum)},
+            "gpu_launches": int(lsum)}
+
+
+# dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the dominant kernel, from an `ncu --set full` capture;
+# it belongs to the library build the capture was taken with and says so (traffic_source). The 50 MB framebuffer is
+# still in the 126 MB L2 when K1 ends, so DRAM sees ~8 MB; the algorithmic bytes are 12 B/pixel = 50 MB.
+K1_DRAM_TRAFFIC = {"spiral_2048_oblique_orbit": (653568 + 7398912, "profiles/r02_k1_ncu_summary.csv")}
+K2_DRAM_TRAFFIC = {2048 * 2048: (50363648 + 3948032, "profiles/r01_k2_ncu_summary.csv")}
+
+
+def time_frames(ctx, scenes_, Wm, K, stream, flush, barrier, after_kernels=None):
+    """W untimed + K timed frames on the device: per frame upload (host) -> [flush L2] -> event -> K1 -> K2 -> [after_kernels]
+    -> event. Returns (sum of the K event intervals in ms, per-frame K1 ms list, per-frame K2 ms list, launches)."""
+    import torch
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+
+    def step(i, k=None):
+        if scenes_[i] is None:                      # a rank without rows in tiles mode
+            if after_kernels:
+                after_kernels(None)
+            return
+        ctx.upload(scenes_[i])
+        with torch.cuda.stream(stream):
+            flush.zero_()
+            if k is not None:
+                ev[k][0].record(stream)
+            ctx.render_device()
+            ctx.tonemap_device(1.0, 1.0, 1.0)
+            if after_kernels:
+                after_kernels(ctx)
+            if k is not None:
+                ev[k][1].record(stream)
+    for i in range(Wm):
+        step(i)
+    barrier()
+    l0 = ctx.launches()
+    k1, k2 = [], []
+    for k in range(K):
+        step(Wm + k, k)
+        if scenes_[Wm + k] is not None:
+            a, b = ctx.kernel_ms()
+            k1.append(a); k2.append(b)
+    barrier()
+    dev_ms = sum(e0.elapsed_time(e1) for (e0, e1), sc in zip(ev, scenes_[Wm:]) if sc is not None)
+    return dev_ms, k1, k2, ctx.launches() - l0
+
+
+def time_e2e(ctx, scenes_, first, count, nctx, size, barrier):
+    """count frames end to end through host buffers (upload, K1, D2H 12 B/px, K2, D2H 4 B/px), alternating over nctx
+    independent contexts with one host thread each (nctx = 1: strictly serial). Returns (seconds, checksum)."""
+    import torch
+    from gamer_b200.rasterizer import Context
+    dev = torch.cuda.current_device()
+    ctxs = [ctx] + [Context([dev]) for _ in range(nctx - 1)]
+    bufs = [(torch.empty((size, size, 3), dtype=torch.float32).pin_memory(), torch.empty((size, size), dtype=torch.int32).pin_memory())
+            for _ in ctxs]
+
+    def worker(w, lo, n):
+        c, (hr, hi) = ctxs[w], bufs[w]
+        for i in range(lo + w, lo + n, nctx):
+            c.upload(scenes_[i])
+            c.render_ptr(hr.data_ptr())
+            c.tonemap_ptr(1.0, 1.0, 1.0, None, hi.data_ptr())
+
+    def run(lo, n):
+        th = [threading.Thread(target=worker, args=(w, lo, n)) for w in range(nctx)]
+        for t_ in th:
+            t_.start()
+        for t_ in th:
+            t_.join()
+    run(0, min(first, 3))
+    barrier()
+    t0 = time.perf_counter()
+    run(first, count)
+    barrier()
+    secs = time.perf_counter() - t0
+    checksum = float(bufs[0][0][::64, ::64].double().sum())
+    for c in ctxs[1:]:
+        c.close()
+    return secs, checksum
 
 
 def run_ours(args):
     import torch
     import torch.distributed as dist
+    from gamer_b200 import parallel
     from gamer_b200.rasterizer import Context
 
     rank = int(os.environ.get("RANK", "0"))
@@ -215,189 +426,200 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
+    def reduce_(vals, op):
+        t = torch.tensor(vals, dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(t, op=op)
+        return t.tolist()
+    reduce_max = lambda v: reduce_(v, dist.ReduceOp.MAX)
+    reduce_sum = lambda v: reduce_(v, dist.ReduceOp.SUM)
+
     ctx = Context([local])
-    K, Wm = args.steps, args.warmup
-    wl = args.workload
-    size = WORKLOADS[wl][1]
-    tiles = args.mode == "tiles"
-    if tiles:       # strong scaling: every rank renders its interleaved bands of the SAME frame, then one gather
-        from gamer_b200 import parallel
-        full = [make_scene(wl, s) for s in range(Wm + K)]
-        scenes_ = [parallel.band_tile(sc, rank, world) for sc in full]
-    else:           # weak scaling: step s renders frames s*world .. s*world+world-1, one per rank
-        frames = [s * world + rank for s in range(Wm + K)]
-        scenes_ = [make_scene(wl, f) for f in frames]
-
-    # exact work of every timed frame (instrumented kernel, outside the timed region)
-    counts = []
-    for sc in scenes_[Wm:]:
-        ctx.upload(sc)
-        counts.append(ctx.render_counted())
-    my_samples = sum(c["samples"] for c in counts)
-    my_flop = sum(algorithmic_flop(c) for c in counts)
-
     stream = torch.cuda.ExternalStream(ctx.stream(0), device=torch.device("cuda", local))
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")       # > 126 MB L2
-    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+    peaks, peak_src = measured_peaks()
+    sm_count = torch.cuda.get_device_properties(local).multi_processor_count
+    sm_max = float(peaks.get("sm_max_mhz", 1965.0))
+    fp32_peak = sm_count * FP32_LANES_PER_SM * 2 * sm_max * 1e6 / 1e12
+    hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
 
-    gathered = [None, None]
+    def leg(wl, mode, K, Wm, want_clocks=False, e2e_contexts=(1,)):
+        """One workload in one partition mode -> the numbers of a bench line (rank 0 gets the dict, others None)."""
+        size = WORKLOADS[wl][1]
+        tiles = mode == "tiles"
+        if tiles:       # strong scaling: every rank renders its interleaved bands of the SAME frame, then one gather
+            scenes_ = [parallel.band_tile(make_scene(wl, s), rank, world) for s in range(Wm + K)]
+        else:           # weak scaling: step s renders frames s*world .. s*world+world-1, one per rank
+            scenes_ = [make_scene(wl, s * world + rank) for s in range(Wm + K)]
+        counts = []
+        for sc in scenes_[Wm:]:     # exact work of every timed frame (instrumented kernel, outside the timed region)
+            if sc is not None:
+                ctx.upload(sc)
+                counts.append(ctx.render_counted())
+        my_samples = sum(c["samples"] for c in counts)
+        my_flop = sum(algorithmic_flop(c) for c in counts)
+        my_px = scenes_[Wm].frame.width * scenes_[Wm].frame.height if scenes_[Wm] is not None else 0
 
-    def step_device(i, timed_idx=None):
-        ctx.upload(scenes_[i])                      # host-side: scene -> kernel parameter block
-        with torch.cuda.stream(stream):
-            flush.zero_()
-            if timed_idx is not None:
-                ev[timed_idx][0].record(stream)
-            ctx.render_device()                     # K1
-            ctx.tonemap_device(1.0, 1.0, 1.0)       # K2
-            if tiles and world > 1:                 # K3: the one exchange step — gather the disjoint bands
-                rgb_t, _, img_t = ctx.device_tensors()
-                gathered[0] = parallel.gather_bands(rgb_t, size, rank, world)
-                gathered[1] = parallel.gather_bands(img_t, size, rank, world)
-            if timed_idx is not None:
-                ev[timed_idx][1].record(stream)
+        gathered = [None, None]
 
-    for i in range(Wm):
-        step_device(i)
-    clocks = ClockSampler(local)
-    barrier()
-    if rank == 0:
-        clocks.start()
-    l0 = ctx.launches()
-    k1_ms, k2_ms = [], []
-    t_wall0 = time.perf_counter()
-    for k in range(K):
-        step_device(Wm + k, k)
-        a, b = ctx.kernel_ms()
-        k1_ms.append(a)
-        k2_ms.append(b)
-    barrier()
-    t_wall = time.perf_counter() - t_wall0
-    launches = ctx.launches() - l0
-    clk = clocks.stop() if rank == 0 else None
-    dev_ms = sum(e0.elapsed_time(e1) for e0, e1 in ev)
+        def gather(c):              # K3: the one exchange step — the disjoint bands to rank 0 over NVLink
+            if c is None:
+                rgb_t = torch.empty((0, size, 3), dtype=torch.float32, device="cuda")
+                img_t = torch.empty((0, size), dtype=torch.int32, device="cuda")
+            else:
+                rgb_t, _, img_t = c.device_tensors()
+            gathered[0] = parallel.gather_bands(rgb_t, size, rank, world)
+            gathered[1] = parallel.gather_bands(img_t, size, rank, world)
+        clocks = ClockSampler(local)
+        if want_clocks and rank == 0:
+            clocks.start()
+        dev_ms, k1_ms, k2_ms, launches = time_frames(ctx, scenes_, Wm, K, stream, flush, barrier,
+                                                     gather if tiles and world > 1 else None)
+        clk = clocks.stop() if want_clocks and rank == 0 else None
+        gathered[:] = [None, None]
 
-    # ---- e2e: host buffers through the C ABI (upload + K1 + D2H float frame + K2 + D2H 8-bit image) ----
-    host_rgb = torch.empty((size, size, 3), dtype=torch.float32, pin_memory=True)
-    host_img = torch.empty((size, size), dtype=torch.int32, pin_memory=True)
+        # ---- e2e: host buffers through the C ABI ----
+        e2e = {}
+        if tiles and world > 1:
+            # every rank copies its own bands straight into ONE page-locked host frame all ranks map
+            # (gamer_b200_copy_bands): no device collective and no serial copy on the host path
+            shm_rgb = SharedHostFrame("rgb", size * size * 12, rank, barrier)
+            shm_img = SharedHostFrame("img", size * size * 4, rank, barrier)
 
-    def step_e2e(i):
-        ctx.upload(scenes_[i])
-        if tiles and world > 1:                     # bands stay on the device, gather over NVLink, rank 0 reads the frame
-            step_device(i)
-            if rank == 0:
-                with torch.cuda.stream(stream):
-                    host_rgb.copy_(gathered[0], non_blocking=True)
-                    host_img.copy_(gathered[1], non_blocking=True)
-            stream.synchronize()
+            def e2e_step(i):
+                if scenes_[i] is not None:
+                    ctx.upload(scenes_[i])
+                    ctx.render_device()
+                    ctx.tonemap_device(1.0, 1.0, 1.0)
+                    ctx.copy_bands(0, shm_rgb.ptr)
+                    ctx.copy_bands(2, shm_img.ptr)
+            for i in range(min(Wm, 3)):
+                e2e_step(i)
+            barrier()
+            t0 = time.perf_counter()
+            for i in range(Wm, Wm + K):
+                e2e_step(i)
+                barrier()                           # the frame is complete on the host when every rank has copied
+            secs = time.perf_counter() - t0
+            chk = float(np.frombuffer(shm_rgb.mm, dtype=np.float32).reshape(size, size, 3)[::64, ::64].astype(np.float64).sum()) if rank == 0 else 0.0
+            e2e[1] = (secs, chk, "each rank copies its bands into one shared page-locked host frame (gamer_b200_copy_bands)",
+                      shm_rgb.registered and shm_img.registered)
+            shm_rgb.close(); shm_img.close()
         else:
-            ctx.render_ptr(host_rgb.data_ptr())
-            ctx.tonemap_ptr(1.0, 1.0, 1.0, None, host_img.data_ptr())
+            for nctx in e2e_contexts:
+                secs, chk = time_e2e(ctx, scenes_, Wm, K, nctx, size, barrier)
+                e2e[nctx] = (secs, chk, "serial: one context, one host thread" if nctx == 1 else
+                             f"{nctx} contexts, one host thread each: one frame's D2H overlaps the next frame's kernels", True)
 
-    # Two independent contexts, one host thread each, take alternate frames: the blocking calls of one
-    # (D2H of frame k) overlap the kernels of the other (frame k+1). Every frame still goes through
-    # upload -> render -> tonemap with its own host<->device copies inside the timed region.
-    pipelined = not (tiles and world > 1) and args.e2e_contexts > 1
-    if pipelined:
-        ctxs = [ctx] + [Context([local]) for _ in range(args.e2e_contexts - 1)]
-        bufs = [(host_rgb, host_img)] + [(torch.empty_like(host_rgb).pin_memory(), torch.empty_like(host_img).pin_memory())
-                                         for _ in range(args.e2e_contexts - 1)]
-
-        def worker(w, first, count):
-            c, (hr, hi) = ctxs[w], bufs[w]
-            for i in range(first + w, first + count, len(ctxs)):
-                c.upload(scenes_[i])
-                c.render_ptr(hr.data_ptr())
-                c.tonemap_ptr(1.0, 1.0, 1.0, None, hi.data_ptr())
-
-        def run_e2e(first, count):
-            th = [threading.Thread(target=worker, args=(w, first, count)) for w in range(len(ctxs))]
-            for t_ in th:
-                t_.start()
-            for t_ in th:
-                t_.join()
-    else:
-        def run_e2e(first, count):
-            for i in range(first, first + count):
-                step_e2e(i)
-
-    run_e2e(0, min(Wm, 3))
-    barrier()
-    t0 = time.perf_counter()
-    run_e2e(Wm, K)
-    barrier()
-    e2e_s = time.perf_counter() - t0
-    checksum = float(host_rgb[::64, ::64].double().sum())
-    if pipelined:
-        for c in ctxs[1:]:
-            c.close()
-
-    # ---- K2 alone, cold L2, for its HBM roofline ----
-    k2_cold = []
-    for _ in range(5):
-        with torch.cuda.stream(stream):
-            flush.zero_()
-        ctx.tonemap_device(1.0, 1.0, 1.0)
-        k2_cold.append(ctx.kernel_ms()[1])
-
-    # ---- reduce over ranks: time = max, work = sum ----
-    t = torch.tensor([dev_ms, e2e_s * 1e3, t_wall * 1e3], dtype=torch.float64, device="cuda")
-    w = torch.tensor([float(my_samples), my_flop, float(launches)], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        dist.all_reduce(w, op=dist.ReduceOp.SUM)
-    dev_ms_max, e2e_ms_max, wall_ms_max = t.tolist()
-    tot_samples, tot_flop, tot_launches = w.tolist()
-
-    if rank == 0:
-        peaks, peak_src = measured_peaks()
-        sm_count = torch.cuda.get_device_properties(local).multi_processor_count
-        sm_max = float(peaks.get("sm_max_mhz", 1965.0))
-        fp32_peak = sm_count * FP32_LANES_PER_SM * 2 * sm_max * 1e6 / 1e12
-        k1_avg_ms = sum(k1_ms) / len(k1_ms)
-        k1_tflops = (my_flop / K) / (k1_avg_ms * 1e-3) / 1e12
-        px = size * size
-        k2_best = min(k2_cold)
-        k2_bytes = px * (12 + 4 + 4)
+        # ---- K2 alone, cold L2, for its HBM roofline (this rank's pixels) ----
+        k2_cold = []
+        if scenes_[Wm] is not None:
+            ctx.upload(scenes_[Wm]); ctx.render_device()
+            for _ in range(5):
+                with torch.cuda.stream(stream):
+                    flush.zero_()
+                ctx.tonemap_device(1.0, 1.0, 1.0)
+                k2_cold.append(ctx.kernel_ms()[1])
+        e2e_keys = sorted(e2e)
+        dev_ms_max, *e2e_ms_max = reduce_max([dev_ms] + [e2e[k][0] * 1e3 for k in e2e_keys])
+        tot_samples, tot_flop, tot_launches = reduce_sum([float(my_samples), my_flop, float(launches)])
+        if rank != 0:
+            return None
+        k1_avg_ms = sum(k1_ms) / max(len(k1_ms), 1)
+        k1_tflops = (my_flop / max(len(counts), 1)) / (k1_avg_ms * 1e-3) / 1e12 if k1_ms else 0.0
+        k2_best = min(k2_cold) if k2_cold else None
+        k2_bytes = my_px * (12 + 4 + 4)
+        best = min(range(len(e2e_keys)), key=lambda j: e2e_ms_max[j])
+        e2e_objs = {}
+        for j, kx in enumerate(e2e_keys):
+            e2e_objs[kx] = {"value": tot_samples / (e2e_ms_max[j] * 1e-3), "unit": UNIT,
+                            "h2d_bytes_per_step": (1 if tiles else world) * ctx_scene_bytes(scenes_[Wm]) if scenes_[Wm] is not None else 0,
+                            "d2h_bytes_per_step": (1 if tiles else world) * size * size * 16,
+                            "ms_per_step": e2e_ms_max[j] / K, "checksum": e2e[kx][1], "contexts": kx, "how": e2e[kx][2],
+                            "host_buffers_page_locked": bool(e2e[kx][3])}
+        traffic = K1_DRAM_TRAFFIC.get(wl) if mode == "frames" else None
+        k2_traffic = K2_DRAM_TRAFFIC.get(my_px)
         out = {
             "metric": METRIC, "value": tot_samples / (dev_ms_max * 1e-3), "unit": UNIT, "n_gpus": world,
             "steps": K, "warmup": Wm, "ms_per_step": dev_ms_max / K, "higher_is_better": True, "scaling": "strong" if tiles else "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": wl, "mode": args.mode, "galaxy": WORKLOADS[wl][0] + ".gax (tests/golden/gax)", "size": size,
-                       "ray_step": "0.025f", "frames_per_step": 1 if tiles else world,
-                       "parallelism": (f"interleaved {parallel.BAND}-row bands x{world} + NCCL gather to rank 0" if tiles
-                                       else f"frames x{world}"),
-                       "l2": "256 MB device buffer zeroed between timed iterations (outside the event bracket); "
-                             "inputs are a few KB of scene parameters",
-                       "ray_samples_per_frame": my_samples / K, "octaves_per_frame": sum(c["octaves"] for c in counts) / K},
+            "config": workload_config(wl, mode, world),
+            "work": {"ray_samples_per_frame": tot_samples / K / (1 if tiles else world),
+                     "octaves_per_frame_rank0": sum(c["octaves"] for c in counts) / max(len(counts), 1)},
             "gpu_launches": int(tot_launches),
-            "e2e": {"value": tot_samples / (e2e_ms_max * 1e-3), "unit": UNIT,
-                    "h2d_bytes_per_step": world * ctx_scene_bytes(scenes_[0]), "d2h_bytes_per_step": (1 if tiles else world) * px * 16,
-                    "ms_per_step": e2e_ms_max / K, "checksum": checksum,
-                    "contexts": args.e2e_contexts if pipelined else 1},
+            "e2e": e2e_objs[e2e_keys[best]],
             "roofline": {"kernel": "k1_march", "bound": "fp32", "achieved": k1_tflops, "peak": fp32_peak, "unit": "TFLOP/s",
-                         "frac": k1_tflops / fp32_peak, "traffic": K1_DRAM_TRAFFIC.get(wl),
+                         "frac": k1_tflops / fp32_peak, "traffic": traffic[0] if traffic else None,
+                         "traffic_source": (traffic[1] + " (one ncu --set full capture; not re-measured by this run)") if traffic else None,
                          "peak_source": f"{sm_count} SMs x 128 FP32 lanes x 2 flop x {sm_max:.0f} MHz (sm_max_mhz of "
                                         f"MEASURED_PEAKS.json, {peak_src}); the path is FP32/SFU-pipe bound, not HBM or tensor",
-                         "algorithmic_flop_per_launch": my_flop / K, "launch_ms": k1_avg_ms},
-            "roofline_k2": {"kernel": "k2_tonemap_v4", "bound": "hbm", "achieved": k2_bytes / (k2_best * 1e-3) / 1e9,
-                            "peak": float(peaks.get("hbm_gbs", 6650.0)), "unit": "GB/s",
-                            "frac": k2_bytes / (k2_best * 1e-3) / 1e9 / float(peaks.get("hbm_gbs", 6650.0)),
-                            "traffic": K2_DRAM_TRAFFIC.get(size) if args.mode == "frames" else None, "algorithmic_bytes_per_launch": k2_bytes, "launch_ms": k2_best,
-                            "peak_source": f"hbm_gbs of MEASURED_PEAKS.json ({peak_src})"},
-            "kernel_ms": {"k1_avg": k1_avg_ms, "k2_avg_in_step": sum(k2_ms) / len(k2_ms), "k2_cold_l2": k2_best,
-                          "wall_ms_per_step_incl_flush": wall_ms_max / K},
-            "clocks": clk,
+                         "algorithmic_flop_per_launch": my_flop / max(len(counts), 1), "launch_ms": k1_avg_ms},
+            "kernel_ms": {"k1_avg": k1_avg_ms, "k2_avg_in_step": sum(k2_ms) / max(len(k2_ms), 1), "k2_cold_l2": k2_best},
         }
+        if len(e2e_keys) > 1:
+            out["e2e_serial"] = e2e_objs[1]
+        if k2_best:
+            out["roofline_k2"] = {"kernel": "k2_tonemap_v4", "bound": "hbm", "achieved": k2_bytes / (k2_best * 1e-3) / 1e9,
+                                  "peak": hbm_peak, "unit": "GB/s", "frac": k2_bytes / (k2_best * 1e-3) / 1e9 / hbm_peak,
+                                  "traffic": k2_traffic[0] if k2_traffic else None, "traffic_source": k2_traffic[1] if k2_traffic else None,
+                                  "algorithmic_bytes_per_launch": k2_bytes, "pixels_this_rank": my_px, "launch_ms": k2_best,
+                                  "peak_source": f"hbm_gbs of MEASURED_PEAKS.json ({peak_src})"}
+        if clk:
+            out["clocks"] = clk
+        return out
+
+    K, Wm, wl = args.steps, args.warmup, args.workload
+    out = leg(wl, args.mode, K, Wm, want_clocks=True, e2e_contexts=(1, args.e2e_contexts) if args.e2e_contexts > 1 else (1,))
+
+    # ---- the other BASELINE configs, each a short measured workload of its own ----
+    also = {}
+    if not args.no_extras:
+        import scenes
+        t_ex = leg("sombrero_4096_edge", "tiles", 3, 3)
+        if rank == 0:
+            also["tiles_sombrero_4096"] = {k: t_ex[k] for k in ("value", "unit", "ms_per_step", "scaling", "config", "e2e", "gpu_launches", "kernel_ms")}
+        n_seq = args.sequence_frames
+        seq = [scenes.hd_frame_scene(k, n_frames=360) for k in range(n_seq)]
+        r = run_jobs(ctx, seq, parallel.units_of(rank, world, n_seq), rank, world, barrier, reduce_max, reduce_sum, "frames", args.e2e_contexts)
+        if rank == 0:
+            r["config"] = {"workload": "sequence_1920x1080", "frames": n_seq, "of": 360, "galaxy": "Spiral.gax", "size": "1920x1080 (rows 420..1499 of the 1920^2 image)",
+                           "parallelism": f"frame k -> rank k mod {world}", "l2": "frames differ (camera moves 1 deg per frame); no flush between them"}
+            also["sequence_1920x1080"] = r
+        n_gal = args.batch_galaxies
+        batch = [scenes.random_galaxy_scene(i, 1024) for i in range(n_gal)]
+        # cost of a job without an oracle: its exact algorithmic work at 1/256 of the pixels (64^2, counting kernel,
+        # ~0.1 ms each). Every rank measures all of them itself, so the table needs no exchange. The static proxy
+        # (pixels x octaves per in-slab sample, parallel.job_cost) ignores the view and left 9 % imbalance at N = 2.
+        costs = []
+        for i in range(n_gal):
+            ctx.upload(scenes.random_galaxy_scene(i, 64))
+            costs.append(algorithmic_flop(ctx.render_counted()) + 1.0)
+        table = parallel.longest_job_first(costs, world)
+        r = run_jobs(ctx, batch, table[rank], rank, world, barrier, reduce_max, reduce_sum, "galaxies", args.e2e_contexts)
+        if rank == 0:
+            r["config"] = {"workload": "batch_256_1024", "galaxies": n_gal, "of": 256, "size": 1024, "seed": 20261104,
+                           "parallelism": f"longest-job-first over {world} ranks on each galaxy's exact work at 64^2 (parallel.longest_job_first)",
+                           "l2": "every job is a different galaxy; no flush between them"}
+            also["batch_256_1024"] = r
+        if world == 1:
+            c = leg("spiral_2048_cli_view", "frames", 3, 3)
+            also["cli_view"] = {k: c[k] for k in ("value", "unit", "ms_per_step", "config", "roofline", "gpu_launches")}
+
+    if rank == 0:
         if world == 1 and not args.no_cpu:
-            v, cores, desc, secs, kind, port = time_cpu(wl, args.cpu_row_stride)
-            out["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": kind, "sample": desc, "seconds": secs}
+            arm = CpuArm(wl, args.cpu_row_stride)
+            best = min(arm.step() for _ in range(1))
+            out["cpu_baseline"] = {"value": arm.samples / best, "unit": UNIT, "cores": arm.cores, "kind": arm.kind,
+                                   "sample": arm.describe(), "seconds": best}
+            out["parity"] = parity_against_cpu_rows(ctx, arm)
+            port = port_value(arm)
             if port:
                 out["cpu_baseline"]["oracle_port"] = port
+            arm.close()
+        if also:
+            out["also"] = also
         print(json.dumps(out), flush=True)
-    # torch tensors that were used on the context's stream must be released while that stream still exists
-    gathered[:] = [None, None]
-    del flush, host_rgb, host_img
+    del flush
     torch.cuda.synchronize()
     torch.cuda.empty_cache()
     if world > 1:
@@ -413,8 +635,9 @@ def ctx_scene_bytes(scene) -> int:
 
 def run_reference(args):
     """Reference arm: the reference's CPU implementation of the path on the host cores (class CpuArm: the
-    reference's own sources compiled in place when oracle/_ref travelled here, else the oracle port), all host
-    threads, each step a bounded sample of the same workload."""
+    reference's own sources compiled in place when oracle/_ref travelled here, else the oracle port), ALL host
+    threads (asked for explicitly), each step a bounded sample of the same workload. Runs on rank 0 only; loads neither
+    torch nor libgamer_b200.so."""
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     if rank != 0:
@@ -429,18 +652,20 @@ def run_reference(args):
             times.append(dt)
     total = sum(times)
     value = samples * len(times) / total
-    size = WORKLOADS[wl][1]
     frac = sc.frame.height / sc.frame.full_size
-    desc = f"each step = {arm.describe()}; a whole frame is ~{1 / frac:.0f}x that"
+    desc = (f"each step = {arm.describe()}; a whole frame is ~{1 / frac:.0f}x that "
+            f"(~{1e3 * total / len(times) / frac:.0f} ms per full frame at this rate)")
+    loaded = [l.split()[-1] for l in open("/proc/self/maps") if "libgamer_b200" in l]
     out = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
-           "warmup": args.warmup, "ms_per_step": 1e3 * total / len(times), "higher_is_better": True, "scaling": "weak",
+           "warmup": args.warmup, "ms_per_step": 1e3 * total / len(times), "higher_is_better": True,
+           "scaling": "strong" if args.mode == "tiles" else "weak",
            "vs_baseline": None, "dtype": "f64/f32 (reference mix)", "data": "synthetic",
-           "config": {"workload": wl, "galaxy": WORKLOADS[wl][0] + ".gax (tests/golden/gax)", "size": size, "ray_step": "0.025f",
-                      "sample": desc, "est_ms_per_full_frame": 1e3 * total / len(times) / frac},
+           "config": workload_config(wl, args.mode, world),
            "cpu_baseline": {"value": value, "unit": UNIT, "cores": arm.cores, "kind": arm.kind, "sample": desc,
                             **({"oracle_port": port_value(arm)} if arm.kind == "reference" else {})},
            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-           "gpu_launches": 0}
+           "gpu_launches": 0, "product_library_loaded": bool(loaded)}
+    arm.close()
     print(json.dumps(out), flush=True)
 
 
@@ -453,10 +678,14 @@ def main():
     ap.add_argument("--workload", default="spiral_2048_oblique_orbit", choices=list(WORKLOADS))
     ap.add_argument("--mode", default="frames", choices=["frames", "tiles"],
                     help="N>1: frames = one frame per rank per step (weak, no collective); tiles = one frame split "
-                         "into interleaved row bands + NCCL gather (strong)")
+                         "into interleaved row bands + the final gather (strong)")
     ap.add_argument("--e2e-contexts", type=int, default=3,
-                    help="independent gamer_ctx (one host thread each) the e2e leg alternates frames over; 1 = strictly serial")
-    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+                    help="independent gamer_ctx (one host thread each) the pipelined e2e leg alternates frames over; the "
+                         "strictly serial figure (1 context) is always measured as well")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline and parity legs")
+    ap.add_argument("--no-extras", action="store_true", help="skip the C3 / C4 / C5 / C2a workloads carried under 'also'")
+    ap.add_argument("--sequence-frames", type=int, default=360, help="frames of the C4 sequence to render (of 360)")
+    ap.add_argument("--batch-galaxies", type=int, default=256, help="galaxies of the C5 batch to render (of 256)")
     ap.add_argument("--cpu-row-stride", type=int, default=16, help="cpu_baseline sample: every n-th row")
     ap.add_argument("--ref-row-stride", type=int, default=64, help="--impl reference step: every n-th row")
     args = ap.parse_args()

@@ -41,6 +41,18 @@ class Spectra:
         return None
 
 
+# Host math of the parameter model (camera matrix, galaxy rotation): the product library's by default. bench.py's
+# reference arm installs the CPU oracle's equivalents instead, so that arm never loads libgamer_b200.so at all.
+_host_math = None
+
+
+def set_host_math(camera_inv_vp=None, rotation_to=None):
+    """camera_inv_vp(cam, target, up, fov) -> 16 floats [row*4+col]; rotation_to(orient) -> (w, x, y, z).
+    None restores the product library (gamer_b200_camera_inv_vp / gamer_b200_rotation_to_orientation)."""
+    global _host_math
+    _host_math = (camera_inv_vp, rotation_to) if camera_inv_vp and rotation_to else None
+
+
 @dataclass
 class GamerCamera:
     m_camera: Sequence[float] = (3.0, 3.0, 3.0)
@@ -50,6 +62,8 @@ class GamerCamera:
 
     def setupViewmatrix(self) -> np.ndarray:
         """inverse(projection * view) as 16 float32 [row*4+col] (gamercamera.cpp:185-208)."""
+        if _host_math:
+            return np.array(_host_math[0](self.m_camera, self.m_target, self.m_up, float(self.m_perspective)), dtype=np.float32)
         lib = _lib.load()
         v3 = C.c_float * 3
         out = (C.c_float * 16)()
@@ -107,6 +121,8 @@ class GalaxyInstance:
 
     def rotmat(self):
         """setupQuaternions (galaxyinstance.cpp:69-71)."""
+        if _host_math:
+            return [float(v) for v in _host_math[1](self.m_orientation)]
         lib = _lib.load()
         q = (C.c_float * 4)()
         _lib.check(None, lib.gamer_b200_rotation_to_orientation((C.c_float * 3)(*self.m_orientation), q))

@@ -5,8 +5,8 @@ python -m pytest tests -m gpu -q -x 2>&1 | tail -3
 for f in "" gamer_b200/lib/variants/lib_*.so; do
   if [ -z "$f" ]; then unset GAMER_B200_LIB; name=base; else export GAMER_B200_LIB=$PWD/$f; name=$(basename $f .so); fi
   [ -n "$f" ] && [ ! -f "$f" ] && continue
-  python bench.py --steps 4 --warmup 3 --no-cpu > gpurun_out/ab_$name.json 2>> gpurun_out/ab.err
-  python bench.py --steps 2 --warmup 3 --no-cpu --workload spiral_2048_cli_view > gpurun_out/ab_cli_$name.json 2>> gpurun_out/ab.err
+  python bench.py --steps 4 --warmup 3 --no-cpu --no-extras > gpurun_out/ab_$name.json 2>> gpurun_out/ab.err
+  python bench.py --steps 2 --warmup 3 --no-cpu --no-extras --workload spiral_2048_cli_view > gpurun_out/ab_cli_$name.json 2>> gpurun_out/ab.err
   python - <<PY
 import json
 a=json.load(open("gpurun_out/ab_$name.json")); b=json.load(open("gpurun_out/ab_cli_$name.json"))
