@@ -43,12 +43,28 @@ WORKER = textwrap.dedent("""
             frame = parallel.gather_bands(rgb, size, rank, world)
             image = parallel.gather_bands(img, size, rank, world)
         stream.synchronize()
+        # the host-side gather: every rank copies its bands into ONE frame in shared memory (gamer_b200_copy_bands)
+        path = "/dev/shm/gamer_b200_test_%s_%s" % (os.environ["MASTER_PORT"], name)
+        if rank == 0:
+            with open(path, "wb") as fh:
+                fh.truncate(size * size * 16)
+        dist.barrier()
+        mm = np.memmap(path, dtype=np.uint8, mode="r+", shape=(size * size * 16,))
+        ctx.copy_bands(0, mm[: size * size * 12].ctypes.data)
+        ctx.copy_bands(2, mm[size * size * 12:].ctypes.data)
+        dist.barrier()
         if rank == 0:
             ctx.upload(sc)
             whole = ctx.render()
             argb, shadow = ctx.tonemap(1.0, 1.0, 1.0)
             assert np.array_equal(frame.cpu().numpy(), whole), name + ": sharded frame differs from single-GPU frame"
             assert np.array_equal(image.cpu().numpy().view(np.uint32), shadow), name + ": sharded image differs"
+            assert np.array_equal(np.frombuffer(mm[: size * size * 12], dtype=np.float32).reshape(size, size, 3), whole), name + ": copy_bands frame differs"
+            assert np.array_equal(np.frombuffer(mm[size * size * 12:], dtype=np.uint32).reshape(size, size), shadow), name + ": copy_bands image differs"
+        del mm
+        dist.barrier()
+        if rank == 0:
+            os.unlink(path)
     dist.barrier()
     ctx.close()
     dist.destroy_process_group()
