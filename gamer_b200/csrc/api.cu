@@ -32,6 +32,7 @@ struct Dev {
     int *abort_flag = nullptr;
     unsigned int *progress = nullptr;
     unsigned int *progress_host = nullptr;    // pinned
+    double *wtab = nullptr;                    // the frame's getWinding tables (scene_build.cpp), DEV_MAX_GALAXIES of them
     unsigned int n_blocks = 0;
     int rows = 0;                              // local rows this device renders
     DScene scene;
@@ -82,6 +83,7 @@ void free_dev(Dev &d) {
     if (d.counters) cudaFree(d.counters);
     if (d.abort_flag) cudaFree(d.abort_flag);
     if (d.progress) cudaFree(d.progress);
+    if (d.wtab) cudaFree(d.wtab);
     if (d.progress_host) cudaFreeHost(d.progress_host);
     for (auto &e : d.ev) if (e) cudaEventDestroy(e);
     if (d.st) cudaStreamDestroy(d.st);
@@ -261,6 +263,7 @@ int gamer_b200_create(gamer_ctx **out, const int32_t *device_ids, int32_t n_devi
         if (e == cudaSuccess) e = cudaMalloc(&d.counters, GAMER_CNT_N * sizeof(unsigned long long));
         if (e == cudaSuccess) e = cudaMalloc(&d.abort_flag, sizeof(int));
         if (e == cudaSuccess) e = cudaMalloc(&d.progress, 2 * sizeof(unsigned int));
+        if (e == cudaSuccess) e = cudaMalloc(&d.wtab, (size_t)DEV_MAX_GALAXIES * WT_DOUBLES_PER_GALAXY * sizeof(double));
         if (e == cudaSuccess) e = cudaHostAlloc(&d.progress_host, sizeof(unsigned int), cudaHostAllocDefault);
         if (e == cudaSuccess) e = cudaMemset(d.abort_flag, 0, sizeof(int));
         if (e == cudaSuccess) e = cudaMemset(d.progress, 0, 2 * sizeof(unsigned int));
@@ -301,8 +304,14 @@ int gamer_b200_upload(gamer_ctx *ctx, const GamerFrame *frame, const GamerGalaxy
             f.band_stride = MD_BAND_ROWS * n;
             f.height = d.rows > 0 ? d.rows : 1;
         }
-        int rc = gk_build_scene(&f, galaxies, components, &d.scene, msg, sizeof(msg));
+        std::vector<double> wtab_host;
+        int rc = gk_build_scene(&f, galaxies, components, &d.scene, msg, sizeof(msg), &wtab_host);
         if (rc) return set_err(ctx, rc, msg);
+        d.scene.wtab = d.wtab;
+        if (!wtab_host.empty()) {      // pageable source: staged before the call returns; ordered before the next kernel
+            CK(cudaSetDevice(d.device));
+            CK(cudaMemcpyAsync(d.wtab, wtab_host.data(), wtab_host.size() * sizeof(double), cudaMemcpyHostToDevice, d.st));
+        }
         if (d.rows > 0) {
             rc = ensure_capacity(ctx, d, (size_t)d.rows * frame->width);
             if (rc) return rc;

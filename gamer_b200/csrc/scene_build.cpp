@@ -42,8 +42,90 @@ void normalize3(const float in[3], float out[3]) {
 
 }  // namespace
 
+// ---- getWinding as a certified table --------------------------------------------------------------------------------
+// getWinding(rad) = atan(exp(-0.25 / (0.5 (rad + 0.05))) / windingB) * 2 * windingN (galaxycomponent.h:156-165) is, in
+// s = 1 / (rad + 0.05), the function G(s) = atan(exp(-s / 2) / windingB) * 2 windingN: analytic, with its nearest
+// singularities at distance pi from the real axis, so on intervals of width 0.25 a degree-9 Chebyshev interpolant is
+// accurate to ~1e-17 of the local magnitude. The kernel evaluates one reciprocal and one Horner chain instead of two
+// divisions, an exp and an atan in FP64 (a serial chain of ~90 operations, once per in-slab sample).
+// What the reference consumes is the FLOAT twirl angle float(W * winding * 180): the kernel checks that the table's
+// certified error bound cannot change that float and evaluates getWinding directly when it could (kernels.cu).
+// The certification is done here, against libm, on the radii the kernel can meet: a table that misses WT_CERT_REL is dropped.
+#define WT_CERT_REL 0x1p-46
+
+namespace {
+double winding_direct(const GamerGalaxy &g, float radius) {       // the reference's expression, in its operation order
+    const double r = double(radius) + 0.05;
+    return std::atan(std::exp(-0.25 / (0.5 * r)) / g.winding_b) * 2 * g.winding_n;
+}
+}  // namespace
+
+double gk_winding_from_table(const DGalaxy &d, const double *coeffs, float radius) {
+    const double s = 1.0 / (double(radius) + 0.05);
+    const double u = (s - d.wt_s0) * (1.0 / WT_H);
+    int i = int(u);
+    if (i < 0) i = 0;
+    if (i > d.wt_n - 1) i = d.wt_n - 1;
+    const double x = std::fma(2.0, u - double(i), -1.0);
+    const double *c = coeffs + d.wt_off + size_t(i) * WT_COEFFS;
+    double v = c[WT_COEFFS - 1];
+    for (int k = WT_COEFFS - 2; k >= 0; k--) v = std::fma(v, x, c[k]);
+    return v;
+}
+
+void gk_build_winding_table(const GamerGalaxy &g, DGalaxy &d, std::vector<double> &coeffs) {
+    d.wt_n = 0; d.wt_s0 = 0; d.wt_off = int32_t(coeffs.size());
+    // radius = |P| / axis.x with P inside the ellipsoid: at most max(axis) / |axis.x| (a little more for rounding)
+    const double amax = std::fmax(std::fabs(g.axis[0]), std::fmax(std::fabs(g.axis[1]), std::fabs(g.axis[2])));
+    const double r_max = 1.02 * amax / std::fabs(g.axis[0]) + 0.01;
+    const double s_hi = 20.0, s_lo = 1.0 / (r_max + 0.05);           // rad = 0 is s = 20
+    const int n = int(std::ceil((s_hi - s_lo) / WT_H)) + 1;
+    if (n > WT_MAX_INTERVALS || !(g.winding_b != 0)) return;
+    const double s0 = s_hi - n * WT_H + 0.5 * WT_H;                  // the last interval ends half an interval beyond s = 20
+    const size_t base = coeffs.size();
+    coeffs.resize(base + size_t(n) * WT_COEFFS);
+    auto G = [&](double s) { return std::atan(std::exp(-0.5 * s) / g.winding_b) * 2 * g.winding_n; };
+    const double PI = 3.14159265358979323846;
+    for (int i = 0; i < n; i++) {
+        const double mid = s0 + (i + 0.5) * WT_H, half = 0.5 * WT_H;
+        double fj[WT_COEFFS], ch[WT_COEFFS];
+        for (int j = 0; j < WT_COEFFS; j++) fj[j] = G(mid + half * std::cos(PI * (j + 0.5) / WT_COEFFS));
+        for (int k = 0; k < WT_COEFFS; k++) {                         // Chebyshev coefficients of the interpolant
+            double a = 0;
+            for (int j = 0; j < WT_COEFFS; j++) a += fj[j] * std::cos(PI * k * (j + 0.5) / WT_COEFFS);
+            ch[k] = a * (k == 0 ? 1.0 : 2.0) / WT_COEFFS;
+        }
+        // Chebyshev -> monomial basis: T_0 = 1, T_1 = x, T_{k+1} = 2 x T_k - T_{k-1}
+        double mono[WT_COEFFS] = {0}, Tkm1[WT_COEFFS] = {1}, Tk[WT_COEFFS] = {0, 1};
+        for (int q = 0; q < WT_COEFFS; q++) mono[q] += ch[0] * Tkm1[q] + ch[1] * Tk[q];
+        for (int k = 2; k < WT_COEFFS; k++) {
+            double Tn[WT_COEFFS] = {0};
+            for (int q = 0; q < WT_COEFFS; q++) {
+                if (q > 0) Tn[q] += 2.0 * Tk[q - 1];
+                Tn[q] -= Tkm1[q];
+            }
+            for (int q = 0; q < WT_COEFFS; q++) { mono[q] += ch[k] * Tn[q]; Tkm1[q] = Tk[q]; Tk[q] = Tn[q]; }
+        }
+        for (int q = 0; q < WT_COEFFS; q++) coeffs[base + size_t(i) * WT_COEFFS + q] = mono[q];
+    }
+    d.wt_s0 = s0; d.wt_n = n;
+    // certification on float radii across the whole range (dense near both ends of every interval)
+    double worst = 0;
+    for (int i = 0; i < n && worst <= WT_CERT_REL; i++)
+        for (int t = 0; t <= 16; t++) {
+            const double s = s0 + (i + t / 16.0) * WT_H;
+            const double r = 1.0 / s - 0.05;
+            if (r < 0 || r > r_max) continue;
+            const float radius = float(r);
+            const double want = winding_direct(g, radius), got = gk_winding_from_table(d, coeffs.data(), radius);
+            const double rel = std::fabs(got - want) / std::fmax(std::fabs(want), 1e-300);
+            if (!(rel <= worst)) worst = rel;
+        }
+    if (!(worst <= WT_CERT_REL)) { coeffs.resize(base); d.wt_n = 0; }
+}
+
 int gk_build_scene(const GamerFrame *f, const GamerGalaxy *gal, const GamerComponent *comp, DScene *out, char *err,
-                   size_t errlen) {
+                   size_t errlen, std::vector<double> *wtab_host) {
     auto fail = [&](const char *m) { if (err && errlen) std::snprintf(err, errlen, "%s", m); return GAMER_E_ARG; };
     if (!f || !out) return fail("null frame");
     if (f->width <= 0 || f->height <= 0 || f->full_size <= 0) return fail("frame size must be positive");
@@ -217,6 +299,8 @@ int gk_build_scene(const GamerFrame *f, const GamerGalaxy *gal, const GamerCompo
             q.rwq = float(std::pow(2.5, w));
         }
         d.comp_count = nc - d.comp_begin;
+        d.wt_n = 0;
+        if (wtab_host && d.any_arm) gk_build_winding_table(g, d, *wtab_host);
         // twirl sharing: every class but bulge and stars evaluates its noise at twirl(p, winding) with
         // winding = getWinding(r) * cp.winding (0 without arm or winding): components with the same factor get the same
         // point, so the kernel keeps the last twirled point of a sample and the group it belongs to

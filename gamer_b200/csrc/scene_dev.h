@@ -14,6 +14,12 @@
 #define DEV_MAX_GALAXIES   8
 #define DEV_MAX_COMPONENTS 64
 #define DEV_RIDGED_OCTAVES 9
+// getWinding as a table (scene_build.cpp, winding_table): per galaxy up to WT_MAX_INTERVALS intervals of width WT_H in
+// s = 1 / (radius + 0.05), a degree-9 polynomial (WT_COEFFS doubles, monomials in x in [-1, 1]) on each
+#define WT_MAX_INTERVALS 96
+#define WT_COEFFS 10
+#define WT_H 0.25
+#define WT_DOUBLES_PER_GALAXY (WT_MAX_INTERVALS * WT_COEFFS)
 
 // flags
 #define DC_HAS_ARM      1    // cp.arm != 0                (galaxycomponent.cpp:69)
@@ -80,6 +86,9 @@ struct DGalaxy {
     int32_t any_tshare;               // some components share a twirl angle (DComp::tgroup >= 0)
     double  winding_b, winding_n;     // getWinding is evaluated in double (its result feeds the twirl angle)
     double  inv_winding_b_d;          // 1 / windingB (double)
+    double  wt_s0;                    // winding table: s of the first interval's left end
+    int32_t wt_n;                     // intervals (0: no table for this galaxy, getWinding is evaluated directly)
+    int32_t wt_off;                   // offset of this galaxy's coefficients in DScene::wtab (doubles)
     int32_t orient_y;                 // orientation and twirl axis are exactly (0,1,0) and rotmat is the identity:
                                       // dot(p, orient) = p.y, P = (p.x, 0, p.z), twirl_y (qtf.cuh) — every shipped galaxy
     int32_t _padg;
@@ -101,6 +110,7 @@ struct DScene {
     float   len_lo_thr;      // exact: ... the lower clamp iff |p-cam| <= len_lo_thr (tested second)
     float   alive_margin;    // bound on |(-dot(p - origin, dir)) - sum of steps| over a whole march (+inf: always test exactly)
     float   d_hi, d_lo;      // |p - cam| above d_hi: the step is certainly 0.01; below d_lo: certainly minRayStep (sqrt of est2_*)
+    const double *wtab;      // device memory: the winding tables of this frame's galaxies (api.cu uploads them), or null
     DGalaxy gal[DEV_MAX_GALAXIES];
     DComp   comp[DEV_MAX_COMPONENTS];
 };
