@@ -27,25 +27,24 @@ struct NoiseCtx {
 // word k of thread t at [k][t] (conflict free). volatile: every access is a real load or store.
 // Words: 0-2 p, 3-5 dir, 6-8 origin, 9-11 camera relative to the galaxy, 12 length, 13 loop bound (-inf: no ray),
 // 14 step, 15 weight, 16 distance marched (+inf: no ray), 17 / 18 the fast-sample windows (marched < [17]: the step is
-// certainly 0.01 and the ray alive; marched > [18]: certainly minRayStep), 19 / 20 the loop bound for those two steps,
-// 21 twirl group of the point in 22-24 (-1: none yet).
+// certainly 0.01 and the ray alive; marched > [18]: certainly minRayStep), 19 whether the winding in 26-28 came from the
+// table (1) or from the direct evaluation (0), 20 twirl group of the point in 21-23 (-1: none yet).
 #define REC_HI_LIM 17
 #define REC_LO_FROM 18
-#define REC_THR_HI 19
-#define REC_THR_LO 20
-#define REC_TG 21
+#define REC_WTAB 19
+#define REC_TG 20
 // values of ONE in-slab sample shared by every component of the galaxy. They live here and not in registers because
 // they are needed on both sides of the noise calls: what ptxas cannot keep in a register across a call it keeps in
 // LOCAL memory for its whole life, and with 768 threads a 96-byte stack is 72 KB per SM against 28 KB of L1 (ncu: 61 %
 // local hit rate, long-scoreboard stalls on every reload). A shared-memory load costs one issue slot and ~25 cycles.
-#define REC_DOTT 25      // height above the plane along the axis (exact)
-#define REC_PLEN 26      // |P| fast float
-#define REC_W 27         // getWinding(radius) narrowed
-#define REC_WD 28        // ... in double (it feeds the twirl angle): words 28, 29
-#define REC_THETA 30     // atan2(q.x, q.z), q = rotmat * P
-#define REC_IVAL 31      // val * weight of the component being evaluated (live across its noise call)
-#define REC_K 32         // index of the component being evaluated (the loop counter, as float bits)
-#define K1_REC_WORDS 33
+#define REC_DOTT 24      // height above the plane along the axis (exact)
+#define REC_PLEN 25      // |P| fast float
+#define REC_W 26         // getWinding(radius) narrowed
+#define REC_WD 27        // ... in double (it feeds the twirl angle): words 27, 28
+#define REC_THETA 29     // atan2(q.x, q.z), q = rotmat * P
+#define REC_IVAL 30      // val * weight of the component being evaluated (live across its noise call)
+#define REC_K 31         // index of the component being evaluated (the loop counter, as float bits)
+#define K1_REC_WORDS 32
 static_assert(GN_DYN_SMEM + K1_REC_WORDS * K1_THREADS * 4u <= 232448u, "tables + ray records exceed the 227 KB a CTA can have");
 struct Rec {
     volatile float *base;
@@ -60,16 +59,54 @@ __device__ __forceinline__ void rec_set_d(const Rec rec, int k, double v) {
     rec[k] = __int_as_float(__double2loint(v)); rec[k + 1] = __int_as_float(__double2hiint(v));
 }
 
-// getWinding (galaxycomponent.h:156-165) and the atan2 of getTheta (:150-153), once per sample
-__device__ __forceinline__ void arm_base(const DGalaxy &g, const Rec rec, f3 P) {
-    // radius exactly as getRadius returns it: float |P| (double sqrt) / float axis.x, then the
-    // reference's double expression atan(exp(-0.25/(0.5*r))/windingB)*2*windingN
-    const float radius = fdiv_nc(v_length(P), g.axis_x, frcp_nc(g.axis_x));
+// getWinding (galaxycomponent.h:156-165), the reference's double expression atan(exp(-0.25/(0.5*r))/windingB)*2*windingN,
+// evaluated directly: a serial FP64 chain of two divisions, an exp and an atan. Out of line: taken only when there is no
+// table, or for the one sample in ~10^5 whose twirl angle the table cannot decide (eval_component).
+__device__ __noinline__ void winding_direct(const DGalaxy &g, float radius, float *rec_base) {
+    const Rec rec = {rec_base};
     const double r = __dadd_rn((double)radius, 0.05);
     const double e = dmath::exp_nc(dmath::div_nc(-0.25, __dmul_rn(0.5, r)));
     const double Wd = __dmul_rn(__dmul_rn(dmath::atan_nc(dmath::div_nc(e, g.winding_b)), 2.0), g.winding_n);
     rec_set_d(rec, REC_WD, Wd);
     rec[REC_W] = (float)Wd;
+    rec[REC_WTAB] = 0.0f;
+}
+// radius exactly as getRadius returns it: float |P| (double sqrt) / float axis.x
+__device__ __forceinline__ float exact_radius(const DGalaxy &g, f3 P) {
+    return fdiv_nc(v_length(P), g.axis_x, frcp_nc(g.axis_x));
+}
+// getWinding and the atan2 of getTheta (:150-153), once per sample. With a table (scene_build.cpp, winding_table):
+// s = 1 / (radius + 0.05) by a Newton reciprocal, the interval of s, one degree-9 Horner chain on coefficients read
+// through the read-only path — certified on the host to 2^-46 of the reference's own expression.
+__device__ __forceinline__ void arm_base(const DScene &sc, const DGalaxy &g, const Rec rec, f3 P) {
+    const float radius = exact_radius(g, P);
+    bool done = false;
+    if (g.wt_n > 0) {
+        const double r = __dadd_rn((double)radius, 0.05);
+        double y;
+        asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(r));
+        double e = __fma_rn(-r, y, 1.0);
+        e = __fma_rn(e, e, e);
+        y = __fma_rn(y, e, y);
+        y = __fma_rn(__fma_rn(-r, y, 1.0), y, y);                        // s = 1 / r to an ulp
+        const double u = __dmul_rn(__dsub_rn(y, g.wt_s0), 1.0 / WT_H);
+        const int i = __double2int_rz(u);
+        if (u >= 0.0 && i < g.wt_n) {
+            const double x = __fma_rn(2.0, __dsub_rn(u, (double)i), -1.0);
+            const double2 *c = reinterpret_cast<const double2 *>(sc.wtab + g.wt_off + i * WT_COEFFS);
+            const double2 c01 = __ldg(c), c23 = __ldg(c + 1), c45 = __ldg(c + 2), c67 = __ldg(c + 3), c89 = __ldg(c + 4);
+            double v = __fma_rn(c89.y, x, c89.x);
+            v = __fma_rn(v, x, c67.y); v = __fma_rn(v, x, c67.x);
+            v = __fma_rn(v, x, c45.y); v = __fma_rn(v, x, c45.x);
+            v = __fma_rn(v, x, c23.y); v = __fma_rn(v, x, c23.x);
+            v = __fma_rn(v, x, c01.y); v = __fma_rn(v, x, c01.x);
+            rec_set_d(rec, REC_WD, v);
+            rec[REC_W] = (float)v;
+            rec[REC_WTAB] = 1.0f;
+            done = true;
+        }
+    }
+    if (!done) winding_direct(g, radius, const_cast<float *>(rec.base));
     f3 q = g.rot_identity ? P : q_rotate(g.rot, P);
     rec[REC_THETA] = dmath::atan2f_fast(q.x, q.z);
 }
@@ -202,10 +239,25 @@ __device__ __forceinline__ void eval_component(const DScene &sc, const DGalaxy &
         if (rec[REC_W] != rec[REC_W]) {
             const f3 pa = {rec[0], rec[1], rec[2]};
             const f3 orient = {g.orient[0], g.orient[1], g.orient[2]};
-            arm_base(g, rec, ORIENT_Y ? f3{pa.x, 0.0f, pa.z} : v_sub(pa, v_mul(orient, rec[REC_DOTT])));
+            arm_base(sc, g, rec, ORIENT_Y ? f3{pa.x, 0.0f, pa.z} : v_sub(pa, v_mul(orient, rec[REC_DOTT])));
         }
         val *= arm_value(g, c.arm15, rec[REC_W] + rec[REC_THETA] + c.delta);   // winding - (-theta + disp): W + theta + delta - disp
-        if (flags & DC_HAS_WINDING) winding = __dmul_rn(rec_get_d(rec, REC_WD), c.winding_d);
+        if (flags & DC_HAS_WINDING) {
+            winding = __dmul_rn(rec_get_d(rec, REC_WD), c.winding_d);
+            if (rec[REC_WTAB] != 0.0f) {
+                // What the reference consumes is float(winding * 180), the twirl angle. The table is within 2^-46 of the
+                // direct evaluation (certified, scene_build.cpp); if 2^-44 either way rounds to the same float the table
+                // decides, otherwise (one sample in ~10^5) getWinding is evaluated directly for this sample.
+                const double a = __dmul_rn(winding, 180.0), del = __dmul_rn(fabs(a), 0x1p-44);
+                if (__double2float_rn(__dsub_rn(a, del)) != __double2float_rn(__dadd_rn(a, del))) {
+                    const f3 pa = {rec[0], rec[1], rec[2]};
+                    const f3 orient = {g.orient[0], g.orient[1], g.orient[2]};
+                    winding_direct(g, exact_radius(g, ORIENT_Y ? f3{pa.x, 0.0f, pa.z} : v_sub(pa, v_mul(orient, rec[REC_DOTT]))),
+                                   const_cast<float *>(rec.base));
+                    winding = __dmul_rn(rec_get_d(rec, REC_WD), c.winding_d);
+                }
+            }
+        }
     }
     {
         const float ival0 = val * rec[15];
@@ -340,8 +392,6 @@ __device__ __forceinline__ void march(const DScene &sc, const DGalaxy &g, const 
         const float sure_below = length_f - sc.alive_margin;
         rec[REC_HI_LIM] = (active && g.fast_ok) ? fminf(dist0 - sc.d_hi - sc.alive_margin, sure_below) : -INFINITY;
         rec[REC_LO_FROM] = (active && g.fast_ok) ? dist0 - sc.d_lo + sc.alive_margin : INFINITY;
-        rec[REC_THR_HI] = __double2float_ru(__dadd_rn((double)length_f, 0.01));
-        rec[REC_THR_LO] = __double2float_ru(__dadd_rn((double)length_f, sc.min_ray_step));
     }
     if (COUNT && active) cn.rays++;
     const bool fast_ok = g.fast_ok != 0;
@@ -367,7 +417,8 @@ __device__ __forceinline__ void march(const DScene &sc, const DGalaxy &g, const 
             // rounding involved), so the loop test dot(p - origin, ll) < thr is evaluated as -dot(p - origin, dir) < thr.
             const f3 orient = {g.orient[0], g.orient[1], g.orient[2]};
             // the two clamped step states (rasterizer.cpp:449): step = 0.01 and step = minRayStep
-            const float thr_hi = rec[REC_THR_HI], thr_lo = rec[REC_THR_LO];
+            const float thr_hi = __double2float_ru(__dadd_rn((double)length_f, 0.01));
+            const float thr_lo = __double2float_ru(__dadd_rn((double)length_f, sc.min_ray_step));
             const float hi_lim = rec[REC_HI_LIM], lo_from = rec[REC_LO_FROM];
             const float s_hi = __double2float_rn(0.01), s_lo = __double2float_rn(sc.min_ray_step);
             const float w_hi = (float)(0.01 * 200.0), w_lo = (float)(sc.min_ray_step * 200.0);
