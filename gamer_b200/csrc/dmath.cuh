@@ -20,6 +20,9 @@
 #define DM_FMA(a, b, c) __fma_rn((a), (b), (c))
 #define DM_MUL(a, b) __dmul_rn((a), (b))
 #define DM_ADD(a, b) __dadd_rn((a), (b))
+#define DMF_MUL(a, b) __fmul_rn((a), (b))
+#define DMF_ADD(a, b) __fadd_rn((a), (b))
+#define DMF_DIV(a, b) __fdiv_rn((a), (b))
 #elif defined(__CUDACC__)
 #define DM_FN __host__ __device__ inline
 #define DM_FMA(a, b, c) fma((a), (b), (c))
@@ -30,6 +33,11 @@
 #define DM_FMA(a, b, c) fma((a), (b), (c))
 #define DM_MUL(a, b) ((a) * (b))
 #define DM_ADD(a, b) ((a) + (b))
+#endif
+#if !defined(__CUDA_ARCH__)   // host: the translation units are built with -ffp-contract=off
+#define DMF_MUL(a, b) ((a) * (b))
+#define DMF_ADD(a, b) ((a) + (b))
+#define DMF_DIV(a, b) ((a) / (b))
 #endif
 
 namespace dmath {
@@ -137,6 +145,58 @@ DM_FN double atan_nc(double x) {
     const double corr = DM_MUL(t, DM_ADD(s1, s2));
     const double r = DM_ADD(hi, -DM_ADD(DM_ADD(corr, -lo), -t));        // hi - ((t (s1+s2) - lo) - t); hi = lo = 0 below 7/16
     return x < 0.0 ? -r : r;
+}
+
+// atanf(x) and atan2f(y, x) exactly as glibc < 2.41 computes them (sysdeps/ieee754/flt-32/s_atanf.c, e_atan2f.c: the
+// fdlibm float versions, every operation a separately rounded float; constants as the DECIMAL literals of the source,
+// which are what the compiler sees — the hex in its comments is one ulp off for aT[0]). Not correctly rounded: 16 % of
+// arguments give the float next to the rounded double atan2. The reference's getTheta (galaxycomponent.h:150-153) calls
+// atan2 on two floats, which in C++ is this float overload; with a NEGATIVE arm exponent (arm_value_neg, kernels.cu) a
+// sample next to the pole of pow(1 - v/pi, e) turns one ulp of theta into a percent of the pixel, so the libm is part
+// of the result there. Finite arguments only (the callers pass components of a finite point).
+// tests/test_cpu.py compares both with the host's libm.
+DM_FN float atanf_glibc(float x) {
+    const float aT0 = 3.3333334327e-01f, aT1 = -2.0000000298e-01f, aT2 = 1.4285714924e-01f, aT3 = -1.1111110449e-01f,
+                aT4 = 9.0908870101e-02f, aT5 = -7.6918758452e-02f, aT6 = 6.6610731184e-02f, aT7 = -5.8335702866e-02f,
+                aT8 = 4.9768779427e-02f, aT9 = -3.6531571299e-02f, aT10 = 1.6285819933e-02f;
+    const bool neg = x < 0.0f;
+    const float ax = fabsf(x);
+    float hi = 0.0f, lo = 0.0f, t = x;
+    bool small = false;
+    if (ax >= 33554432.0f) return neg ? -1.5707963267948966f : 1.5707963267948966f;        // |x| >= 2^25: hi[3] + lo[3]
+    if (ax < 0.4375f) { if (ax < 0x1p-29f) return x; small = true; }
+    else if (ax < 0.6875f) { t = DMF_DIV(DMF_ADD(DMF_MUL(2.0f, ax), -1.0f), DMF_ADD(2.0f, ax)); hi = 4.6364760399e-01f; lo = 5.0121582440e-09f; }
+    else if (ax < 1.1875f) { t = DMF_DIV(DMF_ADD(ax, -1.0f), DMF_ADD(ax, 1.0f)); hi = 7.8539812565e-01f; lo = 3.7748947079e-08f; }
+    else if (ax < 2.4375f) { t = DMF_DIV(DMF_ADD(ax, -1.5f), DMF_ADD(1.0f, DMF_MUL(1.5f, ax))); hi = 9.8279368877e-01f; lo = 3.4473217170e-08f; }
+    else { t = DMF_DIV(-1.0f, ax); hi = 1.5707962513e+00f; lo = 7.5497894159e-08f; }
+    const float z = DMF_MUL(t, t), w = DMF_MUL(z, z);
+    float s1 = DMF_ADD(aT8, DMF_MUL(w, aT10));
+    s1 = DMF_ADD(aT6, DMF_MUL(w, s1)); s1 = DMF_ADD(aT4, DMF_MUL(w, s1));
+    s1 = DMF_ADD(aT2, DMF_MUL(w, s1)); s1 = DMF_ADD(aT0, DMF_MUL(w, s1));
+    s1 = DMF_MUL(z, s1);
+    float s2 = DMF_ADD(aT7, DMF_MUL(w, aT9));
+    s2 = DMF_ADD(aT5, DMF_MUL(w, s2)); s2 = DMF_ADD(aT3, DMF_MUL(w, s2)); s2 = DMF_ADD(aT1, DMF_MUL(w, s2));
+    s2 = DMF_MUL(w, s2);
+    const float ts = DMF_MUL(t, DMF_ADD(s1, s2));
+    if (small) return DMF_ADD(t, -ts);
+    const float r = DMF_ADD(hi, -DMF_ADD(DMF_ADD(ts, -lo), -t));
+    return neg ? -r : r;
+}
+DM_FN float atan2f_glibc(float y, float x) {
+    const float pi_o_2 = 1.5707963705e+00f, pi = 3.1415927410e+00f, pi_lo = -8.7422776573e-08f;
+    if (x == 1.0f) return atanf_glibc(y);
+    const bool yneg = signbit(y), xneg = signbit(x);
+    if (y == 0.0f) return xneg ? (yneg ? -pi : pi) : y;                  // pi + tiny rounds to pi
+    if (x == 0.0f) return yneg ? -pi_o_2 : pi_o_2;
+    uint32_t hx, hy;
+    memcpy(&hx, &x, 4); memcpy(&hy, &y, 4);
+    const int k = ((int)(hy & 0x7fffffffu) - (int)(hx & 0x7fffffffu)) >> 23;
+    float z;
+    if (k > 60) z = DMF_ADD(pi_o_2, DMF_MUL(0.5f, pi_lo));
+    else if (xneg && k < -60) z = 0.0f;
+    else z = atanf_glibc(fabsf(DMF_DIV(y, x)));
+    if (!xneg) return yneg ? -z : z;
+    return yneg ? DMF_ADD(DMF_ADD(z, -pi_lo), -pi) : DMF_ADD(pi, -DMF_ADD(z, -pi_lo));
 }
 
 // sin and cos of a (|a| < 1e5): a = k pi/2 + r by a three-term Cody-Waite reduction, fdlibm's k_sin / k_cos kernels

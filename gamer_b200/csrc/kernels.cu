@@ -125,18 +125,37 @@ __device__ __forceinline__ float find_difference(float d) {
 // negative (wrapped phase difference beyond 3.14159265) gives NaN and is dropped by the reference's fmax; with every arm
 // out of range, or a single one (no fmax then), the NaN reaches `val` and fails the `val * weight > 0.0005` test.
 // e > 0: the maximum is pow(1 - min_j v_j / pi, e), and a base clamped to 0 gives 0, which also contributes nothing.
-// e < 0 (no shipped galaxy; out of line): the maximum is at the LARGEST in-range v_j; none in range -> 0.
-__device__ __noinline__ float arm_value_neg(const DGalaxy &g, float arm15, float base) {
-    float best = -1.0f;
+// e < 0 (no shipped galaxy; out of line): the maximum is at the LARGEST in-range v_j; none in range -> 0. Near
+// v = pi the base goes to zero and the negative exponent amplifies any error of the phase, which the reference forms in
+// double (getWinding, theta + delta, findDifference: galaxycomponent.h:100-153) — except atan2 itself, which on two
+// floats is the libm's FLOAT atan2f. This path does the same: the winding in double from the record, glibc's atan2f
+// restated bit for bit (dmath::atan2f_glibc), the differences in double with M_PI = 3.14159265; only the final pow of
+// the (well-conditioned) base is float.
+__device__ __noinline__ float arm_value_neg(const DGalaxy &g, float arm15, double delta_d, float *rec_base, bool orient_y) {
+    const Rec rec = {rec_base};
+    const f3 pa = {rec[0], rec[1], rec[2]};
+    const f3 orient = {g.orient[0], g.orient[1], g.orient[2]};
+    const f3 P = orient_y ? f3{pa.x, 0.0f, pa.z} : v_sub(pa, v_mul(orient, rec[REC_DOTT]));
+    // rotmat * P exactly as QQuaternion rotates a vector (two float quaternion products): even the identity quaternion
+    // perturbs z by an ulp there ((z + y) - y), and a sample within 1e-6 of the pole turns that into a percent
+    const fq rq = {g.rot[0], g.rot[1], g.rot[2], g.rot[3]};
+    const fq qv = q_mul_qt(q_mul_qt(rq, fq{0.0f, P.x, P.y, P.z}), fq{rq.w, -rq.x, -rq.y, -rq.z});
+    const double base = __dadd_rn(__dadd_rn(rec_get_d(rec, REC_WD), (double)dmath::atan2f_glibc(qv.x, qv.z)), delta_d);
+    const double PI_REF = 3.14159265, TP = 2 * 3.14159265, FP = 2 * 3.14159265 * 2;
+    double best = -1.0;                 // the smallest non-negative base 1 - v / pi over the arms
     for (int j = 0; j < g.no_arms; j++) {
-        const float vj = find_difference(base - g.arm[j]);
-        if (1.0f - vj * (1.0f / 3.14159265f) >= 0.0f) best = fmaxf(best, vj);
+        const double d = __dsub_rn(base, g.arm_d[j]);
+        double v = fmin(fabs(d), fabs(d - TP));
+        v = fmin(v, fabs(d + TP));
+        v = fmin(v, fabs(d - FP));
+        v = fmin(v, fabs(d + FP));
+        const double bj = 1.0 - dmath::div_nc(v, PI_REF);
+        if (bj >= 0.0 && (best < 0.0 || bj < best)) best = bj;
     }
-    if (best < 0.0f) return 0.0f;
-    return ex2a(arm15 * lg2a(1.0f - best * (1.0f / 3.14159265f)));
+    if (best < 0.0) return 0.0f;
+    return ex2a(arm15 * lg2a((float)best));
 }
 __device__ __forceinline__ float arm_value(const DGalaxy &g, float arm15, float base) {
-    if (!(arm15 > 0.0f)) return arm_value_neg(g, arm15, base);
     float v = find_difference(base - g.arm[0]);
     if (g.no_arms > 1) v = fminf(v, find_difference(base - g.arm[1]));
     if (g.no_arms > 2) v = fminf(v, find_difference(base - g.arm[2]));
@@ -241,7 +260,9 @@ __device__ __forceinline__ void eval_component(const DScene &sc, const DGalaxy &
             const f3 orient = {g.orient[0], g.orient[1], g.orient[2]};
             arm_base(sc, g, rec, ORIENT_Y ? f3{pa.x, 0.0f, pa.z} : v_sub(pa, v_mul(orient, rec[REC_DOTT])));
         }
-        val *= arm_value(g, c.arm15, rec[REC_W] + rec[REC_THETA] + c.delta);   // winding - (-theta + disp): W + theta + delta - disp
+        // winding - (-theta + disp): W + theta + delta - disp
+        if (c.arm15 > 0.0f) val *= arm_value(g, c.arm15, rec[REC_W] + rec[REC_THETA] + c.delta);
+        else val *= arm_value_neg(g, c.arm15, c.delta_d, const_cast<float *>(rec.base), ORIENT_Y);
         if (flags & DC_HAS_WINDING) {
             winding = __dmul_rn(rec_get_d(rec, REC_WD), c.winding_d);
             if (rec[REC_WTAB] != 0.0f) {

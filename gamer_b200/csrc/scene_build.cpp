@@ -200,7 +200,7 @@ int gk_build_scene(const GamerFrame *f, const GamerGalaxy *gal, const GamerCompo
             d.inv_axis2[i] = float(1.0 / (g.axis[i] * g.axis[i]));   // util.h:68-70: float product, double divide
         }
         normalize3(g.orient, d.axis_n);
-        for (int i = 0; i < 4; i++) { d.rot[i] = g.rotmat[i]; d.arm[i] = float(g.arm[i]); }
+        for (int i = 0; i < 4; i++) { d.rot[i] = g.rotmat[i]; d.arm[i] = float(g.arm[i]); d.arm_d[i] = g.arm[i]; }
         d.rot_identity = (g.rotmat[0] == 1.f && g.rotmat[1] == 0.f && g.rotmat[2] == 0.f && g.rotmat[3] == 0.f);
         d.axis_x = g.axis[0];
         d.orient_y = d.rot_identity && g.orient[0] == 0.f && g.orient[1] == 1.f && g.orient[2] == 0.f &&
@@ -244,6 +244,7 @@ int gk_build_scene(const GamerFrame *f, const GamerGalaxy *gal, const GamerCompo
             q.inv_z0 = float(1.0 / std::fabs(c.z0));
             q.inv_inner = float(1.0 / inner);
             q.delta = float(c.delta);
+            q.delta_d = c.delta;
             q.winding = float(c.winding);
             q.winding_d = c.winding;
             q.noise_offset = float(c.noise_offset);

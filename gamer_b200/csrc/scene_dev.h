@@ -61,6 +61,7 @@ struct DComp {
     float   strength4;       // 4 * strength (the 4 of sech^2)
     float   inner_k;         // 1 / (axis.x * inner): smoothstep argument = |P| * inner_k
     float   bk;              // bulge: strength * iscale * float(rayStep), the factor of `weight` in its emission
+    double  delta_d;         // cp.delta as the double the reference adds in getTheta (negative arm exponents only)
 };
 
 struct DGalaxy {
@@ -86,6 +87,7 @@ struct DGalaxy {
     int32_t any_tshare;               // some components share a twirl angle (DComp::tgroup >= 0)
     double  winding_b, winding_n;     // getWinding is evaluated in double (its result feeds the twirl angle)
     double  inv_winding_b_d;          // 1 / windingB (double)
+    double  arm_d[4];                 // arm1..arm4 as the reference's doubles (negative arm exponents only)
     double  wt_s0;                    // winding table: s of the first interval's left end
     int32_t wt_n;                     // intervals (0: no table for this galaxy, getWinding is evaluated directly)
     int32_t wt_off;                   // offset of this galaxy's coefficients in DScene::wtab (doubles)

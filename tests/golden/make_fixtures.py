@@ -132,9 +132,28 @@ def star_layers():
     np.savez_compressed(os.path.join(HERE, "ref_star_layers.npz"), **out)
 
 
+def negarm_frames():
+    """tests/golden/ref_negarm_frames.npz: the negative-arm synthetic galaxies rendered by the reference's own code
+    (a file of its own so that ref_path_frames.npz need not be rewritten)."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import ref_cases
+    import ref_path_lib
+    frames = {}
+    for name, case in ref_cases.negarm_cases().items():
+        rp, gis, preview = case
+        for kind in ("src", "o2"):
+            with ref_path_lib.RefRasterizer(rp, gis, kind) as r:
+                frames[name + "|" + kind] = r.render(preview)
+        print(name, float(frames[name + "|src"].max()), int(np.isnan(frames[name + "|src"]).sum()))
+    np.savez_compressed(os.path.join(HERE, "ref_negarm_frames.npz"), **frames)
+
+
 if __name__ == "__main__":
-    if sys.argv[1:] == ["stars"]:
+    if sys.argv[1:] == ["negarm"]:
+        negarm_frames()
+    elif sys.argv[1:] == ["stars"]:
         star_layers()
     else:
         main()
         star_layers()
+        negarm_frames()

@@ -58,6 +58,16 @@ def cases():
     return out
 
 
+def negarm_cases():
+    """Negative arm exponents (tests/golden/ref_negarm_frames.npz): three arms (fmax drops the NaN arm) and one (the NaN
+    reaches the contribution test), each from two views."""
+    out = {}
+    for kind in ("negarm3", "negarm1"):
+        for v in ("oblique", "faceon"):
+            out["%s/%s" % (kind, v)] = _one(kind, v, galaxy=_synthetic(kind))
+    return out
+
+
 # AssembleImage settings checked on top of some of the frames: (exposure, gamma, saturation)
 TONEMAPS = [(1.0, 1.0, 1.0), (0.5, 0.8, 1.3), (2.5, 1.6, 0.4), (0.1, 0.45, 2.0)]
 TONEMAP_CASES = ["Spiral/cli", "three/outside", "allclasses/edge"]

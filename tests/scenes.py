@@ -63,6 +63,18 @@ def synthetic_galaxy(kind="allclasses") -> Galaxy:
     if kind == "ellipsoid":
         p.axis = [1.0, 0.6, 0.8]
     C = ComponentParams
+    if kind in ("negarm3", "negarm1"):
+        # a NEGATIVE arm exponent with a strong winding and a large delta: the wrapped phase difference passes
+        # 3.14159265, where getArm's base goes negative and pow gives NaN (galaxycomponent.h:140-146): with three arms
+        # fmax drops the NaN arm, with one arm the NaN fails the `val * weight > 0.0005` test
+        p.windingB, p.windingN, p.noArms = 0.45, 5.0, (3.0 if kind == "negarm3" else 1.0)
+        g.componentParams = [
+            C("bulge", 30.0, "Yellow", 1.0, 0.02, 6.0, 1.0, 0.0, 0.1, 1.0, 0.0, 1.0, 1.0, 0.1, "b"),
+            C("disk", 40.0, "Blue", -0.05, 0.03, 0.45, 1.0, 2.5, 0.15, 8.0, 0.0, 0.7, 1.0, 0.1, "d neg arm"),
+            C("dust2", 60.0, "Red", -0.02, 0.025, 0.4, 1.0, 1.2, 0.1, 5.0, 1.05, 1.5, 1.0, 0.2, "d2 neg arm"),
+            C("stars", 4.0, "White", 0.3, 0.04, 0.35, 1.0, 0.0, 0.3, 40.0, 0.0, 9.0, 1.0, 0.0, "s"),
+        ]
+        return g
     if kind == "sharing":
         # twirl sharing (DComp::tgroup): three components with winding 0.12 and two without arms (winding factor 0),
         # interleaved with a fourth factor so that the kept point is replaced between members of a group

@@ -230,7 +230,9 @@ def test_oracle_fbm_and_ridged_equal_reference_class_golden(oracle):
 def test_dmath_host_build_matches_libm(tmp_path):
     """csrc/dmath.cuh (the call-free FP64 exp / atan / sincos and the fast atan2f of K1) compiled for the host and
     compared with libm over the argument ranges the kernel uses: <= 1 ulp in double, identical once narrowed to float
-    (which is all the reference consumes: the winding angle and the twirl quaternion)."""
+    (which is all the reference consumes: the winding angle and the twirl quaternion). atan2f_glibc / atanf_glibc
+    (the theta of a negative arm exponent) must equal glibc's own float functions bit for bit (glibc < 2.41: the
+    fdlibm versions; skipped with a newer libm, whose atan2f is a different, correctly rounded algorithm)."""
     import subprocess
     src = tmp_path / "dm.cpp"
     hdr = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "gamer_b200", "csrc", "dmath.cuh")
@@ -242,7 +244,7 @@ def test_dmath_host_build_matches_libm(tmp_path):
 static double ulps(double a, double b) { if (a == b) return 0; double u = std::fabs(std::nextafter(b, INFINITY) - b); return std::fabs(a - b) / u; }
 int main() {
     srand(1);
-    double me = 0, ma = 0, ms = 0; float mf = 0; long mism = 0;
+    double me = 0, ma = 0, ms = 0; float mf = 0; long mism = 0, mg = 0;
     for (long i = 0; i < 1000000; i++) {
         double u = rand() / (double)RAND_MAX;
         double x = -12.0 * u, e = dmath::exp_nc(x), er = exp(x);
@@ -254,16 +256,24 @@ int main() {
         mism += ((float)s != (float)sin(an)) + ((float)c != (float)cos(an));
         float fy = (float)(2 * (rand() / (double)RAND_MAX) - 1), fx = (float)(2 * (rand() / (double)RAND_MAX) - 1);
         mf = fmaxf(mf, fabsf(dmath::atan2f_fast(fy, fx) - (float)atan2((double)fy, (double)fx)));
+        if (i & 2) fy *= 1e-3f;
+        if (i & 4) fx *= 1e-4f;
+        float ag = dmath::atan2f_glibc(fy, fx), al = atan2f(fy, fx), tg = dmath::atanf_glibc(6.0f * fy), tl = atanf(6.0f * fy);
+        mg += (memcmp(&ag, &al, 4) != 0) + (memcmp(&tg, &tl, 4) != 0);    // the libm's float atan2f / atanf, bit for bit
     }
-    printf("%%.4f %%.4f %%.3g %%.3g %%ld\n", me, ma, ms, (double)mf, mism);
+    printf("%%.4f %%.4f %%.3g %%.3g %%ld %%ld\n", me, ma, ms, (double)mf, mism, mg);
 }
 ''' % hdr)
     exe = tmp_path / "dm"
     subprocess.run(["g++", "-O2", "-ffp-contract=off", "-o", str(exe), str(src)], check=True)
-    me, ma, ms, mf, mism = subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.split()
+    me, ma, ms, mf, mism, mg = subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.split()
     assert float(me) <= 1.0 and float(ma) <= 1.0, (me, ma)
     assert float(ms) <= 3e-16 and float(mf) <= 5e-7, (ms, mf)
     assert int(mism) == 0
+    import platform
+    lib, ver = platform.libc_ver()
+    if lib == "glibc" and tuple(int(v) for v in ver.split(".")[:2]) < (2, 41):
+        assert int(mg) == 0
 
 
 def test_scene_builder_twirl_groups_and_exact_thresholds(tmp_path):

@@ -170,3 +170,42 @@ def test_gpu_star_layer_equals_reference_rendergaussian(gpu_ctx):
         gpu_ctx.upload(full.tile(3, 5, size - 7, h))
         part = gpu_ctx.render_stars(lst, want_layer=True)
         assert np.all(np.abs(part.astype(np.float64) - layer[5:5 + h, 3:size - 4]) <= ulp[5:5 + h, 3:size - 4]), name
+
+
+# ---- negative arm exponents: pow of a negative base is NaN in the reference, and fmax / the contribution test quench it ----
+NEGARM = ref_cases.negarm_cases()
+
+
+@pytest.fixture(scope="module")
+def negarm_golden():
+    return np.load(os.path.join(ROOT, "tests", "golden", "ref_negarm_frames.npz"))
+
+
+@pytest.mark.parametrize("kind", sorted(KINDS))
+@pytest.mark.parametrize("name", sorted(NEGARM))
+def test_oracle_equals_reference_frame_negative_arm(negarm_golden, oracle, name, kind):
+    """getArm with a negative exponent and a wrapped phase difference beyond 3.14159265 (galaxycomponent.h:120-146):
+    frames of the reference's own code, three arms (fmax drops the NaN arm) and one arm (the NaN fails the
+    `val * weight > 0.0005` test). The oracle reproduces them bit for bit."""
+    sc = ref_cases.scene_of(NEGARM[name], no_radial_gate=KINDS[kind])
+    rgb, _ = oracle.render(sc)
+    ref = negarm_golden[name + "|" + kind]
+    assert ref.max() > 1.0 and np.isfinite(ref).all()
+    assert np.array_equal(rgb.view(np.uint32), ref.view(np.uint32)), float(np.abs(rgb - ref).max())
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", sorted(NEGARM))
+def test_gpu_equals_reference_frame_negative_arm(negarm_golden, gpu_ctx, oracle, name):
+    """The CUDA path on the same scenes: finite, within the 1e-3 bar of the reference's frame, sample counts equal the
+    oracle's (pow(0, negative) = +inf used to reach the pixel)."""
+    sc = ref_cases.scene_of(NEGARM[name])
+    gpu_ctx.upload(sc)
+    cnt = gpu_ctx.render_counted()
+    img = gpu_ctx.render()
+    ref = negarm_golden[name + "|src"]
+    _, rcnt = oracle.render(sc)
+    assert np.isfinite(img).all()
+    assert cnt["samples"] == rcnt["samples"] and cnt["gates"] == rcnt["gates"]
+    err = np.abs(img.astype(np.float64) - ref) / (1e-3 * np.abs(ref.astype(np.float64)) + 1e-5)
+    assert err.max() <= 1.0, (name, float(err.max()))
