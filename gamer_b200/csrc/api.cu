@@ -397,9 +397,10 @@ static int tonemap_common(gamer_ctx *ctx, double exposure, double gamma, double 
             stars_dev = d.stars;
         }
         CK(cudaEventRecord(d.ev[2], d.st));
-        CK(gk::launch_k2(d.rgb, stars_dev, d.argb, d.shadow, px, exposure, gamma, saturation, d.sm_count, d.st));
+        int k2_launches = 1;          // 2 when the pixel count leaves a remainder modulo 4 (the scalar kernel takes it)
+        CK(gk::launch_k2(d.rgb, stars_dev, d.argb, d.shadow, px, exposure, gamma, saturation, d.sm_count, d.st, &k2_launches));
         CK(cudaEventRecord(d.ev[3], d.st));
-        ctx->launches += 1;
+        ctx->launches += k2_launches;
     }
     int rc = sync_all(ctx);
     if (rc) return rc;

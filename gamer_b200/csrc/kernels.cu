@@ -2,6 +2,7 @@
 // sm_100a only.  See march.cuh / noise.cuh for the design notes and the reference citations.
 #include <mutex>
 #include "march.cuh"
+#include "tone.cuh"
 #include "kernels.h"
 
 using namespace gmarch;
@@ -680,45 +681,31 @@ k1_march(const __grid_constant__ DScene sc, float *__restrict__ out, unsigned lo
 }
 
 // ---- K2: Buffer2D::PostProcess + ToColorBuffer (buffer2d.cpp:65-85,106-126) -------------------------
-// HBM-bound: 12 B (+12 B stars) read, 8 B written per pixel. pow is evaluated in double like the
-// reference (3 per pixel; the kernel stays memory-bound).
+// HBM-bound: 12 B (+12 B stars) read, 8 B written per pixel. What is written is one BYTE per channel,
+// (int)clamp(10 v), and the reference forms v through float -> double -> float -> double -> float: 13 conversions per
+// pixel on the quarter-rate XU pipe, which was this kernel's limit (ncu r02: XU 76 % busy, HBM at half its rate).
+// tone_fast forms the same v in plain FP32 together with a proven bound on its distance from the reference's float,
+// and decides the byte whenever no integer lies within that bound of 10 v; otherwise (about one pixel in 10^4) the
+// pixel goes through tone_exact, the reference's own chain. The result is the reference's byte in every case.
+
+template <bool GAMMA>
 __device__ __forceinline__ void tone_px(float x, float y, float z, float inv_exposure, double gamma, double saturation,
-                                        uint32_t &argb, uint32_t &shadow) {
+                                        const tone::ToneSat k, uint32_t &argb, uint32_t &shadow) {
     x = __fmul_rn(x, inv_exposure); y = __fmul_rn(y, inv_exposure); z = __fmul_rn(z, inv_exposure);
-    if (gamma != 1.0) { x = (float)pow((double)x, gamma); y = (float)pow((double)y, gamma); z = (float)pow((double)z, gamma); }
-    // center = double(float sum) / 3.0, correctly rounded without the generic division: q = RN(s/3) up to an
-    // ulp, r = s - 3q exactly (FMA), q + r/3 rounded once. s has a 24-bit significand, so s/3 is either exact
-    // or continues in the period-2 pattern 0101.../1010... and is never close to a rounding boundary.
-    const double s3 = (double)__fadd_rn(__fadd_rn(x, y), z);
-    const double inv3 = 1.0 / 3.0;
-    const double q3 = __dmul_rn(s3, inv3);
-    double center = __fma_rn(__fma_rn(-3.0, q3, s3), inv3, q3);
-    float tx = (float)(center - x), ty = (float)(center - y), tz = (float)(center - z);
-    x = (float)__dsub_rn(center, __dmul_rn(saturation, (double)tx));
-    y = (float)__dsub_rn(center, __dmul_rn(saturation, (double)ty));
-    z = (float)__dsub_rn(center, __dmul_rn(saturation, (double)tz));
-    x = __fmul_rn(x, 10.0f); y = __fmul_rn(y, 10.0f); z = __fmul_rn(z, 10.0f);
-    // Util::clamp: std::min(255, v) then std::max(0, v) — NaN becomes 255
-    x = (x < 255.0f) ? x : 255.0f; x = (0.0f < x) ? x : 0.0f;
-    y = (y < 255.0f) ? y : 255.0f; y = (0.0f < y) ? y : 0.0f;
-    z = (z < 255.0f) ? z : 255.0f; z = (0.0f < z) ? z : 0.0f;
-    // (int)v for v in [0, 255]: v + 2^23 rounded DOWN leaves floor(v) in the low significand bits — an FADD on the FMA
-    // pipe instead of a third kind of conversion on the XU pipe, the busiest unit of this kernel (ncu: 76 % while active)
-    uint32_t r = __float_as_uint(__fadd_rd(x, 8388608.0f)) & 0xFFu, g = __float_as_uint(__fadd_rd(y, 8388608.0f)) & 0xFFu,
-             b = __float_as_uint(__fadd_rd(z, 8388608.0f)) & 0xFFu;
-    argb   = 0xFF000000u | (b << 16) | (g << 8) | r;
-    shadow = 0xFF000000u | (r << 16) | (g << 8) | b;
+    if (GAMMA) { x = (float)pow((double)x, gamma); y = (float)pow((double)y, gamma); z = (float)pow((double)z, gamma); }
+    tone::tone_mapped(x, y, z, saturation, k, argb, shadow);
 }
 
+template <bool GAMMA>
 __global__ void __launch_bounds__(256, 4)
 k2_tonemap(const float *__restrict__ rgb, const float *__restrict__ stars, uint32_t *__restrict__ argb,
-           uint32_t *__restrict__ shadow, size_t n, double inv_exposure_d, double gamma, double saturation) {
+           uint32_t *__restrict__ shadow, size_t n, float inv_exposure, double gamma, double saturation,
+           const tone::ToneSat ks) {
     // Persistent grid (4 CTAs per SM, 64 registers per thread), grid-stride, FOUR independent pixels per thread and iteration with all
     // loads issued before the arithmetic: a single pixel per iteration is a chain of dependent load
     // latencies. The three 4-byte loads of a warp cover the same 384 contiguous bytes, so every fetched
     // sector is fully used. Once HBM is fed, the bound is the reference's float<->double traffic:
     // 16 conversions per pixel on the quarter-rate XU pipe.
-    const float inv_exposure = (float)inv_exposure_d;
     const size_t nth = (size_t)gridDim.x * blockDim.x;
     size_t k = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
     for (; k + 3 * nth < n; k += 4 * nth) {
@@ -738,7 +725,7 @@ k2_tonemap(const float *__restrict__ rgb, const float *__restrict__ stars, uint3
 #pragma unroll
         for (int u = 0; u < 4; u++) {
             uint32_t o, h;
-            tone_px(v[u][0], v[u][1], v[u][2], inv_exposure, gamma, saturation, o, h);
+            tone_px<GAMMA>(v[u][0], v[u][1], v[u][2], inv_exposure, gamma, saturation, ks, o, h);
             if (argb)   argb[k + u * nth] = o;
             if (shadow) shadow[k + u * nth] = h;
         }
@@ -747,7 +734,7 @@ k2_tonemap(const float *__restrict__ rgb, const float *__restrict__ stars, uint3
         float x = rgb[3 * k], y = rgb[3 * k + 1], z = rgb[3 * k + 2];
         if (stars) { x = __fadd_rn(x, stars[3 * k]); y = __fadd_rn(y, stars[3 * k + 1]); z = __fadd_rn(z, stars[3 * k + 2]); }
         uint32_t o, h;
-        tone_px(x, y, z, inv_exposure, gamma, saturation, o, h);
+        tone_px<GAMMA>(x, y, z, inv_exposure, gamma, saturation, ks, o, h);
         if (argb)   argb[k] = o;
         if (shadow) shadow[k] = h;
     }
@@ -756,39 +743,84 @@ k2_tonemap(const float *__restrict__ rgb, const float *__restrict__ stars, uint3
 // K2 for 16-byte aligned buffers (the normal case; launch_k2 checks): four CONSECUTIVE pixels per thread — three 16-byte
 // loads (48 B of RGB), one 16-byte store per output image, a quarter of the memory instructions of the scalar kernel —
 // and no grid-stride loop: one group per thread, 1536 resident threads per SM, the block scheduler does the balancing.
-// The last n % 4 pixels are done by the first threads, one each.
-__global__ void __launch_bounds__(256, 6)
-k2_tonemap_v4(const float *__restrict__ rgb, const float *__restrict__ stars, uint32_t *__restrict__ argb,
-              uint32_t *__restrict__ shadow, size_t n, double inv_exposure_d, double gamma, double saturation) {
-    const float inv_exposure = (float)inv_exposure_d;
-    const size_t tid = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
-    const size_t groups = n >> 2;
-    if (tid < groups) {
-        const float4 *r4 = reinterpret_cast<const float4 *>(rgb), *s4 = reinterpret_cast<const float4 *>(stars);
-        float4 a = r4[3 * tid], b = r4[3 * tid + 1], c = r4[3 * tid + 2];
-        if (stars) {
-            const float4 p = s4[3 * tid], q = s4[3 * tid + 1], r = s4[3 * tid + 2];
-            a.x = __fadd_rn(a.x, p.x); a.y = __fadd_rn(a.y, p.y); a.z = __fadd_rn(a.z, p.z); a.w = __fadd_rn(a.w, p.w);
-            b.x = __fadd_rn(b.x, q.x); b.y = __fadd_rn(b.y, q.y); b.z = __fadd_rn(b.z, q.z); b.w = __fadd_rn(b.w, q.w);
-            c.x = __fadd_rn(c.x, r.x); c.y = __fadd_rn(c.y, r.y); c.z = __fadd_rn(c.z, r.z); c.w = __fadd_rn(c.w, r.w);
-        }
-        uint4 o, h;
-        tone_px(a.x, a.y, a.z, inv_exposure, gamma, saturation, o.x, h.x);
-        tone_px(a.w, b.x, b.y, inv_exposure, gamma, saturation, o.y, h.y);
-        tone_px(b.z, b.w, c.x, inv_exposure, gamma, saturation, o.z, h.z);
-        tone_px(c.y, c.z, c.w, inv_exposure, gamma, saturation, o.w, h.w);
-        if (argb)   reinterpret_cast<uint4 *>(argb)[tid] = o;
-        if (shadow) reinterpret_cast<uint4 *>(shadow)[tid] = h;
+// The kernel is bound by instruction issue (ncu r02b: 70 warp instructions per pixel before this arrangement), so what
+// is not arithmetic is kept out of it (and what remains above the copy-only kernel's 14.3 us is not issue either: 70 ->
+// 54 instructions per pixel changed nothing, nor did 64..512 threads per block; a persistent variant fed by
+// cp.async.bulk into per-warp or per-CTA shared-memory rings was 2-6 us SLOWER and is not kept): the four pixels are decided in FP32 first and ONE branch covers the rare group
+// with an undecided pixel; the stars addend is a template parameter (as a run-time test it becomes 3 predicated loads
+// and 12 predicated adds that issue for nothing); indices are 32-bit; the n % 4 remainder pixels go to the scalar kernel.
+#ifndef K2_BLOCK
+#define K2_BLOCK 256
+#endif
+#ifndef K2_MINB
+#define K2_MINB 6
+#endif
+// float(pow(double(x), gamma)) like Buffer2D::PostProcess; out of line: twelve inlined copies per thread spill
+__device__ __noinline__ float pow_gamma(float x, double gamma) { return (float)pow((double)x, gamma); }
+template <bool GAMMA>
+__device__ __forceinline__ void expose_px(float &x, float &y, float &z, float inv_exposure, double gamma) {
+    x = __fmul_rn(x, inv_exposure); y = __fmul_rn(y, inv_exposure); z = __fmul_rn(z, inv_exposure);
+    if (GAMMA) { x = pow_gamma(x, gamma); y = pow_gamma(y, gamma); z = pow_gamma(z, gamma); }
+}
+// four consecutive pixels (48 B) of the frame, plus the star layer, exposed and gamma-mapped. (Loading the warp's 1536
+// bytes with three fully coalesced loads and redistributing them through shared memory was measured: the copy-only
+// kernel takes 14.27 us either way and the full kernel got slower, 16.35 -> 18.4 us.)
+template <bool GAMMA, bool STARS>
+__device__ __forceinline__ void k2_load_group(const float4 *__restrict__ r4, const float4 *__restrict__ s4, uint32_t tid,
+                                              float inv_exposure, double gamma, float4 &a, float4 &b, float4 &c) {
+    a = r4[3 * (size_t)tid]; b = r4[3 * (size_t)tid + 1]; c = r4[3 * (size_t)tid + 2];
+    if (STARS) {
+        const float4 p = s4[3 * (size_t)tid], q = s4[3 * (size_t)tid + 1], r = s4[3 * (size_t)tid + 2];
+        a.x = __fadd_rn(a.x, p.x); a.y = __fadd_rn(a.y, p.y); a.z = __fadd_rn(a.z, p.z); a.w = __fadd_rn(a.w, p.w);
+        b.x = __fadd_rn(b.x, q.x); b.y = __fadd_rn(b.y, q.y); b.z = __fadd_rn(b.z, q.z); b.w = __fadd_rn(b.w, q.w);
+        c.x = __fadd_rn(c.x, r.x); c.y = __fadd_rn(c.y, r.y); c.z = __fadd_rn(c.z, r.z); c.w = __fadd_rn(c.w, r.w);
     }
-    const size_t k = (groups << 2) + tid;
-    if (tid < 4 && k < n) {
-        float x = rgb[3 * k], y = rgb[3 * k + 1], z = rgb[3 * k + 2];
-        if (stars) { x = __fadd_rn(x, stars[3 * k]); y = __fadd_rn(y, stars[3 * k + 1]); z = __fadd_rn(z, stars[3 * k + 2]); }
+    expose_px<GAMMA>(a.x, a.y, a.z, inv_exposure, gamma);
+    expose_px<GAMMA>(a.w, b.x, b.y, inv_exposure, gamma);
+    expose_px<GAMMA>(b.z, b.w, c.x, inv_exposure, gamma);
+    expose_px<GAMMA>(c.y, c.z, c.w, inv_exposure, gamma);
+}
+template <bool GAMMA, bool STARS>
+__device__ __noinline__ void k2_fix_group(const float4 *r4, const float4 *s4, uint4 *argb, uint4 *shadow, uint32_t tid,
+                                          uint32_t undecided, float inv_exposure, double gamma, double saturation) {
+    const float *rgb = reinterpret_cast<const float *>(r4 + 3 * tid), *st = reinterpret_cast<const float *>(s4 + 3 * tid);
+    for (int u = 0; u < 4; u++) {
+        if (!((undecided >> u) & 1u)) continue;
+        float x = rgb[3 * u], y = rgb[3 * u + 1], z = rgb[3 * u + 2];
+        if (STARS) { x = __fadd_rn(x, st[3 * u]); y = __fadd_rn(y, st[3 * u + 1]); z = __fadd_rn(z, st[3 * u + 2]); }
+        expose_px<GAMMA>(x, y, z, inv_exposure, gamma);
         uint32_t o, h;
-        tone_px(x, y, z, inv_exposure, gamma, saturation, o, h);
-        if (argb)   argb[k] = o;
-        if (shadow) shadow[k] = h;
+        tone::tone_mapped_exact(x, y, z, saturation, o, h);
+        if (argb)   reinterpret_cast<uint32_t *>(argb + tid)[u] = o;
+        if (shadow) reinterpret_cast<uint32_t *>(shadow + tid)[u] = h;
     }
+}
+template <bool GAMMA, bool STARS>
+__global__ void __launch_bounds__(K2_BLOCK, K2_MINB)
+k2_tonemap_v4(const float4 *__restrict__ r4, const float4 *__restrict__ s4, uint4 *__restrict__ argb,
+              uint4 *__restrict__ shadow, uint32_t groups, float inv_exposure, double gamma, double saturation,
+              const tone::ToneSat ks) {
+    const uint32_t tid = blockIdx.x * K2_BLOCK + threadIdx.x;
+    if (tid >= groups) return;
+    float4 a, b, c;
+    k2_load_group<GAMMA, STARS>(r4, s4, tid, inv_exposure, gamma, a, b, c);
+    uint4 o, h;
+#ifdef K2_DIAG_COPY      // timing experiment only (results are wrong): the memory pattern without the arithmetic
+    o = make_uint4(__float_as_uint(a.x), __float_as_uint(a.w), __float_as_uint(b.z), __float_as_uint(c.y));
+    h = make_uint4(__float_as_uint(a.y), __float_as_uint(b.x), __float_as_uint(b.w), __float_as_uint(c.z));
+    const bool ok0 = true, ok1 = true, ok2 = true, ok3 = c.w != 12345.0f;
+#else
+    const bool ok0 = tone::tone_mapped_fast(a.x, a.y, a.z, ks, o.x, h.x);
+    const bool ok1 = tone::tone_mapped_fast(a.w, b.x, b.y, ks, o.y, h.y);
+    const bool ok2 = tone::tone_mapped_fast(b.z, b.w, c.x, ks, o.z, h.z);
+    const bool ok3 = tone::tone_mapped_fast(c.y, c.z, c.w, ks, o.w, h.w);
+#endif
+    if (argb)   argb[tid] = o;
+    if (shadow) shadow[tid] = h;
+    // about one group in a thousand has an undecided pixel: its words are written again by the exact chain, out of line,
+    // from pixels loaded again - nothing of the cold path is live in the path every thread takes
+    const uint32_t undecided = (ok0 ? 0u : 1u) | (ok1 ? 0u : 2u) | (ok2 ? 0u : 4u) | (ok3 ? 0u : 8u);
+    if (undecided) k2_fix_group<GAMMA, STARS>(r4, s4, argb, shadow, tid, undecided, inv_exposure, gamma, saturation);
 }
 
 // ---- K4: background star layer. Buffer2D::RenderGaussian (buffer2d.cpp:224-243) for every star --------
@@ -937,18 +969,38 @@ cudaError_t launch_k1(const DScene &sc, float *out_dev, unsigned long long *coun
 }
 
 cudaError_t launch_k2(const float *rgb, const float *stars, uint32_t *argb, uint32_t *shadow, size_t n, double exposure,
-                      double gamma, double saturation, int sm_count, cudaStream_t st) {
+                      double gamma, double saturation, int sm_count, cudaStream_t st, int *n_launches) {
+    if (n_launches) *n_launches = 1;
     size_t want = (n + 255) / 256;
     size_t cap = (size_t)sm_count * 4;          // 4 resident CTAs of 256 threads per SM (64 registers each), grid-stride
     int blocks = (int)(want < cap ? want : cap);
     if (blocks < 1) blocks = 1;
     const uintptr_t al = (uintptr_t)rgb | (uintptr_t)stars | (uintptr_t)argb | (uintptr_t)shadow;
-    if ((al & 15u) == 0 && n >= 4) {
-        const size_t threads = (n >> 2) + 4;         // one group of four pixels per thread; the first threads also take the remainder
-        k2_tonemap_v4<<<(unsigned)((threads + 255) / 256), 256, 0, st>>>(rgb, stars, argb, shadow, n, 1.0 / exposure, gamma, saturation);
+    // the float constants of the launch are formed here, once: in the kernel they would be XU conversions per pixel
+    const float inv_exposure = (float)(1.0 / exposure);
+    const tone::ToneSat ks = tone::tone_sat(saturation);
+    const bool g = gamma != 1.0;
+    if ((al & 15u) == 0 && n >= 4 && (n >> 2) <= 0x7FFFFFFFu / 3u) {
+        const uint32_t groups = (uint32_t)(n >> 2);          // one group of four consecutive pixels per thread
+        const unsigned grid = (groups + K2_BLOCK - 1) / K2_BLOCK;
+        const size_t done = (size_t)groups << 2, rest = n - done;          // the n % 4 remainder: the scalar kernel, one block
+        cudaError_t e;
+#define K2_LAUNCH(G, S) k2_tonemap_v4<G, S><<<grid, K2_BLOCK, 0, st>>>( \
+            reinterpret_cast<const float4 *>(rgb), reinterpret_cast<const float4 *>(stars), reinterpret_cast<uint4 *>(argb), \
+            reinterpret_cast<uint4 *>(shadow), groups, inv_exposure, gamma, saturation, ks)
+        if (g) { if (stars) K2_LAUNCH(true, true); else K2_LAUNCH(true, false); }
+        else   { if (stars) K2_LAUNCH(false, true); else K2_LAUNCH(false, false); }
+#undef K2_LAUNCH
+        e = cudaGetLastError();
+        if (n_launches) *n_launches = rest ? 2 : 1;
+        if (e != cudaSuccess || rest == 0) return e;
+        rgb += 3 * done; if (stars) stars += 3 * done; if (argb) argb += done; if (shadow) shadow += done;
+        if (g) k2_tonemap<true><<<1, 32, 0, st>>>(rgb, stars, argb, shadow, rest, inv_exposure, gamma, saturation, ks);
+        else k2_tonemap<false><<<1, 32, 0, st>>>(rgb, stars, argb, shadow, rest, inv_exposure, gamma, saturation, ks);
         return cudaGetLastError();
     }
-    k2_tonemap<<<blocks, 256, 0, st>>>(rgb, stars, argb, shadow, n, 1.0 / exposure, gamma, saturation);
+    if (g) k2_tonemap<true><<<blocks, 256, 0, st>>>(rgb, stars, argb, shadow, n, inv_exposure, gamma, saturation, ks);
+    else k2_tonemap<false><<<blocks, 256, 0, st>>>(rgb, stars, argb, shadow, n, inv_exposure, gamma, saturation, ks);
     return cudaGetLastError();
 }
 

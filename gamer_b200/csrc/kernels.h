@@ -11,7 +11,7 @@ cudaError_t launch_k1(const DScene &sc, float *out_dev, unsigned long long *coun
                       unsigned int *progress_dev /* [0] tiles done, [1] ticket; both zeroed by the caller */, bool counted,
                       int sm_count, cudaStream_t st, unsigned int *n_tiles);
 cudaError_t launch_k2(const float *rgb, const float *stars, uint32_t *argb, uint32_t *shadow, size_t n, double exposure,
-                      double gamma, double saturation, int sm_count, cudaStream_t st);
+                      double gamma, double saturation, int sm_count, cudaStream_t st, int *n_launches = nullptr);
 cudaError_t launch_k4(const GamerStar *stars, int n, float *layer, const DScene &sc, cudaStream_t st);
 cudaError_t launch_probe_simplex(const float *xyz, int n, double frequency, int32_t *lat, float *val, cudaStream_t st);
 cudaError_t launch_probe_fbm(const float *xyz, int n, int octaves, float pers, float inv_maxamp, double scale, float *out,

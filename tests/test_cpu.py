@@ -494,3 +494,69 @@ int main() {
     out = subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.split()
     assert out[0] == "24" and out[2] == "1", out
     assert int(out[3]) <= 96 * 10 * 8
+
+
+def test_tonemap_fp32_decision_never_disagrees_with_the_exact_chain(tmp_path):
+    """csrc/tone.cuh compiled for the host: K2 decides a byte in FP32 only where its error bound leaves no integer of
+    1..255 within reach of 10 v, and goes through the reference's double chain otherwise. On random pixels, on pixels
+    constructed to land within +-4 ulp of every byte boundary (grey and coloured, nine saturations), and on
+    zeros / subnormals / overflow / infinities / NaN: a decided byte always equals the exact chain's, the combined
+    function always does, and nearly every random pixel is decided."""
+    import subprocess
+    hdr = os.path.join(ROOT, "gamer_b200", "csrc", "tone.cuh")
+    src = tmp_path / "tn.cpp"
+    src.write_text(r'''
+#include "@HDR@"
+#include <cstdio>
+#include <random>
+int main() {
+    std::mt19937_64 rng(7);
+    std::uniform_real_distribution<double> U(0, 1);
+    const double sats[] = {1.0, 1.467, 0.5, 0.0, -1.0, 3.7, 1e-3, 0.9999999, 25.0};
+    long n = 0, decided = 0, bad = 0, undec_adv = 0, nadv = 0;
+    auto check = [&](float x, float y, float z, double S, bool adv) {
+        uint32_t ea, es, fa, fs;
+        { const uint32_t p = tone::tone_exact(x, y, z, S); ea = 0xFF000000u | p; es = 0xFF000000u | ((p & 255u) << 16) | (p & 0xFF00u) | (p >> 16); }
+        const tone::ToneSat k = tone::tone_sat(S);
+        uint32_t r, g, b;
+        const bool ok = tone::tone_decide(x, y, z, k, r, g, b);
+        if (adv) { nadv++; undec_adv += !ok; } else { n++; decided += ok; }
+        if (ok) { tone::pack_px(r, g, b, fa, fs); if (fa != ea || fs != es) { if (bad < 10) printf("BAD %a %a %a S %g: %08x %08x\n", x, y, z, S, fa, ea); bad++; } }
+        uint32_t ma, ms; tone::tone_mapped(x, y, z, S, k, ma, ms);
+        if (ma != ea || ms != es) bad++;
+    };
+    for (long i = 0; i < 2000000; i++) {
+        const double S = sats[i % 9];
+        double sc = (i & 1) ? 30.0 : pow(10.0, -6 + 8 * U(rng));
+        check((float)(sc * U(rng)), (float)(sc * U(rng)), (float)(sc * U(rng)), S, false);
+    }
+    for (long i = 0; i < 2000000; i++) {
+        const double S = sats[i % 9];
+        const int m = 1 + (int)(rng() % 256);          // 1..256
+        float x, y, z;
+        if (i % 3 == 0) { x = y = z = (float)(m / 10.0); }
+        else {
+            y = (float)(26.0 * U(rng)); z = (float)(26.0 * U(rng));
+            const double den = (1 - S) / 3 + S;
+            if (fabs(den) < 1e-3) continue;
+            x = (float)((m / 10.0 - (1 - S) * ((double)y + z) / 3) / den);
+        }
+        int ul = (int)(rng() % 9) - 4;
+        for (int q = 0; q < (ul < 0 ? -ul : ul); q++) x = nextafterf(x, ul < 0 ? -INFINITY : INFINITY);
+        if (i % 3 == 0) { y = z = x; if (i % 2) y = nextafterf(y, INFINITY); }
+        check(x, y, z, S, true);
+        check(y, x, z, S, true);
+        check(z, y, x, S, true);
+    }
+    const float sp[] = {0.0f, -0.0f, -1.0f, 1e-40f, 255.0f, 25.5f, 25.6f, 1e30f, 3e38f, INFINITY, -INFINITY, NAN, 1e-45f};
+    for (float a : sp) for (float b : sp) for (float c : sp) for (double S : sats) check(a, b, c, S, true);
+    printf("random: %ld of %ld decided in FP32 (%.6f); boundary cases %ld, undecided %ld; wrong %ld\n", decided, n, decided / (double)n, nadv, undec_adv, bad);
+    return bad != 0;
+}
+'''.replace("@HDR@", hdr))
+    exe = tmp_path / "tn"
+    subprocess.run(["g++", "-O2", "-ffp-contract=off", "-o", str(exe), str(src)], check=True)
+    r = subprocess.run([str(exe)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout
+    frac = float(r.stdout.split("(")[1].split(")")[0])
+    assert frac > 0.999, r.stdout

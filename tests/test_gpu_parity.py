@@ -216,6 +216,35 @@ def test_tonemap_exact(gpu_ctx, oracle):
     assert d.max() <= 1 and (d > 0).mean() < 1e-3
 
 
+def test_tonemap_at_the_byte_boundaries(gpu_ctx, oracle):
+    """K2 decides a byte in FP32 where its error bound allows and runs the reference's double chain otherwise
+    (csrc/tone.cuh). Pixels placed within a few ulp of every byte boundary — grey, coloured, negative, overexposed,
+    infinite and NaN — through the `stars` addend must give the oracle's words exactly, at several saturations."""
+    sc = scenes.single_galaxy_scene("Spiral", 128, "outside")
+    gpu_ctx.upload(sc)
+    img = gpu_ctx.render()
+    h, w = img.shape[:2]
+    rng = np.random.default_rng(11)
+    for sat, exposure in ((1.0, 1.0), (1.467, 0.767), (0.35, 1.0), (-0.5, 1.3), (4.0, 1.0)):
+        m = rng.integers(1, 257, size=(h, w)).astype(np.float64) / 10.0 * exposure        # the value a channel should reach
+        tgt = np.empty((h, w, 3), dtype=np.float64)
+        grey = rng.random((h, w)) < 0.4
+        y = rng.uniform(0, 26, (h, w)); z = rng.uniform(0, 26, (h, w))
+        den = (1 - sat) / 3 + sat
+        x = (m - (1 - sat) * (y + z) / 3) / den                 # the saturated first channel lands on m
+        tgt[..., 0] = np.where(grey, m, x); tgt[..., 1] = np.where(grey, m, y); tgt[..., 2] = np.where(grey, m, z)
+        tgt = tgt.astype(np.float32)
+        ul = rng.integers(-4, 5, size=tgt.shape)
+        tgt = (tgt.view(np.int32) + ul.astype(np.int32)).view(np.float32)         # +- 4 ulp around the boundary
+        special = rng.random((h, w)) < 0.01
+        tgt[special] = rng.choice(np.array([0.0, -3.0, 1e-40, 25.5, 25.6, 1e30, 3e38, np.inf, -np.inf, np.nan], dtype=np.float32),
+                                  size=(int(special.sum()), 3))
+        stars = (tgt - img).astype(np.float32)                     # img + stars is tgt up to an ulp: still on the boundary
+        a_g, s_g = gpu_ctx.tonemap(exposure, 1.0, sat, stars)
+        a_c, s_c = oracle.tonemap(img, exposure, 1.0, sat, stars)
+        assert np.array_equal(a_g, a_c) and np.array_equal(s_g, s_c), (sat, exposure, int((a_g != a_c).sum()))
+
+
 def test_tonemap_ragged_sizes(gpu_ctx, oracle):
     """pixel counts that are not a multiple of the kernel's 4-pixel vector width (tail path), with stars"""
     for size in (33, 35, 37):
@@ -228,8 +257,12 @@ def test_tonemap_ragged_sizes(gpu_ctx, oracle):
         assert np.array_equal(a_g, a_c) and np.array_equal(s_g, s_c), size
     # every remainder of the pixel count modulo 4, fewer pixels than one vector (scalar kernel), gamma != 1
     full = scenes.single_galaxy_scene("Sombrero", 64, "oblique")
-    for (w, h), gamma in (((33, 2), 1.0), ((33, 3), 0.8), ((31, 4), 1.0), ((3, 1), 0.8), ((1, 1), 1.0), ((2, 1), 1.3)):
-        gpu_ctx.upload(full.tile(20, 30, w, h))
+    # ... and frames large enough for the TMA-pipelined kernel (>= 2048 groups of four pixels) whose last 256-group tile is
+    # partial, with and without a remainder modulo 4
+    big = scenes.single_galaxy_scene("Sombrero", 160, "oblique")
+    for (w, h), gamma in (((33, 2), 1.0), ((33, 3), 0.8), ((31, 4), 1.0), ((3, 1), 0.8), ((1, 1), 1.0), ((2, 1), 1.3),
+                          ((100, 100), 1.0), ((101, 99), 0.8), ((128, 97), 1.0), ((131, 127), 1.0)):
+        gpu_ctx.upload((big if w >= 100 else full).tile(20, 30, w, h))
         img = gpu_ctx.render()
         assert img.shape[:2] == (h, w)
         stars = np.random.default_rng(w * h).uniform(0, 2, img.shape).astype(np.float32)
