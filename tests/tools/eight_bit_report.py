@@ -1,8 +1,8 @@
 """The reference harness's own pass criterion on its own workload: every shipped galaxy at 64x64 from the singleGalaxy.sh
 view (tools/galaxy_repro.py:1024-1032), 8-bit RGB values of the CUDA path against the CPU oracle's, which the harness
-requires to be IDENTICAL (compare_images, :988-995). Prints one line per fixture.  python tools/eight_bit_report.py"""
+requires to be IDENTICAL (compare_images, :988-995). Prints one line per fixture.  python tests/tools/eight_bit_report.py"""
 import os, sys
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
 import numpy as np
 import oracle_lib, scenes
