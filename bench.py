@@ -332,9 +332,9 @@ def run_jobs(ctx, jobs, my_ids, rank, world, barrier, reduce_max, reduce_sum, un
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the dominant kernel, from an `ncu --set full` capture;
 # it belongs to the library build the capture was taken with and says so (traffic_source). The 50 MB framebuffer is
 # still in the 126 MB L2 when K1 ends, so DRAM sees ~8 MB; the algorithmic bytes are 12 B/pixel = 50 MB.
-K1_DRAM_TRAFFIC = {"spiral_2048_oblique_orbit": (182784 + 3159552, "profiles/r02_k1_ncu_summary.csv"),
-                   "spiral_2048_cli_view": (100864 + 3268608, "profiles/r02_k1_cli_ncu_summary.csv")}
-K2_DRAM_TRAFFIC = {2048 * 2048: (50342912 + 3042048, "profiles/r02b_k2_ncu_summary.csv")}
+K1_DRAM_TRAFFIC = {"spiral_2048_oblique_orbit": (425728 + 3480576, "profiles/r02_k1_ncu_summary.csv"),
+                   "spiral_2048_cli_view": (116992 + 4035840, "profiles/r02_k1_cli_ncu_summary.csv")}
+K2_DRAM_TRAFFIC = {2048 * 2048: (50342400 + 2795776, "profiles/r02b_k2_ncu_summary.csv")}
 
 
 def time_frames(ctx, scenes_, Wm, K, stream, flush, barrier, after_kernels=None):
