@@ -684,15 +684,17 @@ k1_march(const __grid_constant__ DScene sc, float *__restrict__ out, unsigned lo
 // HBM-bound: 12 B (+12 B stars) read, 8 B written per pixel. What is written is one BYTE per channel,
 // (int)clamp(10 v), and the reference forms v through float -> double -> float -> double -> float: 13 conversions per
 // pixel on the quarter-rate XU pipe, which was this kernel's limit (ncu r02: XU 76 % busy, HBM at half its rate).
-// tone_fast forms the same v in plain FP32 together with a proven bound on its distance from the reference's float,
-// and decides the byte whenever no integer lies within that bound of 10 v; otherwise (about one pixel in 10^4) the
-// pixel goes through tone_exact, the reference's own chain. The result is the reference's byte in every case.
+// csrc/tone.cuh forms the same value in plain FP32 together with a proven bound on its distance from the reference's
+// float, and decides the byte whenever no byte boundary lies within that bound; otherwise (about one pixel in 10^3 - 10^4)
+// the pixel goes through tone_exact, the reference's own chain. The result is the reference's byte in every case.
 
+// float(pow(double(x), gamma)) like Buffer2D::PostProcess; out of line: twelve inlined copies per thread spill
+__device__ __noinline__ float pow_gamma(float x, double gamma) { return (float)pow((double)x, gamma); }
 template <bool GAMMA>
 __device__ __forceinline__ void tone_px(float x, float y, float z, float inv_exposure, double gamma, double saturation,
                                         const tone::ToneSat k, uint32_t &argb, uint32_t &shadow) {
     x = __fmul_rn(x, inv_exposure); y = __fmul_rn(y, inv_exposure); z = __fmul_rn(z, inv_exposure);
-    if (GAMMA) { x = (float)pow((double)x, gamma); y = (float)pow((double)y, gamma); z = (float)pow((double)z, gamma); }
+    if (GAMMA) { x = pow_gamma(x, gamma); y = pow_gamma(y, gamma); z = pow_gamma(z, gamma); }
     tone::tone_mapped(x, y, z, saturation, k, argb, shadow);
 }
 
@@ -701,11 +703,11 @@ __global__ void __launch_bounds__(256, 4)
 k2_tonemap(const float *__restrict__ rgb, const float *__restrict__ stars, uint32_t *__restrict__ argb,
            uint32_t *__restrict__ shadow, size_t n, float inv_exposure, double gamma, double saturation,
            const tone::ToneSat ks) {
-    // Persistent grid (4 CTAs per SM, 64 registers per thread), grid-stride, FOUR independent pixels per thread and iteration with all
-    // loads issued before the arithmetic: a single pixel per iteration is a chain of dependent load
+    // The scalar kernel: buffers that are not 16-byte aligned, frames of fewer than four pixels, and the n % 4 remainder
+    // of k2_tonemap_v4. Persistent grid (4 CTAs per SM), grid-stride, FOUR independent pixels per thread and iteration
+    // with all loads issued before the arithmetic: a single pixel per iteration is a chain of dependent load
     // latencies. The three 4-byte loads of a warp cover the same 384 contiguous bytes, so every fetched
-    // sector is fully used. Once HBM is fed, the bound is the reference's float<->double traffic:
-    // 16 conversions per pixel on the quarter-rate XU pipe.
+    // sector is fully used.
     const size_t nth = (size_t)gridDim.x * blockDim.x;
     size_t k = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
     for (; k + 3 * nth < n; k += 4 * nth) {
@@ -755,8 +757,6 @@ k2_tonemap(const float *__restrict__ rgb, const float *__restrict__ stars, uint3
 #ifndef K2_MINB
 #define K2_MINB 6
 #endif
-// float(pow(double(x), gamma)) like Buffer2D::PostProcess; out of line: twelve inlined copies per thread spill
-__device__ __noinline__ float pow_gamma(float x, double gamma) { return (float)pow((double)x, gamma); }
 template <bool GAMMA>
 __device__ __forceinline__ void expose_px(float &x, float &y, float &z, float inv_exposure, double gamma) {
     x = __fmul_rn(x, inv_exposure); y = __fmul_rn(y, inv_exposure); z = __fmul_rn(z, inv_exposure);
