@@ -267,10 +267,14 @@ class SharedHostFrame:
             os.unlink(self.path)
 
 
-def run_jobs(ctx, jobs, my_ids, rank, world, barrier, reduce_max, reduce_sum, unit_name, e2e_contexts=3):
-    """A list of independent render jobs (frames of a sequence, galaxies of a batch): this rank renders jobs[i] for i in
-    my_ids, in that order. No collective in the data path. Device time over the whole list with CUDA events on the
-    context's stream (max over ranks); e2e through host buffers, frames alternating over e2e_contexts contexts."""
+def run_jobs(ctx, jobs, my_ids, rank, world, barrier, reduce_max, reduce_sum, unit_name, e2e_contexts=3, queue=None):
+    """A list of independent render jobs (frames of a sequence, galaxies of a batch). Static: this rank renders jobs[i]
+    for i in my_ids, in that order. With `queue` (parallel.JobQueue, one shared counter for all ranks) the device leg takes
+    its jobs from the queue instead - a rank asks for the next one when its GPU has finished the last (render_device
+    returns after the kernel) - and my_ids only says whose exact work this rank COUNTS beforehand (the totals are summed
+    over the ranks either way); the e2e leg then replays the jobs this rank ended up with. No collective in the data path.
+    Device time over the whole list with CUDA events on the context's stream (max over ranks); e2e through host buffers,
+    frames alternating over e2e_contexts contexts."""
     import torch
     from gamer_b200.rasterizer import Context
     mine = [jobs[i] for i in my_ids]
@@ -287,10 +291,19 @@ def run_jobs(ctx, jobs, my_ids, rank, world, barrier, reduce_max, reduce_sum, un
     barrier()
     l0 = ctx.launches()
     e0.record(stream)
-    for sc in mine:
-        ctx.upload(sc)
-        ctx.render_device()
-        ctx.tonemap_device(1.0, 1.0, 1.0)
+    if queue is None:
+        for sc in mine:
+            ctx.upload(sc)
+            ctx.render_device()
+            ctx.tonemap_device(1.0, 1.0, 1.0)
+    else:
+        taken = []
+        for j in queue:
+            taken.append(j)
+            ctx.upload(jobs[j])
+            ctx.render_device()
+            ctx.tonemap_device(1.0, 1.0, 1.0)
+        mine = [jobs[j] for j in taken]
     e1.record(stream)
     barrier()
     dev_ms = e0.elapsed_time(e1) if mine else 0.0
@@ -601,11 +614,16 @@ def run_ours(args):
         for i in range(n_gal):
             ctx.upload(scenes.random_galaxy_scene(i, 64))
             costs.append(algorithmic_flop(ctx.render_counted()) + 1.0)
-        table = parallel.longest_job_first(costs, world)
-        r = run_jobs(ctx, batch, table[rank], rank, world, barrier, reduce_max, reduce_sum, "galaxies", args.e2e_contexts)
+        # one queue for all ranks in longest-job-first order (parallel.JobQueue): the static table of
+        # parallel.longest_job_first balances the estimated costs and left 6.7 % between the slowest rank and the mean
+        # at N = 8 (232 ms against 217.5); a rank that finishes early now takes the next job instead
+        order = parallel.ljf_order(costs)
+        r = run_jobs(ctx, batch, parallel.units_of(rank, world, n_gal), rank, world, barrier, reduce_max, reduce_sum, "galaxies",
+                     args.e2e_contexts, queue=parallel.JobQueue(order, "batch"))
         if rank == 0:
             r["config"] = {"workload": "batch_256_1024", "galaxies": n_gal, "of": 256, "size": 1024, "seed": 20261104,
-                           "parallelism": f"longest-job-first over {world} ranks on each galaxy's exact work at 64^2 (parallel.longest_job_first)",
+                           "parallelism": f"one job queue over {world} ranks, longest job first by each galaxy's exact work at 64^2 "
+                                          "(parallel.JobQueue: a shared counter in the c10d store, control plane only)",
                            "l2": "every job is a different galaxy; no flush between them"}
             also["batch_256_1024"] = r
         if world == 1:

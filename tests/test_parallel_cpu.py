@@ -61,6 +61,20 @@ WORKER = textwrap.dedent("""
     sm = parallel.sum_over_ranks([1.0], "cpu")[0]
     assert mx == world - 1 and sm == world
     assert parallel.units_of(rank, world, 5) == list(range(rank, 5, world))
+    # the shared job queue: every index of the order handed out exactly once over the two ranks
+    import time, random
+    order = parallel.ljf_order([float((7 * i) % 13) for i in range(40)])
+    random.seed(rank)
+    mine = []
+    for j in parallel.JobQueue(order, "t1"):
+        mine.append(j); time.sleep(random.random() * 2e-3)
+    got = [None, None]
+    dist.all_gather_object(got, mine)
+    assert sorted(got[0] + got[1]) == list(range(40)), got
+    assert all(order.index(a) < order.index(b) for m in got for a, b in zip(m, m[1:])), "a rank's jobs are not in queue order"
+    assert len(got[0]) > 5 and len(got[1]) > 5, got
+    assert list(parallel.JobQueue(order, "t1")) == []          # the same queue is spent; a new name is a new queue
+    dist.barrier()
     dist.destroy_process_group()
     print("rank %d ok" % rank, flush=True)   # one write for the text: the ranks share the pipe
 """)
@@ -105,6 +119,12 @@ def test_longest_job_first_balances_and_is_deterministic():
     lpt = max(sum(skew[j] for j in r) for r in parallel.longest_job_first(skew, 8))
     mod = max(sum(skew[j] for j in parallel.units_of(r, 8, 64)) for r in range(8))
     assert lpt <= mod
+
+
+def test_job_queue_single_process_is_the_order_itself():
+    order = parallel.ljf_order([3.0, 9.0, 1.0, 9.0])
+    assert order == [1, 3, 0, 2]
+    assert list(parallel.JobQueue(order, "solo")) == order
 
 
 def test_job_cost_counts_octaves_of_active_components():
