@@ -209,11 +209,14 @@ def test_tonemap_exact(gpu_ctx, oracle):
     a_g, s_g = gpu_ctx.tonemap(0.767, 1.0, 1.467, stars)
     a_c, s_c = oracle.tonemap(img, 0.767, 1.0, 1.467, stars)
     assert np.array_equal(a_g, a_c) and np.array_equal(s_g, s_c)
-    # gamma != 1 goes through pow(): allow one 8-bit step on a vanishing fraction of channels
-    a_g, s_g = gpu_ctx.tonemap(0.767, 0.867, 1.467)
-    a_c, s_c = oracle.tonemap(img, 0.767, 0.867, 1.467)
-    d = np.abs(((s_g[..., None] >> np.array([16, 8, 0])) & 255).astype(int) - ((s_c[..., None] >> np.array([16, 8, 0])) & 255).astype(int))
-    assert d.max() <= 1 and (d > 0).mean() < 1e-3
+    # gamma != 1 goes through pow() in double on both sides: CUDA's (<= 2 ulp) and glibc's (< 1 ulp) can give different
+    # FLOATS only when the exact power lies within ~2^-52 of a float rounding boundary (~1e-8 per call), and the byte
+    # differs only if that float also sits on a byte boundary. On these fixed inputs (and on 15.7 M channel values at
+    # 512^2 for five gammas, measured once) every word is identical, so the test asks for that.
+    for gamma in (0.867, 2.2):
+        a_g, s_g = gpu_ctx.tonemap(0.767, gamma, 1.467)
+        a_c, s_c = oracle.tonemap(img, 0.767, gamma, 1.467)
+        assert np.array_equal(a_g, a_c) and np.array_equal(s_g, s_c), gamma
 
 
 def test_tonemap_at_the_byte_boundaries(gpu_ctx, oracle):
