@@ -10,8 +10,9 @@ using namespace gmarch;
 namespace {
 
 // ONE persistent CTA of K1_WARPS warps per SM (80 registers per thread); each warp draws 8 x 4 pixel tiles from a
-// ticket counter. The noise tables (2 x 64 KB) and the per-thread ray records (48 KB) then exist once per SM.
-// Measured: 24 x 1 = 12 x 2 warps; 10 x 2 (96 registers) and 8 x 3 are 2-3 % slower.
+// ticket counter. The noise tables (2 x 64 KB) and the per-thread ray records (84 KB) then exist once per SM.
+// Measured: 24 x 1 = 12 x 2 warps; 10 x 2 (96 registers) and 8 x 3 are 2-3 % slower; 28 x 1 (72 registers, 48 B of spill
+// stores) is 1.0 % faster on the exterior view and 0.8 % slower on the in-disk one.
 #ifndef K1_WARPS
 #define K1_WARPS 24
 #endif
@@ -26,26 +27,33 @@ struct NoiseCtx {
 
 // The per-thread ray record of march(): K1_REC_WORDS floats per thread in shared memory behind the noise tables,
 // word k of thread t at [k][t] (conflict free). volatile: every access is a real load or store.
-// Words: 0-2 p, 3-5 dir, 6-8 origin, 9-11 camera relative to the galaxy, 12 length, 13 loop bound (-inf: no ray),
-// 14 step, 15 weight, 16 distance marched (+inf: no ray), 17 / 18 the fast-sample windows (marched < [17]: the step is
-// certainly 0.01 and the ray alive; marched > [18]: certainly minRayStep), 19 whether the winding in 26-28 came from the
-// table (1) or from the direct evaluation (0), 20 twirl group of the point in 21-23 (-1: none yet).
-#define REC_HI_LIM 17
-#define REC_LO_FROM 18
-#define REC_WTAB 19
-#define REC_TG 20
+// Words: 0-2 p, 3-5 dir, 6-8 origin, 9 length, 10 loop bound (-inf: no ray), 11 step, 12 weight, 13 distance marched
+// (+inf: no ray), 14 / 15 the fast-sample windows (marched < [14]: the step is certainly 0.01 and the ray alive;
+// marched > [15]: certainly minRayStep), 16 whether the winding in 24-25 came from the table (1) or from the direct
+// evaluation (0), 17 twirl group of the point in 18-20 (-1: none yet). The camera relative to the galaxy is NOT here: it
+// is the same for every ray and is formed from the constant bank where it is needed (three subtractions, the same
+// three the record's loads were). 28 words: 24 or 28 warps fit beside the noise tables.
+#define REC_LEN 9
+#define REC_THR 10
+#define REC_STEP 11
+#define REC_WEIGHT 12
+#define REC_MARCHED 13
+#define REC_HI_LIM 14
+#define REC_LO_FROM 15
+#define REC_WTAB 16
+#define REC_TG 17
 // values of ONE in-slab sample shared by every component of the galaxy. They live here and not in registers because
 // they are needed on both sides of the noise calls: what ptxas cannot keep in a register across a call it keeps in
 // LOCAL memory for its whole life, and with 768 threads a 96-byte stack is 72 KB per SM against 28 KB of L1 (ncu: 61 %
 // local hit rate, long-scoreboard stalls on every reload). A shared-memory load costs one issue slot and ~25 cycles.
-#define REC_DOTT 24      // height above the plane along the axis (exact)
-#define REC_PLEN 25      // |P| fast float
-#define REC_W 26         // getWinding(radius) narrowed
-#define REC_WD 27        // ... in double (it feeds the twirl angle): words 27, 28
-#define REC_THETA 29     // atan2(q.x, q.z), q = rotmat * P
-#define REC_IVAL 30      // val * weight of the component being evaluated (live across its noise call)
-#define REC_K 31         // index of the component being evaluated (the loop counter, as float bits)
-#define K1_REC_WORDS 32
+#define REC_DOTT 21      // height above the plane along the axis (exact)
+#define REC_PLEN 22      // |P| fast float
+#define REC_WT 23        // float(getWinding(radius)) + atan2(q.x, q.z), q = rotmat * P: the arm phase without delta and
+                         // the arm's own offset (value arithmetic); NaN: not formed yet for this sample
+#define REC_WD 24        // getWinding(radius) in double (it feeds the twirl angle): words 24, 25
+#define REC_IVAL 26      // val * weight of the component being evaluated (live across its noise call)
+#define REC_K 27         // index of the component being evaluated (the loop counter, as float bits)
+#define K1_REC_WORDS 28
 static_assert(GN_DYN_SMEM + K1_REC_WORDS * K1_THREADS * 4u <= 232448u, "tables + ray records exceed the 227 KB a CTA can have");
 struct Rec {
     volatile float *base;
@@ -69,7 +77,6 @@ __device__ __noinline__ void winding_direct(const DGalaxy &g, float radius, floa
     const double e = dmath::exp_nc(dmath::div_nc(-0.25, __dmul_rn(0.5, r)));
     const double Wd = __dmul_rn(__dmul_rn(dmath::atan_nc(dmath::div_nc(e, g.winding_b)), 2.0), g.winding_n);
     rec_set_d(rec, REC_WD, Wd);
-    rec[REC_W] = (float)Wd;
     rec[REC_WTAB] = 0.0f;
 }
 // radius exactly as getRadius returns it: float |P| (double sqrt) / float axis.x
@@ -102,14 +109,13 @@ __device__ __forceinline__ void arm_base(const DScene &sc, const DGalaxy &g, con
             v = __fma_rn(v, x, c23.y); v = __fma_rn(v, x, c23.x);
             v = __fma_rn(v, x, c01.y); v = __fma_rn(v, x, c01.x);
             rec_set_d(rec, REC_WD, v);
-            rec[REC_W] = (float)v;
             rec[REC_WTAB] = 1.0f;
             done = true;
         }
     }
     if (!done) winding_direct(g, radius, const_cast<float *>(rec.base));
     f3 q = g.rot_identity ? P : q_rotate(g.rot, P);
-    rec[REC_THETA] = dmath::atan2f_fast(q.x, q.z);
+    rec[REC_WT] = (float)rec_get_d(rec, REC_WD) + dmath::atan2f_fast(q.x, q.z);
 }
 
 // findDifference (galaxycomponent.h:103-118) with M_PI = 3.14159265 (util.h:20)
@@ -219,7 +225,7 @@ __device__ __forceinline__ void eval_component(const DScene &sc, const DGalaxy &
     const int cls = c.cls;
     if (cls == GAMER_CLASS_BULGE) {   // galaxycomponents.cpp:5-25 — evaluated at every sample, no gates
         const f3 pb = {rec[0], rec[1], rec[2]};
-        const float i = bulge_term(c.bk * rec[15], c.r0, sqrta(fmaf(pb.z, pb.z, fmaf(pb.y, pb.y, pb.x * pb.x))));
+        const float i = bulge_term(c.bk * rec[REC_WEIGHT], c.r0, sqrta(fmaf(pb.z, pb.z, fmaf(pb.y, pb.y, pb.x * pb.x))));
         Ir = fmaf(i, c.spec[0], Ir); Ig = fmaf(i, c.spec[1], Ig); Ib = fmaf(i, c.spec[2], Ib);
         if (COUNT) cn.evals++;
         return;
@@ -256,13 +262,13 @@ __device__ __forceinline__ void eval_component(const DScene &sc, const DGalaxy &
     if (flags & DC_HAS_ARM) {
         // getWinding / getTheta of the sample, formed by the first component that gets this far (a NaN marks "not yet"):
         // a fifth of the in-slab samples of an exterior view lie beyond every armed component's radial cut-off
-        if (rec[REC_W] != rec[REC_W]) {
+        if (rec[REC_WT] != rec[REC_WT]) {
             const f3 pa = {rec[0], rec[1], rec[2]};
             const f3 orient = {g.orient[0], g.orient[1], g.orient[2]};
             arm_base(sc, g, rec, ORIENT_Y ? f3{pa.x, 0.0f, pa.z} : v_sub(pa, v_mul(orient, rec[REC_DOTT])));
         }
         // winding - (-theta + disp): W + theta + delta - disp
-        if (c.arm15 > 0.0f) val *= arm_value(g, c.arm15, rec[REC_W] + rec[REC_THETA] + c.delta);
+        if (c.arm15 > 0.0f) val *= arm_value(g, c.arm15, rec[REC_WT] + c.delta);
         else val *= arm_value_neg(g, c.arm15, c.delta_d, const_cast<float *>(rec.base), ORIENT_Y);
         if (flags & DC_HAS_WINDING) {
             winding = __dmul_rn(rec_get_d(rec, REC_WD), c.winding_d);
@@ -282,7 +288,7 @@ __device__ __forceinline__ void eval_component(const DScene &sc, const DGalaxy &
         }
     }
     {
-        const float ival0 = val * rec[15];
+        const float ival0 = val * rec[REC_WEIGHT];
         if (!(ival0 > 0.0005f)) return;
         rec[REC_IVAL] = ival0;
     }
@@ -399,11 +405,10 @@ __device__ __forceinline__ void march(const DScene &sc, const DGalaxy &g, const 
         rec[0] = origin.x; rec[1] = origin.y; rec[2] = origin.z;      // p starts at origin
         rec[3] = dir.x; rec[4] = dir.y; rec[5] = dir.z;
         rec[6] = origin.x; rec[7] = origin.y; rec[8] = origin.z;
-        rec[9] = camrel.x; rec[10] = camrel.y; rec[11] = camrel.z;
-        rec[12] = length_f;
-        rec[16] = active ? 0.0f : INFINITY;            // distance marched so far (estimate, see the run loop)
+        rec[REC_LEN] = length_f;
+        rec[REC_MARCHED] = active ? 0.0f : INFINITY;            // distance marched so far (estimate, see the run loop)
         // the first test uses step = rayStep; a ray that is not marched has no bound at all
-        rec[13] = active ? __double2float_ru(__dadd_rn((double)length_f, sc.ray_step)) : -INFINITY;
+        rec[REC_THR] = active ? __double2float_ru(__dadd_rn((double)length_f, sc.ray_step)) : -INFINITY;
         // Every ray starts at the camera, so p - camera is parallel to dir and |p - camera| = dist0 - (distance marched)
         // up to rounding (bounded by sc.alive_margin like the loop test): it falls monotonically along the march. The
         // step clamp(|p - camera| * rayStep, minRayStep, 0.01) is therefore CERTAINLY 0.01 while marched < dist0 - d_hi -
@@ -426,13 +431,13 @@ __device__ __forceinline__ void march(const DScene &sc, const DGalaxy &g, const 
         {   // ---- run of off-slab samples ---------------------------------------------------------------------
             f3 p = {rec[0], rec[1], rec[2]};
             const f3 dir = {rec[3], rec[4], rec[5]};
-            const f3 camrel_ = {rec[9], rec[10], rec[11]};
-            const float length_f = rec[12];
-            float thr = rec[13];
+            const f3 camrel_ = v_sub({sc.cam[0], sc.cam[1], sc.cam[2]}, {g.pos[0], g.pos[1], g.pos[2]});   // = camrel, bit for bit
+            const float length_f = rec[REC_LEN];
+            float thr = rec[REC_THR];
             // The exact loop test costs ten instructions and decides only at the very end of a ray: d = -dot(p - origin,
             // dir) differs from the running sum of the steps by rounding alone (bounded by sc.alive_margin, scene_build.cpp),
             // so while that sum stays below length - margin the ray is certainly alive (the bound is length + step).
-            float marched = rec[16];
+            float marched = rec[REC_MARCHED];
             const float sure_below = length_f - sc.alive_margin;
             float stepf = 0.f, weight = 0.f;
             // ll = normalized(isp2 - origin) of the reference is -dir bit for bit (negation commutes with every
@@ -542,7 +547,7 @@ __device__ __forceinline__ void march(const DScene &sc, const DGalaxy &g, const 
                 if (__any_sync(FULL, need) || !any_alive) break;
             }
             rec[0] = p.x; rec[1] = p.y; rec[2] = p.z;
-            rec[13] = thr; rec[14] = stepf; rec[15] = weight; rec[16] = marched;
+            rec[REC_THR] = thr; rec[REC_STEP] = stepf; rec[REC_WEIGHT] = weight; rec[REC_MARCHED] = marched;
         }
         if (!any_alive) break;
         if (need) {   // ---- one in-slab sample ------------------------------------------------------------------
@@ -553,7 +558,7 @@ __device__ __forceinline__ void march(const DScene &sc, const DGalaxy &g, const 
                 const f3 P = ORIENT_Y ? f3{sp.x, 0.0f, sp.z} : v_sub(sp, v_mul(orient, dott));   // p.y - p.y*1 = 0
                 rec[REC_DOTT] = dott;
                 rec[REC_PLEN] = sqrta(fmaf(P.z, P.z, fmaf(P.y, P.y, P.x * P.x)));
-                rec[REC_W] = __int_as_float(0x7fc00000);       // getWinding / getTheta: not formed yet (eval_component)
+                rec[REC_WT] = __int_as_float(0x7fc00000);       // getWinding / getTheta: not formed yet (eval_component)
             }
 #ifndef K1_NO_TWIRL_CACHE
             if (g.any_tshare) rec[REC_TG] = -1.0f;
@@ -565,9 +570,9 @@ __device__ __forceinline__ void march(const DScene &sc, const DGalaxy &g, const 
             if (COUNT) { cn.samples++; cn.gates += g.comp_count + g.noop_count; }
             const f3 dir = {rec[3], rec[4], rec[5]};
             const f3 p0 = {rec[0], rec[1], rec[2]};
-            const float stepf = rec[14];
+            const float stepf = rec[REC_STEP];
             const f3 pn = v_sub(p0, v_mul(dir, stepf));
-            rec[16] = rec[16] + stepf;
+            rec[REC_MARCHED] = rec[REC_MARCHED] + stepf;
             rec[0] = pn.x; rec[1] = pn.y; rec[2] = pn.z;
             Ir = fmaxf(0.0f, Ir); Ig = fmaxf(0.0f, Ig); Ib = fmaxf(0.0f, Ib);   // Util::floor (util.h:62-64)
         }
