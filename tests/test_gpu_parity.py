@@ -242,7 +242,8 @@ def test_tonemap_at_the_byte_boundaries(gpu_ctx, oracle):
         special = rng.random((h, w)) < 0.01
         tgt[special] = rng.choice(np.array([0.0, -3.0, 1e-40, 25.5, 25.6, 1e30, 3e38, np.inf, -np.inf, np.nan], dtype=np.float32),
                                   size=(int(special.sum()), 3))
-        stars = (tgt - img).astype(np.float32)                     # img + stars is tgt up to an ulp: still on the boundary
+        with np.errstate(invalid="ignore", over="ignore"):           # the special values: inf - x, nan - x
+            stars = (tgt - img).astype(np.float32)                 # img + stars is tgt up to an ulp: still on the boundary
         a_g, s_g = gpu_ctx.tonemap(exposure, 1.0, sat, stars)
         a_c, s_c = oracle.tonemap(img, exposure, 1.0, sat, stars)
         assert np.array_equal(a_g, a_c) and np.array_equal(s_g, s_c), (sat, exposure, int((a_g != a_c).sum()))
